@@ -1,0 +1,132 @@
+"""ctypes binding of libedison_b200.so (include/edison_b200.h).  numpy arrays in, numpy arrays out."""
+import ctypes
+import os
+
+import numpy as np
+
+FRAME_LEN, N_MEL, N_COEFF, N_FRAMES, N_CLASSES = 1024, 32, 13, 31, 10
+NET_IN = N_FRAMES * N_COEFF
+SOFTMAX_CMSIS_REF, SOFTMAX_CMSIS_SIMD, SOFTMAX_NNOM_LOCAL = 0, 1, 2
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_lib = None
+
+
+class EdisonError(RuntimeError):
+    pass
+
+
+class _Cfg(ctypes.Structure):
+    _fields_ = [("device", ctypes.c_int), ("data_dir", ctypes.c_char_p), ("softmax_mode", ctypes.c_int),
+                ("chunk_clips", ctypes.c_size_t)]
+
+
+def lib_path():
+    return os.path.join(_HERE, "libedison_b200.so")
+
+
+def lib():
+    """Load the shared library (no CUDA call is made by loading it)."""
+    global _lib
+    if _lib is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise EdisonError("%s is missing: run `make` (or __graft_entry__.build()) first; there is no fallback" % p)
+        L = ctypes.CDLL(p)
+        vp, sz, ci = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int
+        L.edison_init.argtypes = [ctypes.POINTER(_Cfg)]
+        L.edison_last_error.restype = ctypes.c_char_p
+        L.edison_launch_count.restype = ctypes.c_ulonglong
+        L.edison_host_alloc.restype = vp
+        L.edison_host_alloc.argtypes = [sz]
+        L.edison_host_free.argtypes = [vp]
+        L.edison_mfcc_q15_batch.argtypes = [vp, sz, vp]
+        L.edison_mfcc_q15_clips.argtypes = [vp, sz, sz, sz, vp, vp]
+        L.edison_kws_batch.argtypes = [vp, sz, sz, vp, vp, vp]
+        L.edison_infer_q7_batch.argtypes = [vp, sz, vp, vp]
+        L.edison_mfcc_q15_clips_dev.argtypes = [vp, sz, sz, sz, vp, vp, vp]
+        L.edison_infer_q7_batch_dev.argtypes = [vp, sz, vp, vp, vp]
+        L.edison_kws_batch_dev.argtypes = [vp, sz, sz, vp, vp, vp, vp]
+        L.edison_sync.argtypes = [vp]
+        L.edison_debug_sqrt_q31.argtypes = [vp, sz, vp]
+        L.edison_debug_mag_sweep.argtypes = [ctypes.c_uint32, ctypes.c_uint32, vp, vp]
+        L.edison_set_softmax_mode.argtypes = [ci]
+        L.audioCalcMFCCs.argtypes = [vp, ctypes.POINTER(ctypes.POINTER(ctypes.c_int16))]
+        L.aiRunInference.argtypes = [vp, vp]
+        L.aiGetKeywordFromIndex.restype = ctypes.c_char_p
+        L.aiGetKeywordFromIndex.argtypes = [ctypes.c_uint32]
+        L.aiGetKeywordCount.restype = ctypes.c_uint32
+        L.edison_net_input_window.restype = ctypes.POINTER(ctypes.c_int8)
+        _lib = L
+    return _lib
+
+
+def check(rc, what="edison"):
+    if rc != 0:
+        raise EdisonError("%s failed (%d): %s" % (what, rc, lib().edison_last_error().decode(errors="replace")))
+
+
+def init(device=-1, data_dir=None, softmax_mode=SOFTMAX_CMSIS_REF, chunk_clips=0):
+    cfg = _Cfg(device, data_dir.encode() if data_dir else None, softmax_mode, chunk_clips)
+    check(lib().edison_init(ctypes.byref(cfg)), "edison_init")
+
+
+def shutdown():
+    lib().edison_shutdown()
+
+
+def set_softmax_mode(mode):
+    check(lib().edison_set_softmax_mode(mode), "edison_set_softmax_mode")
+
+
+def launch_count():
+    return int(lib().edison_launch_count())
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+
+
+def mfcc_q15_batch(pcm):
+    """pcm: int16 [n_frames, 1024] (or flat) -> int16 [n_frames, 32]   (audioCalcMFCCs per frame)"""
+    pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
+    if pcm.size % FRAME_LEN:
+        raise ValueError("pcm length must be a multiple of 1024")
+    n = pcm.size // FRAME_LEN
+    out = np.empty((n, N_MEL), dtype=np.int16)
+    check(lib().edison_mfcc_q15_batch(_p(pcm), n, _p(out)), "edison_mfcc_q15_batch")
+    return out
+
+
+def mfcc_q15_clips(pcm, n_clips, frames_per_clip, clip_stride, want_mfcc=True, want_net_in=True):
+    pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
+    need = (n_clips - 1) * clip_stride + frames_per_clip * FRAME_LEN if n_clips else 0
+    if pcm.size < need:
+        raise ValueError("pcm holds %d samples, need %d" % (pcm.size, need))
+    nf = n_clips * frames_per_clip
+    mf = np.empty((nf, N_MEL), dtype=np.int16) if want_mfcc else None
+    ni = np.empty((nf, N_COEFF), dtype=np.int8) if want_net_in else None
+    check(lib().edison_mfcc_q15_clips(_p(pcm), n_clips, frames_per_clip, clip_stride, _p(mf), _p(ni)), "edison_mfcc_q15_clips")
+    return mf, ni
+
+
+def kws_batch(pcm, n_clips, clip_stride=N_FRAMES * FRAME_LEN, want_softmax=True, want_net_in=False):
+    """appHifMfccAndInference over n_clips clips -> (logits [n,10], softmax [n,10] | None, net_in [n,403] | None)"""
+    pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
+    need = (n_clips - 1) * clip_stride + N_FRAMES * FRAME_LEN if n_clips else 0
+    if pcm.size < need:
+        raise ValueError("pcm holds %d samples, need %d" % (pcm.size, need))
+    lg = np.empty((n_clips, N_CLASSES), dtype=np.int8)
+    sm = np.empty((n_clips, N_CLASSES), dtype=np.int8) if want_softmax else None
+    ni = np.empty((n_clips, NET_IN), dtype=np.int8) if want_net_in else None
+    check(lib().edison_kws_batch(_p(pcm), n_clips, clip_stride, _p(lg), _p(sm), _p(ni)), "edison_kws_batch")
+    return lg, sm, ni
+
+
+def infer_q7_batch(net_in, want_softmax=True):
+    net_in = np.ascontiguousarray(net_in, dtype=np.int8).reshape(-1, NET_IN)
+    n = net_in.shape[0]
+    lg = np.empty((n, N_CLASSES), dtype=np.int8)
+    sm = np.empty((n, N_CLASSES), dtype=np.int8) if want_softmax else None
+    check(lib().edison_infer_q7_batch(_p(net_in), n, _p(lg), _p(sm)), "edison_infer_q7_batch")
+    return lg, sm

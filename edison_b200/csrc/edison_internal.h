@@ -1,0 +1,43 @@
+// edison_internal.h -- declarations shared by the translation units of libedison_b200.so
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "mfcc_q15_core.cuh"
+
+namespace edison {
+
+// ---- front-end ----------------------------------------------------------------------------------
+struct MfccLaunch {
+  const int16_t *pcm;          // device
+  long long n_clips;
+  int frames_per_clip;
+  long long clip_stride;       // samples
+  int16_t *mfcc;               // device [n_clips*frames_per_clip][32] or nullptr
+  int8_t *net_in;              // device [n_clips*frames_per_clip][13] or nullptr
+  const MfccTables *tables;    // device
+};
+// fills the twiddle / split / sqrt-exception tables (formula-generated, checksummed against the
+// values of the reference's CMSIS build) and copies the mel blob in; returns 0 or EDISON_E_*
+int build_mfcc_tables(MfccTables *host_tables, const char *mel_blob_path, char *err, size_t errlen);
+cudaError_t launch_mfcc_q15(const MfccLaunch &p, int sm_count, cudaStream_t stream);
+cudaError_t mfcc_q15_configure(void);   // opt-in to large dynamic shared memory (once)
+
+// ---- int8 net -----------------------------------------------------------------------------------
+struct NnomModel;   // device-side packed weights, defined in nnom_q7_kernel.cu
+int nnom_load(const char *blob_path, NnomModel **out_dev_model, int *in_scale, int *in_min, int *in_max,
+              char *err, size_t errlen);
+void nnom_free(NnomModel *m);
+cudaError_t nnom_configure(void);
+cudaError_t launch_nnom_q7(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits,
+                           int8_t *softmax, int softmax_mode, int sm_count, cudaStream_t stream);
+
+// ---- debug kernels --------------------------------------------------------------------------------
+cudaError_t launch_debug_sqrt(const int32_t *d_in, size_t n, int32_t *d_out, cudaStream_t stream);
+cudaError_t launch_debug_mag_sweep(uint32_t lo, uint32_t hi, const uint32_t *d_exc, unsigned long long *d_out2,
+                                   cudaStream_t stream);
+
+void count_launch(void);
+
+}  // namespace edison

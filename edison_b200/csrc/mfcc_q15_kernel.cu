@@ -1,0 +1,201 @@
+// mfcc_q15_kernel.cu -- K1: batched q15 MFCC front-end for sm_100a.
+//
+// Replaces audioCalcMFCCs (firmware/src/audioprocessing.c:116-215) + mfccToNetInput
+// (firmware/src/app.c:675-695) over a batch of frames.  One warp owns one frame at a time and
+// walks groups of 8 consecutive frames; the arithmetic lives in mfcc_q15_core.cuh.
+//
+// HBM traffic per frame: 2,048 B of PCM read once (coalesced 128 B per warp-load), 64 B of q15
+// coefficients and/or 13 B of int8 net input written.  Everything else stays in registers and
+// shared memory.  The kernel is integer-issue bound, so the grid is persistent:
+// one 16-warp CTA per SM.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "edison_internal.h"
+#include "../../include/edison_b200.h"
+
+namespace edison {
+
+constexpr int kWarpsPerCta = 16;
+constexpr int kThreads = kWarpsPerCta * 32;
+
+struct WarpSmem {
+  int xr[kXchPlane];
+  int xi[kXchPlane];
+  int spect[512];
+  int mel[kGroup * 32];
+};
+// the DCT scratch (z: 8*16 I2 = 1 KiB, out: 8*32 int = 1 KiB) aliases xr, which is idle by then
+static_assert(sizeof(I2) * kGroup * 16 + sizeof(int) * kGroup * 32 <= sizeof(int) * kXchPlane, "dct scratch");
+
+struct CtaSmem {
+  MfccTables T;
+  WarpSmem w[kWarpsPerCta];
+};
+
+__device__ __forceinline__ uint32_t ld_nc_u32(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.b32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_nc_u16(const uint16_t *p) {
+  uint16_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(v) : "l"(p));
+  return v;
+}
+
+__global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  CtaSmem &S = *reinterpret_cast<CtaSmem *>(smem_raw);
+  {  // tables: global -> shared, once per CTA
+    const int4 *src = reinterpret_cast<const int4 *>(P.tables);
+    int4 *dst = reinterpret_cast<int4 *>(&S.T);
+    for (int i = threadIdx.x; i < (int)(sizeof(MfccTables) / 16); i += kThreads) dst[i] = src[i];
+  }
+  __syncthreads();
+  const MfccTables &T = S.T;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  WarpSmem &W = S.w[warp];
+  const long long n_frames = P.n_clips * P.frames_per_clip;
+  const long long n_groups = (n_frames + kGroup - 1) / kGroup;
+  const long long warp_global = (long long)blockIdx.x * kWarpsPerCta + warp;
+  const long long warp_stride = (long long)gridDim.x * kWarpsPerCta;
+
+  for (long long grp = warp_global; grp < n_groups; grp += warp_stride) {
+    for (int g = 0; g < kGroup; g++) {
+      const long long f = grp * kGroup + g;
+      if (f >= n_frames) {  // ragged tail: the group's unused rows are never stored
+        W.mel[32 * g + lane] = 0;
+        continue;
+      }
+      const long long clip = f / P.frames_per_clip;
+      const int fic = (int)(f - clip * P.frames_per_clip);
+      const int16_t *frame = P.pcm + clip * P.clip_stride + (long long)fic * kFrameLen;
+      uint32_t w[16];
+      if ((reinterpret_cast<uintptr_t>(frame) & 3u) == 0) {
+        const uint32_t *fw = reinterpret_cast<const uint32_t *>(frame);
+#pragma unroll
+        for (int q = 0; q < 16; q++) w[q] = ld_nc_u32(fw + 32 * q + lane);
+      } else {  // odd sample offset (clip stride not a multiple of 2 samples)
+        const uint16_t *fh = reinterpret_cast<const uint16_t *>(frame);
+#pragma unroll
+        for (int q = 0; q < 16; q++)
+          w[q] = ld_nc_u16(fh + 64 * q + 2 * lane) | (ld_nc_u16(fh + 64 * q + 2 * lane + 1) << 16);
+      }
+      int peak = phase_a(lane, w, T, W.xr, W.xi);
+      peak = __reduce_max_sync(0xffffffffu, peak);   // also orders the exchange-1 stores
+      __syncwarp();
+      if (peak > kNoSatPeak) {
+        phase_b<true>(lane, T, W.xr, W.xi);
+        __syncwarp();
+        phase_c<true>(lane, T, W.xr, W.xi, W.spect);
+      } else {
+        phase_b<false>(lane, T, W.xr, W.xi);
+        __syncwarp();
+        phase_c<false>(lane, T, W.xr, W.xi, W.spect);
+      }
+      __syncwarp();
+      W.mel[32 * g + lane] = phase_mel(lane, T, W.spect);
+      __syncwarp();
+    }
+    // dct2_q15 for the 8 frames of the group, 4 lanes per frame
+    I2 *z = reinterpret_cast<I2 *>(W.xr);
+    int *out = W.xr + 2 * kGroup * 16;
+    dct_stage1(lane, T, W.mel, z);
+    __syncwarp();
+    dct_stage2(lane, z);
+    __syncwarp();
+#pragma unroll
+    for (int it = 0; it < 4; it++) dct_split(32 * it + lane, T, z, out);
+    __syncwarp();
+    const long long f0 = grp * kGroup;
+    if (P.mfcc) {  // 8 frames x 64 B, one 16-byte store per lane
+      const int fr = lane >> 2, part = lane & 3;
+      if (f0 + fr < n_frames) {
+        const int *o = out + 32 * fr + 8 * part;
+        uint4 v;
+        v.x = (uint32_t)(o[0] & 0xffff) | ((uint32_t)o[1] << 16);
+        v.y = (uint32_t)(o[2] & 0xffff) | ((uint32_t)o[3] << 16);
+        v.z = (uint32_t)(o[4] & 0xffff) | ((uint32_t)o[5] << 16);
+        v.w = (uint32_t)(o[6] & 0xffff) | ((uint32_t)o[7] << 16);
+        *reinterpret_cast<uint4 *>(P.mfcc + (f0 + fr) * 32 + 8 * part) = v;
+      }
+    }
+    if (P.net_in) {  // 8 frames x 13 int8 (mfccToNetInput)
+      for (int idx = lane; idx < kGroup * kNCoeff; idx += 32) {
+        const int fr = idx / kNCoeff, c = idx - fr * kNCoeff;
+        if (f0 + fr < n_frames) P.net_in[(f0 + fr) * kNCoeff + c] = (int8_t)net_input_q7(out[32 * fr + c], T);
+      }
+    }
+    __syncwarp();
+  }
+}
+
+cudaError_t mfcc_q15_configure(void) {
+  return cudaFuncSetAttribute(mfcc_q15_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
+}
+
+cudaError_t launch_mfcc_q15(const MfccLaunch &p, int sm_count, cudaStream_t stream) {
+  const long long n_frames = p.n_clips * p.frames_per_clip;
+  if (n_frames <= 0) return cudaSuccess;
+  const long long n_groups = (n_frames + kGroup - 1) / kGroup;
+  long long ctas = (n_groups + kWarpsPerCta - 1) / kWarpsPerCta;
+  if (ctas > sm_count) ctas = sm_count;
+  mfcc_q15_kernel<<<(unsigned)ctas, kThreads, sizeof(CtaSmem), stream>>>(p);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// ---- debug kernels (device arithmetic against itself; include/edison_b200.h section 4) ---------
+__global__ void debug_sqrt_kernel(const int32_t *in, size_t n, int32_t *out) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = sqrt_q31_newton(in[i]);
+}
+cudaError_t launch_debug_sqrt(const int32_t *d_in, size_t n, int32_t *d_out, cudaStream_t stream) {
+  if (!n) return cudaSuccess;
+  debug_sqrt_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(d_in, n, d_out);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// mag_q15 takes (re, im); the sweep feeds it through a variant that takes s directly
+__device__ __forceinline__ int mag_from_sum(unsigned s, const uint32_t *exc_bits) {
+  unsigned h = s >> 1;
+  float y = ed_fmul(ed_sqrt_approx(ed_i2f((int)h)), 0.99999618530273437500f);
+  int g = ed_f2i_rz(y);
+  int d = (int)h - g * g;
+  int t = 2 * g + 1;
+  if (d >= t) { d -= t; g += 1; }
+  int dlo = 2 * d + (int)(s & 1u);
+  if (g < 8192) {
+    if (dlo == 0) g -= (int)((exc_bits[g >> 5] >> (g & 31)) & 1u);
+    return g;
+  }
+  int dhi = 4 * g + 2 - dlo;
+  if (dlo <= 13 || dhi <= 11) return (int)(int16_t)(sqrt_q31_newton((int)s) >> 16);
+  return g;
+}
+__global__ void debug_mag_sweep_kernel(uint32_t lo, uint32_t hi, const uint32_t *exc, unsigned long long *out2) {
+  unsigned long long mism = 0, sum = 0;
+  for (unsigned long long s = (unsigned long long)lo + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; s < hi;
+       s += (unsigned long long)gridDim.x * blockDim.x) {
+    const int exact = (int)(int16_t)(sqrt_q31_newton((int)(unsigned)s) >> 16);
+    const int fast = mag_from_sum((unsigned)s, exc);
+    mism += (exact != fast);
+    sum += (unsigned long long)(unsigned)exact * ((s & 1023ull) + 1ull);
+  }
+  for (int o = 16; o; o >>= 1) {
+    mism += __shfl_xor_sync(0xffffffffu, mism, o);
+    sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  }
+  if ((threadIdx.x & 31) == 0) { atomicAdd(out2, mism); atomicAdd(out2 + 1, sum); }
+}
+cudaError_t launch_debug_mag_sweep(uint32_t lo, uint32_t hi, const uint32_t *d_exc, unsigned long long *d_out2,
+                                   cudaStream_t stream) {
+  debug_mag_sweep_kernel<<<148 * 8, 256, 0, stream>>>(lo, hi, d_exc, d_out2);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace edison

@@ -1,0 +1,134 @@
+/* edison_b200.h -- C ABI of libedison_b200.so
+ *
+ * A drop-in for the keyword-spotting hot path of huettern/edison: the firmware's
+ * own entry points keep their names and signatures (section 1), and batched entry points
+ * (section 2) expose the same arithmetic over many frames / clips at once.  Everything behind
+ * this header runs as CUDA kernels for sm_100a; there is no CPU implementation in the library
+ * and every call fails with EDISON_E_NOGPU when no device is usable.
+ *
+ * Plain C, plain pointers and sizes: bind it from C, cgo, ctypes, JNI, ....
+ * File:line references are relative to the reference tree.
+ */
+#ifndef EDISON_B200_H
+#define EDISON_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- constants of the path ------------------------------------------------------------------ */
+#define EDISON_FRAME_LEN      1024  /* AUD_MFCC_FRAME_LEN, firmware/src/audioprocessing.h:14   */
+#define EDISON_N_MEL          32    /* MEL_MTX_COLS, firmware/src/audio/mel_constants.h:10      */
+#define EDISON_N_COEFF        13    /* aiGetInputShape x, firmware/src/ai/ai.c:205-216          */
+#define EDISON_N_FRAMES       31    /* aiGetInputShape y                                        */
+#define EDISON_NET_IN         (EDISON_N_FRAMES * EDISON_N_COEFF)   /* 403                       */
+#define EDISON_N_CLASSES      10    /* firmware/src/ai/nnom/kws_nnom/keywords.txt               */
+#define EDISON_CLIP_SAMPLES   (EDISON_N_FRAMES * EDISON_FRAME_LEN) /* 31,744        */
+
+/* ---- status codes (0 = success, negative = failure; aiRunInference keeps nnom_status_t's
+ *      convention 0 == NN_SUCCESS, firmware/src/ai/nnom/inc/nnom.h) ---------------------------- */
+#define EDISON_OK             0
+#define EDISON_E_ARG         (-1)   /* null pointer, zero stride, misaligned device pointer      */
+#define EDISON_E_NOGPU       (-2)   /* no CUDA device / driver: the library has no CPU path      */
+#define EDISON_E_CUDA        (-3)   /* a CUDA call failed; see edison_last_error()               */
+#define EDISON_E_DATA        (-4)   /* model / table blob missing or malformed                   */
+#define EDISON_E_NOINIT      (-5)   /* edison_init() has not succeeded                           */
+#define EDISON_E_MODEL       (-6)   /* blob describes a graph this build has no kernels for      */
+#define EDISON_E_NOMEM       (-7)
+
+/* softmax variants of the reference builds */
+#define EDISON_SOFTMAX_CMSIS_REF   0  /* arm_softmax_q7 reference branch, arm_softmax_q7.c:217-254 */
+#define EDISON_SOFTMAX_CMSIS_SIMD  1  /* arm_softmax_q7 SIMD branch :83-215 (firmware build)       */
+#define EDISON_SOFTMAX_NNOM_LOCAL  2  /* local_softmax_q7, nnom_local.c:948-1003                   */
+
+typedef struct edison_cfg {
+  int device;             /* CUDA device ordinal; -1 = keep the current device                   */
+  const char *data_dir;   /* holds mel_q15.bin and kws_nnom_q7.bin; NULL = $EDISON_B200_DATA,
+                             else <directory of the .so>/../data                                */
+  int softmax_mode;       /* EDISON_SOFTMAX_*                                                    */
+  size_t chunk_clips;     /* host-pointer calls are pipelined in chunks of this many clips
+                             (0 = default 8192)                                                  */
+} edison_cfg;
+
+/* ---- section 0: library lifetime -------------------------------------------------------------- */
+int edison_init(const edison_cfg *cfg);          /* idempotent per process; cfg may be NULL     */
+void edison_shutdown(void);
+const char *edison_last_error(void);             /* text of the last failure in this thread     */
+int edison_set_softmax_mode(int mode);
+/* number of kernel launches issued by this library since init (bench.py's gpu_launches) */
+unsigned long long edison_launch_count(void);
+/* pinned host memory for callers that want copies to overlap compute */
+void *edison_host_alloc(size_t bytes);
+void edison_host_free(void *p);
+
+/* ---- section 1: the firmware's entry points (batch-of-one wrappers) -------------------------- */
+/* firmware/src/audioprocessing.h:21-22.  *oup points at a library-owned buffer of 32 q15 values
+ * that stays valid until the next call (audioprocessing.c:80, 210).  Not re-entrant, like the
+ * original; calls are serialised on one internal lock. */
+void audioInit(void);
+void audioCalcMFCCs(int16_t *inp, int16_t **oup);
+
+/* firmware/src/ai/ai.h:74-80 */
+int aiInitialize(void);
+void aiGetInputShape(uint16_t *x, uint16_t *y);
+int aiRunInference(void *in_data, void *out_data);   /* in: int8[403], out: int8[10] softmax    */
+const char *aiGetKeywordFromIndex(uint32_t idx);
+uint32_t aiGetKeywordCount(void);
+
+/* firmware/src/ai/ai_nnom.h:4-9 */
+void aiNnomInit(void);
+int aiNnomRunInference(void *in_data, void *out_data);
+int8_t *aiNnomGetInputBuffer(void);
+int8_t *aiNnomGetOutputBuffer(void);
+
+/* firmware/src/app.c:152-153, 675-719 (static there; exported here because the streaming glue
+ * of a host application needs them).  They operate on the library-owned 31x13 window that
+ * edison_net_input_window() returns. */
+void mfccToNetInput(int16_t *mfcc, uint16_t in_x, uint16_t in_y, uint32_t xoffset);
+void mfccToNetInputPush(int16_t *mfcc, uint16_t in_x, uint16_t in_y);
+int8_t *edison_net_input_window(void);
+
+/* ---- section 2: batched entry points (host OR device pointers, detected per call) ------------ */
+/* audioCalcMFCCs over n_frames consecutive 1024-sample frames: mfcc[n_frames][32] q15. */
+int edison_mfcc_q15_batch(const int16_t *pcm, size_t n_frames, int16_t *mfcc);
+
+/* appHifMfccAndInference (firmware/src/app.c:167-221) over n_clips clips.  Clip c starts at
+ * pcm + c * clip_stride_samples and supplies 31 frames.  Any of the outputs may be NULL:
+ * logits[n][10] (Dense output, Q5.2), softmax[n][10] (Q0.7), net_in[n][403]. */
+int edison_kws_batch(const int16_t *pcm, size_t n_clips, size_t clip_stride_samples,
+                     int8_t *logits, int8_t *softmax, int8_t *net_in);
+
+/* aiRunInference over n precomputed net inputs: net_in[n][403] -> logits[n][10], softmax[n][10] */
+int edison_infer_q7_batch(const int8_t *net_in, size_t n, int8_t *logits, int8_t *softmax);
+
+/* Generalised front-end: frames_per_clip frames from each of n_clips clips; writes
+ * mfcc[n_clips*frames_per_clip][32] and/or net_in[n_clips*frames_per_clip][13] (either NULL). */
+int edison_mfcc_q15_clips(const int16_t *pcm, size_t n_clips, size_t frames_per_clip,
+                          size_t clip_stride_samples, int16_t *mfcc, int8_t *net_in);
+
+/* ---- section 3: device-resident variants (all pointers are device pointers; stream is a
+ *      cudaStream_t passed as void*, NULL = the library's stream; asynchronous) --------------- */
+int edison_mfcc_q15_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip,
+                              size_t clip_stride_samples, int16_t *d_mfcc, int8_t *d_net_in,
+                              void *stream);
+int edison_infer_q7_batch_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax,
+                              void *stream);
+int edison_kws_batch_dev(const int16_t *d_pcm, size_t n_clips, size_t clip_stride_samples,
+                         int8_t *d_logits, int8_t *d_softmax, int8_t *d_net_in, void *stream);
+int edison_sync(void *stream);
+
+/* ---- section 4: self-checks used by the tests (device arithmetic against itself) ------------- */
+/* arm_sqrt_q31 (arm_sqrt_q31.c:50-135) evaluated on the device for n host values */
+int edison_debug_sqrt_q31(const int32_t *in, size_t n, int32_t *out);
+/* exhaustive check over s in [lo, hi): counts where the fast magnitude path disagrees with the
+ * exact Newton path on the device, and a 64-bit checksum of the exact results */
+int edison_debug_mag_sweep(uint32_t lo, uint32_t hi, unsigned long long *mismatches,
+                           unsigned long long *checksum);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EDISON_B200_H */
