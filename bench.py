@@ -1,0 +1,272 @@
+#!/usr/bin/env python3
+"""bench.py -- KWS hot path throughput on B200 (contract: see DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step = one pass of the hot path (q15 MFCC front-end K1 + int8 NNoM net K2) over this rank's shard
+of synthetic clips: BASELINE.json config #3 (2^20 clips over 8 GPUs) = 131,072 clips x 31 frames of
+1024 int16 samples per GPU (8.3 GB, far larger than L2), weak scaling.  `value` times the kernels
+with the PCM resident in HBM; `e2e` times edison_kws_batch() -- the C-ABI call a user makes -- on
+pinned HOST buffers, copies included.  The same line carries MFCC-only frames/s on config #2
+(65,536 one-second clips, 15 frames each), the roofline of the dominant kernel and the CPU
+reference timed on this box's cores.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CLIPS_PER_GPU = 131072          # config #3: 2^20 clips / 8 GPUs
+CFG2_CLIPS, CFG2_FPC, CFG2_STRIDE = 65536, 15, 16000
+E2E_CLIPS = 32768               # host-buffer leg: 2.08 GB of pinned PCM per step
+CLIP = 31 * 1024
+K1_BYTES_PER_FRAME = 2048 + 13  # algorithmic: PCM read + int8 net-input row written
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return json.load(fh)["hbm_gbs"], "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons while the timed region runs"""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        self.join(timeout=6)
+        mhz = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        mx = max((int(r[1]) for r in self.rows if r[1].isdigit()), default=None)
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(mhz)}
+
+
+def synth_clips_gpu(torch, n_clips, stride, seed, dev):
+    """int16 [n_clips * stride] on the device: speech-like sinusoids + noise (D1), every 8th clip full-scale
+    uniform (D2, takes the saturating path), every 16th low level (D3).  Deterministic per seed."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    out = torch.empty(n_clips * stride, dtype=torch.int16, device=dev)
+    view = out.view(n_clips, stride)
+    t = torch.arange(stride, device=dev, dtype=torch.float32)
+    step = 4096
+    for c0 in range(0, n_clips, step):
+        nc = min(step, n_clips - c0)
+        x = torch.randn(nc, stride, generator=g, device=dev) * 200.0
+        for _ in range(4):
+            amp = torch.rand(nc, 1, generator=g, device=dev) * 7500 + 500
+            f = torch.rand(nc, 1, generator=g, device=dev) * 3900 + 100
+            ph = torch.rand(nc, 1, generator=g, device=dev) * 6.28
+            x += amp * torch.sin(2 * 3.14159265 * f / 16000.0 * t + ph)
+        idx = torch.arange(c0, c0 + nc, device=dev)
+        full = (idx % 8 == 3).view(-1, 1)
+        low = (idx % 16 == 5).view(-1, 1)
+        u = torch.rand(nc, stride, generator=g, device=dev)
+        x = torch.where(full, u * 65535.0 - 32768.0, x)
+        x = torch.where(low, u * 128.0 - 64.0, x)
+        view[c0:c0 + nc] = x.round().clamp(-32768, 32767).to(torch.int16)
+        del x, u
+    return out
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU implementation on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import cpu_baseline
+    cores = os.cpu_count() or 1
+    per = 64
+    res = cpu_baseline.run(clips_per_proc=per, procs=cores, mfcc_only=False, reps=args.warmup + args.steps)
+    steps = res["step_s"][args.warmup:]
+    ms = 1e3 * sum(steps) / len(steps)
+    val = res["clips"] / (ms / 1e3)
+    line = {"impl": "reference", "metric": "kws_clips_per_s", "value": val, "unit": "clips/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "q15/int8", "data": "synthetic",
+            "config": {"workload": "config#3 shard: clips x 31 frames x 1024 int16, q15 MFCC + int8 NNoM net",
+                       "sample": res["sample"]},
+            "cpu_baseline": {"value": val, "unit": "clips/s", "cores": cores, "kind": res["kind"], "sample": res["sample"]},
+            "e2e": {"value": val, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "mfcc_frames_per_s": val * 31, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import edison_b200 as ed
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    ed.init(device=local_rank)
+    L = ed.lib()
+    chk = ed.capi.check
+    st = torch.cuda.current_stream()
+    sp = ctypes.c_void_p(st.cuda_stream)
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+
+    n = CLIPS_PER_GPU
+    pcm = synth_clips_gpu(torch, n, CLIP, 20 + rank, dev)
+    net_in = torch.empty(n * 403, dtype=torch.int8, device=dev)
+    logits = torch.empty(n, 10, dtype=torch.int8, device=dev)
+    softmax = torch.empty(n, 10, dtype=torch.int8, device=dev)
+    gathered = torch.empty(world * n, 10, dtype=torch.int8, device=dev) if world > 1 else None
+    counts = torch.zeros(10, dtype=torch.int64, device=dev)
+
+    def step(ev=None):
+        if ev: ev[0].record(st)
+        chk(L.edison_mfcc_q15_clips_dev(P(pcm), n, 31, CLIP, None, P(net_in), sp))
+        if ev: ev[1].record(st)
+        chk(L.edison_infer_q7_batch_dev(P(net_in), n, P(logits), P(softmax), sp))
+        if ev: ev[2].record(st)
+        if world > 1:  # the path's only exchange: final gather of logits + class counts
+            dist.all_gather_into_tensor(gathered, logits)
+            c = torch.bincount(logits.argmax(dim=1), minlength=10)
+            dist.all_reduce(c)
+            counts.copy_(c)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    l0 = ed.launch_count()
+    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_begin.record(st)
+    for k in range(args.steps):
+        step(evs[k])
+    t_end.record(st)
+    barrier()
+    launches = ed.launch_count() - l0
+    total_ms = t_begin.elapsed_time(t_end)
+    k1_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
+    k2_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
+    clocks = sampler.summary()
+    if world > 1:
+        t = torch.tensor([total_ms, k1_ms, k2_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, k1_ms, k2_ms = t.tolist()
+    ms_per_step = total_ms / args.steps
+    value = world * n / (ms_per_step / 1e3)
+
+    # ---- MFCC-only on config #2 (65,536 one-second clips -> 15 frames each), device resident
+    pcm2 = pcm[: CFG2_CLIPS * CFG2_STRIDE]
+    mf2 = torch.empty(CFG2_CLIPS * CFG2_FPC, 32, dtype=torch.int16, device=dev)
+    for _ in range(max(args.warmup, 3)):
+        chk(L.edison_mfcc_q15_clips_dev(P(pcm2), CFG2_CLIPS, CFG2_FPC, CFG2_STRIDE, P(mf2), None, sp))
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    a.record(st)
+    for _ in range(args.steps):
+        chk(L.edison_mfcc_q15_clips_dev(P(pcm2), CFG2_CLIPS, CFG2_FPC, CFG2_STRIDE, P(mf2), None, sp))
+    b.record(st)
+    torch.cuda.synchronize()
+    cfg2_ms = a.elapsed_time(b) / args.steps
+    cfg2_fps = CFG2_CLIPS * CFG2_FPC / (cfg2_ms / 1e3)
+
+    # ---- e2e: edison_kws_batch() on pinned HOST buffers, H2D + D2H inside the timed region
+    ne = E2E_CLIPS
+    h_pcm = torch.empty(ne * CLIP, dtype=torch.int16).pin_memory()
+    h_pcm.copy_(pcm[: ne * CLIP])
+    h_logits = torch.empty(ne, 10, dtype=torch.int8).pin_memory()
+    h_softmax = torch.empty(ne, 10, dtype=torch.int8).pin_memory()
+    for _ in range(2):
+        chk(L.edison_kws_batch(P(h_pcm), ne, CLIP, P(h_logits), P(h_softmax), None))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        chk(L.edison_kws_batch(P(h_pcm), ne, CLIP, P(h_logits), P(h_softmax), None))
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = t.item()
+    e2e_val = world * ne / e2e_s
+    same = bool((h_logits.to(dev) == logits[:ne]).all().item())
+
+    if rank == 0:
+        peak, peak_kind = peaks()
+        k1_bytes = n * 31 * K1_BYTES_PER_FRAME
+        achieved = k1_bytes / (k1_ms / 1e3) / 1e9
+        line = {"metric": "kws_clips_per_s", "value": value, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "q15/int8", "data": "synthetic",
+                "config": {"workload": "config#3 shard: %d clips x 31 frames x 1024 int16 per GPU, q15 MFCC + int8 NNoM net" % n,
+                           "clip_samples": CLIP, "global_clips": world * n, "l2": "inputs (8.3 GB/GPU) larger than L2",
+                           "parallelism": "clip shards, dp%d" % world, "peak": peak_kind},
+                "mfcc_frames_per_s": world * n * 31 / (k1_ms / 1e3), "audio_seconds_per_s": value * 31 * 0.064,
+                "k1_ms": k1_ms, "k2_ms": k2_ms,
+                "cfg2_mfcc": {"workload": "config#2: 65,536 x 1 s clips (15 frames each), q15 MFCC only, 1 GPU",
+                              "frames_per_s": cfg2_fps, "clips_per_s": CFG2_CLIPS / (cfg2_ms / 1e3), "ms": cfg2_ms},
+                "roofline": {"kernel": "mfcc_q15_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                             "frac": achieved / peak, "traffic": None, "bytes_per_launch": k1_bytes},
+                "e2e": {"value": e2e_val, "unit": "clips/s", "h2d_bytes_per_step": ne * CLIP * 2, "d2h_bytes_per_step": ne * 20,
+                        "clips_per_step": ne, "matches_device_path": same},
+                "gpu_launches": int(launches), "clocks": clocks}
+        if world == 1 and not args.no_cpu:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import cpu_baseline
+            res = cpu_baseline.run(clips_per_proc=64, procs=os.cpu_count() or 1, reps=1)
+            line["cpu_baseline"] = {"value": res["clips_per_s"], "unit": "clips/s", "cores": res["cores"], "kind": res["kind"],
+                                    "sample": res["sample"]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
