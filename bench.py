@@ -131,7 +131,8 @@ def run_ours(args, rank, world, local_rank):
     ed.init(device=local_rank)
     L = ed.lib()
     chk = ed.capi.check
-    st = torch.cuda.current_stream()
+    st = torch.cuda.Stream(device=dev)   # a real (non-NULL) stream: the library launches on the handle it is given
+    torch.cuda.set_stream(st)
     sp = ctypes.c_void_p(st.cuda_stream)
     P = lambda t: ctypes.c_void_p(t.data_ptr())
 

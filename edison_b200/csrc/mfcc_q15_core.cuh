@@ -11,7 +11,11 @@
 //   phase C  lane owns b4..b0 of 8 butterflies  p = 32 L + 4 i + {0..3}      stage 5 (only the
 //            two outputs per butterfly that land in bins 0..511), magnitude
 //
-// with two exchanges through shared memory (int32 planes re[], im[], padded 4 words per 64).
+// with two exchanges through shared memory (int32 planes re[], im[]).  Phases A and B run as a
+// two-trip loop over the parity e = b0 (16 points = one closed radix-4 x radix-4 block per trip),
+// phase C as a loop over its 8 butterflies: the loops are NOT unrolled, which keeps the kernel's
+// hot code inside the instruction cache (a fully unrolled version was 126 KB of SASS and spent
+// most of its time waiting for instruction fetch; profiles/r01).
 // Bit reversal (arm_bitreversal_16) is folded into phase C's addressing: position p holds bin
 // rev10(p).  Then mel (32 sparse dot products), and, batched over the 8 frames of a group,
 // dct2_q15 (audioprocessing.c:324-436) with 4 lanes per frame.
@@ -30,18 +34,20 @@ constexpr int kNCoeff = 13;       // aiGetInputShape, firmware/src/ai/ai.c:205-2
 constexpr int kGroup = 8;         // frames per warp iteration (DCT batch)
 constexpr int kMelMaxW = 1024;    // capacity for melMtxCompact (915 in the reference header)
 
-// exchange buffer: two planes of 1024 int32 padded by 4 words every 64
-constexpr int kXchPlane = 1024 + 4 * 16;
-ED_HD int xaddr(int p) { return p + ((p >> 6) << 2); }
+// exchange buffer: two planes (re, im) of 1024 int32.  Position p = 64 q + 2 l + e is stored at
+//   e * 544 + 34 q + l          (q = p >> 6, l = (p >> 1) & 31, e = p & 1)
+// so that every access pattern of the three phases is free of bank conflicts.
+constexpr int kXchHalf = 16 * 34;
+constexpr int kXchPlane = 2 * kXchHalf;
 
 // ---- constant tables, one copy per CTA in shared memory -----------------------------------------
 struct MfccTables {
-  I2 tw1[3][256];   // stage 1: [0] W^j  [1] W^2j  [2] W^3j          (co, si) of twiddleCoef_1024_q15
-  I2 tw2[3][64];    // stage 2: W^(4 j (k+1))
-  I2 tw3[3][16];    // stage 3: W^(16 j (k+1))
-  I2 tw4[3][4];     // stage 4: W^(64 j (k+1))
-  I2 tw16[12];      // twiddleCoef_16_q15 (DCT's 16-point CFFT)
-  I2 realA[16];     // realCoefAQ15 at stride 512 (arm_rfft_init_q15.c:213-222, fftLenReal 32)
+  I2 tw1[3][2][4][32];  // stage 1: [k][e][qp][lane] = W^((k+1) j), j = 64 qp + 2 lane + e   (co, si)
+  I2 tw2[3][2][32];     // stage 2: [k][e][lane]     = W^(4 (k+1) j), j = 2 lane + e
+  I2 tw3[3][16];        // stage 3: W^(16 (k+1) j)
+  I2 tw4[3][4];         // stage 4: W^(64 (k+1) j)
+  I2 tw16[12];          // twiddleCoef_16_q15 (DCT's 16-point CFFT)
+  I2 realA[16];         // realCoefAQ15 at stride 512 (arm_rfft_init_q15.c:213-222, fftLenReal 32)
   I2 realB[16];
   uint32_t sqrt_exc[kSqrtExcWords];
   int16_t mel_w[kMelMaxW];      // melMtxCompact   (firmware/src/audio/mel_constants.h:2586)
@@ -52,82 +58,32 @@ struct MfccTables {
   int pad_;
 };
 
-// ---- phase A: load, stages 1 and 2 ---------------------------------------------------------------
-// w[q] = the 32-bit word holding samples 64q+2L (low half) and 64q+2L+1 (high half).
-// Returns max(|min|, |max|) proxy: (max sample, min sample) folded into one "peak" value.
-ED_HD int phase_a(int lane, const uint32_t w[16], const MfccTables &T, int *xr, int *xi) {
-  int re[32], im[32];
-  int mx = -32768, mn = 32767;
+// sample e (0 = low half, 1 = high half) of a packed pair, sign extended
+ED_HD int unpack_half(uint32_t w, int e) {
 #if defined(__CUDA_ARCH__)
-#pragma unroll
+  int r;  // PRMT, generic mode: selector nibble 8|n replicates the sign of byte n (__byte_perm masks that bit)
+  asm("prmt.b32 %0, %1, 0, %2;" : "=r"(r) : "r"(w), "r"(e ? 0xBB32u : 0x9910u));
+  return r;
+#else
+  return e ? (int)w >> 16 : (int)(int16_t)(w & 0xffffu);
 #endif
-  for (int q = 0; q < 16; q++) {
-    int lo = (int)(int16_t)(w[q] & 0xffffu), hi = (int)w[q] >> 16;
-    re[2 * q] = lo; re[2 * q + 1] = hi;
-    mx = imax(mx, imax(lo, hi));
-    mn = imin(mn, imin(lo, hi));
-  }
-  // stage 1 (first-stage formulas, imaginary input zero): butterflies j = 64 qp + 2L + e
+}
+
+// peak of the 32 samples a lane holds: >= |x| - 1 for every sample
+ED_HD int lane_peak(const uint32_t w[16]) {
 #if defined(__CUDA_ARCH__)
+  uint32_t mx = w[0], mn = w[0];
 #pragma unroll
+  for (int q = 1; q < 16; q++) { mx = __vmaxs2(mx, w[q]); mn = __vmins2(mn, w[q]); }
+  const int hi = max((int)mx >> 16, (int)(int16_t)(mx & 0xffffu));
+  const int lo = min((int)mn >> 16, (int)(int16_t)(mn & 0xffffu));
+  return max(hi, -lo - 1);
+#else
+  int hi = -32768, lo = 32767;
+  for (int q = 0; q < 16; q++)
+    for (int e = 0; e < 2; e++) { int v = unpack_half(w[q], e); hi = imax(hi, v); lo = imin(lo, v); }
+  return imax(hi, -lo - 1);
 #endif
-  for (int qp = 0; qp < 4; qp++) {
-    const I4 w1 = *reinterpret_cast<const I4 *>(&T.tw1[0][64 * qp + 2 * lane]);
-    const I4 w2 = *reinterpret_cast<const I4 *>(&T.tw1[1][64 * qp + 2 * lane]);
-    const I4 w3 = *reinterpret_cast<const I4 *>(&T.tw1[2][64 * qp + 2 * lane]);
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-    for (int e = 0; e < 2; e++) {
-      const int c1 = e ? w1.z : w1.x, s1 = e ? w1.w : w1.y;
-      const int c2 = e ? w2.z : w2.x, s2 = e ? w2.w : w2.y;
-      const int c3 = e ? w3.z : w3.x, s3 = e ? w3.w : w3.y;
-      const int a = re[2 * qp + e] >> 2, b = re[2 * (qp + 4) + e] >> 2;
-      const int c = re[2 * (qp + 8) + e] >> 2, d = re[2 * (qp + 12) + e] >> 2;
-      const int R = a + c, S = a - c, Tt = b + d, U = b - d;
-      re[2 * qp + e] = (R + Tt) >> 1;
-      im[2 * qp + e] = 0;
-      const int r2 = R - Tt;
-      re[2 * (qp + 4) + e] = (c2 * r2) >> 16;
-      im[2 * (qp + 4) + e] = (-s2 * r2) >> 16;
-      re[2 * (qp + 8) + e] = (c1 * S - s1 * U) >> 16;       // Sa = (S, -U)
-      im[2 * (qp + 8) + e] = (-c1 * U - s1 * S) >> 16;
-      re[2 * (qp + 12) + e] = (c3 * S + s3 * U) >> 16;      // Ra = (S, U)
-      im[2 * (qp + 12) + e] = (c3 * U - s3 * S) >> 16;
-    }
-  }
-  // stage 2 (middle-stage formulas; operands are bounded by 16384 so no saturation, DESIGN.md)
-  {
-    const I4 w1 = *reinterpret_cast<const I4 *>(&T.tw2[0][2 * lane]);
-    const I4 w2 = *reinterpret_cast<const I4 *>(&T.tw2[1][2 * lane]);
-    const I4 w3 = *reinterpret_cast<const I4 *>(&T.tw2[2][2 * lane]);
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-    for (int g = 0; g < 4; g++) {
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-      for (int e = 0; e < 2; e++) {
-        const I2 t1 = e ? I2{w1.z, w1.w} : I2{w1.x, w1.y};
-        const I2 t2 = e ? I2{w2.z, w2.w} : I2{w2.x, w2.y};
-        const I2 t3 = e ? I2{w3.z, w3.w} : I2{w3.x, w3.y};
-        const int q0 = 2 * (4 * g) + e;
-        bfly_mid<false>(re[q0], im[q0], re[q0 + 2], im[q0 + 2], re[q0 + 4], im[q0 + 4], re[q0 + 6], im[q0 + 6],
-                        t1, t2, t3);
-      }
-    }
-  }
-  // exchange 1: position p = 64 q + 2 L + e
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-  for (int q = 0; q < 16; q++) {
-    const int a = xaddr(64 * q + 2 * lane);
-    *reinterpret_cast<I2 *>(xr + a) = I2{re[2 * q], re[2 * q + 1]};
-    *reinterpret_cast<I2 *>(xi + a) = I2{im[2 * q], im[2 * q + 1]};
-  }
-  return imax(mx, -mn - 1);  // >= |x| - 1 for every sample; compared against kNoSatPeak
 }
 
 // A frame whose peak is at most kNoSatPeak cannot saturate any QADD16/QSUB16 of stages 3..5:
@@ -135,70 +91,91 @@ ED_HD int phase_a(int lane, const uint32_t w[16], const MfccTables &T, int *xr, 
 // two components stay below 32767.
 constexpr int kNoSatPeak = 32000;
 
-// ---- phase B: stages 3 and 4 ---------------------------------------------------------------------
+// ---- phase A: stages 1 and 2 for the 16 points p = 64 q + 2 lane + e of one parity e ------------
+// w[q] = the 32-bit word holding samples 64q+2L (low half) and 64q+2L+1 (high half).
+ED_HD void phase_a(int lane, int e, const uint32_t w[16], const MfccTables &T, int *xr, int *xi) {
+  int re[16], im[16];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int q = 0; q < 16; q++) re[q] = unpack_half(w[q], e) >> 2;  // first stage: inputs >> 2 (:200-212)
+  // stage 1 (first-stage formulas, imaginary input zero): butterflies j = 64 qp + 2L + e
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int qp = 0; qp < 4; qp++) {
+    const I2 w1 = T.tw1[0][e][qp][lane], w2 = T.tw1[1][e][qp][lane], w3 = T.tw1[2][e][qp][lane];
+    const int a = re[qp], b = re[qp + 4], c = re[qp + 8], d = re[qp + 12];
+    const int R = a + c, S = a - c, Tt = b + d, U = b - d;
+    re[qp] = (R + Tt) >> 1;
+    im[qp] = 0;
+    const int r2 = R - Tt;
+    re[qp + 4] = (w2.x * r2) >> 16;
+    im[qp + 4] = (-w2.y * r2) >> 16;
+    re[qp + 8] = (w1.x * S - w1.y * U) >> 16;    // Sa = (S, -U)
+    im[qp + 8] = (-w1.x * U - w1.y * S) >> 16;
+    re[qp + 12] = (w3.x * S + w3.y * U) >> 16;   // Ra = (S, U)
+    im[qp + 12] = (w3.x * U - w3.y * S) >> 16;
+  }
+  // stage 2 (middle-stage formulas; operands are bounded by 16384 so no saturation, DESIGN.md)
+  {
+    const I2 w1 = T.tw2[0][e][lane], w2 = T.tw2[1][e][lane], w3 = T.tw2[2][e][lane];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int g = 0; g < 4; g++)
+      bfly_mid<false>(re[4 * g], im[4 * g], re[4 * g + 1], im[4 * g + 1], re[4 * g + 2], im[4 * g + 2], re[4 * g + 3],
+                      im[4 * g + 3], w1, w2, w3);
+  }
+  // exchange 1
+  const int base = e * kXchHalf + lane;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int q = 0; q < 16; q++) {
+    xr[base + 34 * q] = re[q];
+    xi[base + 34 * q] = im[q];
+  }
+}
+
+// ---- phase B: stages 3 and 4 for the 16 points p = 64 (L>>1) + 4 t + 2 (L&1) + e ----------------
 template <bool SAT>
-ED_HD void phase_b(int lane, const MfccTables &T, int *xr, int *xi) {
-  int re[32], im[32];  // index 2 t + e, t = bits 5..2 of p
-  const int base = xaddr(64 * (lane >> 1) + 2 * (lane & 1));
+ED_HD void phase_b(int lane, int e, const MfccTables &T, int *xr, int *xi) {
+  int re[16], im[16];  // index t = bits 5..2 of p
+  const int base = e * kXchHalf + 34 * (lane >> 1) + (lane & 1);
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
   for (int t = 0; t < 16; t++) {
-    const I2 a = *reinterpret_cast<const I2 *>(xr + base + 4 * t);
-    const I2 b = *reinterpret_cast<const I2 *>(xi + base + 4 * t);
-    re[2 * t] = a.x; re[2 * t + 1] = a.y;
-    im[2 * t] = b.x; im[2 * t + 1] = b.y;
+    re[t] = xr[base + 2 * t];
+    im[t] = xi[base + 2 * t];
   }
   // stage 3: n2 = 16, twiddle index j3 = p & 15 = 4 tl + 2 (L&1) + e
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
   for (int tl = 0; tl < 4; tl++) {
-    const int j = 4 * tl + 2 * (lane & 1);
-    const I4 w1 = *reinterpret_cast<const I4 *>(&T.tw3[0][j]);
-    const I4 w2 = *reinterpret_cast<const I4 *>(&T.tw3[1][j]);
-    const I4 w3 = *reinterpret_cast<const I4 *>(&T.tw3[2][j]);
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-    for (int e = 0; e < 2; e++) {
-      const I2 t1 = e ? I2{w1.z, w1.w} : I2{w1.x, w1.y};
-      const I2 t2 = e ? I2{w2.z, w2.w} : I2{w2.x, w2.y};
-      const I2 t3 = e ? I2{w3.z, w3.w} : I2{w3.x, w3.y};
-      const int i0 = 2 * tl + e;  // th = 0; th adds 8 to the local index
-      bfly_mid<SAT>(re[i0], im[i0], re[i0 + 8], im[i0 + 8], re[i0 + 16], im[i0 + 16], re[i0 + 24], im[i0 + 24],
-                    t1, t2, t3);
-    }
+    const int j = 4 * tl + 2 * (lane & 1) + e;
+    bfly_mid<SAT>(re[tl], im[tl], re[tl + 4], im[tl + 4], re[tl + 8], im[tl + 8], re[tl + 12], im[tl + 12],
+                  T.tw3[0][j], T.tw3[1][j], T.tw3[2][j]);
   }
   // stage 4: n2 = 4, twiddle index j4 = p & 3 = 2 (L&1) + e
   {
-    const int j = 2 * (lane & 1);
-    const I4 w1 = *reinterpret_cast<const I4 *>(&T.tw4[0][j]);
-    const I4 w2 = *reinterpret_cast<const I4 *>(&T.tw4[1][j]);
-    const I4 w3 = *reinterpret_cast<const I4 *>(&T.tw4[2][j]);
+    const int j = 2 * (lane & 1) + e;
+    const I2 w1 = T.tw4[0][j], w2 = T.tw4[1][j], w3 = T.tw4[2][j];
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-    for (int th = 0; th < 4; th++) {
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-      for (int e = 0; e < 2; e++) {
-        const I2 t1 = e ? I2{w1.z, w1.w} : I2{w1.x, w1.y};
-        const I2 t2 = e ? I2{w2.z, w2.w} : I2{w2.x, w2.y};
-        const I2 t3 = e ? I2{w3.z, w3.w} : I2{w3.x, w3.y};
-        const int i0 = 8 * th + e;  // tl adds 2 to the local index
-        bfly_mid<SAT>(re[i0], im[i0], re[i0 + 2], im[i0 + 2], re[i0 + 4], im[i0 + 4], re[i0 + 6], im[i0 + 6],
-                      t1, t2, t3);
-      }
-    }
+    for (int th = 0; th < 4; th++)
+      bfly_mid<SAT>(re[4 * th], im[4 * th], re[4 * th + 1], im[4 * th + 1], re[4 * th + 2], im[4 * th + 2],
+                    re[4 * th + 3], im[4 * th + 3], w1, w2, w3);
   }
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
   for (int t = 0; t < 16; t++) {
-    *reinterpret_cast<I2 *>(xr + base + 4 * t) = I2{re[2 * t], re[2 * t + 1]};
-    *reinterpret_cast<I2 *>(xi + base + 4 * t) = I2{im[2 * t], im[2 * t + 1]};
+    xr[base + 2 * t] = re[t];
+    xi[base + 2 * t] = im[t];
   }
 }
 
@@ -212,23 +189,18 @@ ED_HD int rev5(int i) {
 // r = rev8(j) = 32 rev3(i) + rev5(L) and r + 256.  Outputs 4j+1, 4j+3 are bins >= 512, which
 // nothing reads (the mel filters end at bin 486; audioprocessing.c:157-170).
 template <bool SAT>
-ED_HD void phase_c(int lane, const MfccTables &T, const int *xr, const int *xi, int *spect) {
-  const int rl = rev5(lane);
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-  for (int i = 0; i < 8; i++) {
-    const int a = xaddr(32 * lane + 4 * i);
-    const I4 vr = *reinterpret_cast<const I4 *>(xr + a);
-    const I4 vi = *reinterpret_cast<const I4 *>(xi + a);
-    const int Rr = qadd16<SAT>(vr.x, vr.z), Ri = qadd16<SAT>(vi.x, vi.z);
-    const int Sr = qsub16<SAT>(vr.x, vr.z), Si = qsub16<SAT>(vi.x, vi.z);
-    const int Tr = qadd16<SAT>(vr.y, vr.w), Ti = qadd16<SAT>(vi.y, vi.w);
-    const int Ur = qsub16<SAT>(vr.y, vr.w), Ui = qsub16<SAT>(vi.y, vi.w);
-    const int r = 32 * rev3(i) + rl;
-    spect[r] = mag_q15((Rr + Tr) >> 1, (Ri + Ti) >> 1, T.sqrt_exc);
-    spect[r + 256] = mag_q15((Sr + Ui) >> 1, (Si - Ur) >> 1, T.sqrt_exc);
-  }
+ED_HD void phase_c(int lane, int i, const MfccTables &T, const int *xr, const int *xi, int *spect) {
+  // positions 4j+k, k = 0..3: (k = 0, 2) are adjacent words of the even half, (1, 3) of the odd half
+  const int a = 34 * (lane >> 1) + 16 * (lane & 1) + 2 * i;
+  const I2 ac_r = *reinterpret_cast<const I2 *>(xr + a), bd_r = *reinterpret_cast<const I2 *>(xr + kXchHalf + a);
+  const I2 ac_i = *reinterpret_cast<const I2 *>(xi + a), bd_i = *reinterpret_cast<const I2 *>(xi + kXchHalf + a);
+  const int Rr = qadd16<SAT>(ac_r.x, ac_r.y), Ri = qadd16<SAT>(ac_i.x, ac_i.y);
+  const int Sr = qsub16<SAT>(ac_r.x, ac_r.y), Si = qsub16<SAT>(ac_i.x, ac_i.y);
+  const int Tr = qadd16<SAT>(bd_r.x, bd_r.y), Ti = qadd16<SAT>(bd_i.x, bd_i.y);
+  const int Ur = qsub16<SAT>(bd_r.x, bd_r.y), Ui = qsub16<SAT>(bd_i.x, bd_i.y);
+  const int r = 32 * rev3(i) + rev5(lane);
+  spect[r] = mag_q15((Rr + Tr) >> 1, (Ri + Ti) >> 1, T.sqrt_exc);
+  spect[r + 256] = mag_q15((Sr + Ui) >> 1, (Si - Ur) >> 1, T.sqrt_exc);
 }
 
 // ---- mel: lane m owns filter m (audioprocessing.c:157-170) ---------------------------------------

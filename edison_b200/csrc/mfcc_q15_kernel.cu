@@ -83,17 +83,22 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
         for (int q = 0; q < 16; q++)
           w[q] = ld_nc_u16(fh + 64 * q + 2 * lane) | (ld_nc_u16(fh + 64 * q + 2 * lane + 1) << 16);
       }
-      int peak = phase_a(lane, w, T, W.xr, W.xi);
-      peak = __reduce_max_sync(0xffffffffu, peak);   // also orders the exchange-1 stores
+      const bool sat = __reduce_max_sync(0xffffffffu, lane_peak(w)) > kNoSatPeak;
+#pragma unroll 1
+      for (int e = 0; e < 2; e++) phase_a(lane, e, w, T, W.xr, W.xi);
       __syncwarp();
-      if (peak > kNoSatPeak) {
-        phase_b<true>(lane, T, W.xr, W.xi);
+      if (sat) {
+#pragma unroll 1
+        for (int e = 0; e < 2; e++) phase_b<true>(lane, e, T, W.xr, W.xi);
         __syncwarp();
-        phase_c<true>(lane, T, W.xr, W.xi, W.spect);
+#pragma unroll 1
+        for (int i = 0; i < 8; i++) phase_c<true>(lane, i, T, W.xr, W.xi, W.spect);
       } else {
-        phase_b<false>(lane, T, W.xr, W.xi);
+#pragma unroll 1
+        for (int e = 0; e < 2; e++) phase_b<false>(lane, e, T, W.xr, W.xi);
         __syncwarp();
-        phase_c<false>(lane, T, W.xr, W.xi, W.spect);
+#pragma unroll 1
+        for (int i = 0; i < 8; i++) phase_c<false>(lane, i, T, W.xr, W.xi, W.spect);
       }
       __syncwarp();
       W.mel[32 * g + lane] = phase_mel(lane, T, W.spect);

@@ -116,9 +116,16 @@ ED_HD int ed_clz(int v) { return v ? __builtin_clz((unsigned)v) : 32; }
 ED_HD float ed_sqrt_approx(float v) { return sqrtf(v); }
 #endif
 
+#if defined(__CUDACC__)
+#define ED_HD_NOINLINE static __host__ __device__ __noinline__
+#else
+#define ED_HD_NOINLINE inline
+#endif
+
 ED_HD int mul_q31(int a, int b) { return (int)(((long long)a * (long long)b) >> 31); }
 
-ED_HD int sqrt_q31_newton(int in) {
+// not inlined on the device: it is the rare path of mag_q15 and would bloat the hot loop
+ED_HD_NOINLINE int sqrt_q31_newton(int in) {
   if (in <= 0) return 0;  // :127-133 (returns 0 with ARM_MATH_ARGUMENT_ERROR)
   int sign_bits = ed_clz(in) - 1;                      // :66
   int shift = sign_bits & ~1;                          // :69-76 (even shift)

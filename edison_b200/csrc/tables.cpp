@@ -63,10 +63,12 @@ int build_mfcc_tables(MfccTables *Tp, const char *mel_blob_path, char *err, size
     snprintf(err, errlen, "generated q15 tables differ from the CMSIS reference data (libm rounding?)");
     return EDISON_E_DATA;
   }
-  for (int j = 0; j < 256; j++)
-    for (int k = 0; k < 3; k++) T.tw1[k][j] = tw1024[(k + 1) * j];
-  for (int j = 0; j < 64; j++)
-    for (int k = 0; k < 3; k++) T.tw2[k][j] = tw1024[(k + 1) * 4 * j];
+  for (int k = 0; k < 3; k++)
+    for (int e = 0; e < 2; e++)
+      for (int lane = 0; lane < 32; lane++) {
+        for (int qp = 0; qp < 4; qp++) T.tw1[k][e][qp][lane] = tw1024[(k + 1) * (64 * qp + 2 * lane + e)];
+        T.tw2[k][e][lane] = tw1024[(k + 1) * 4 * (2 * lane + e)];
+      }
   for (int j = 0; j < 16; j++)
     for (int k = 0; k < 3; k++) T.tw3[k][j] = tw1024[(k + 1) * 16 * j];
   for (int j = 0; j < 4; j++)

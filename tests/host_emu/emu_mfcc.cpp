@@ -34,15 +34,19 @@ extern "C" int emu_mfcc_batch(const int16_t *pcm, long n_frames, int16_t *mfcc, 
       if (f >= n_frames) { for (int l = 0; l < 32; l++) mel[32 * g + l] = 0; continue; }
       const uint16_t *frame = (const uint16_t *)(pcm + f * kFrameLen);
       int peak = -1;
+      uint32_t w[32][16];
       for (int lane = 0; lane < 32; lane++) {
-        uint32_t w[16];
-        for (int q = 0; q < 16; q++) w[q] = frame[64 * q + 2 * lane] | ((uint32_t)frame[64 * q + 2 * lane + 1] << 16);
-        int p = phase_a(lane, w, T, xr, xi);
+        for (int q = 0; q < 16; q++) w[lane][q] = frame[64 * q + 2 * lane] | ((uint32_t)frame[64 * q + 2 * lane + 1] << 16);
+        int p = lane_peak(w[lane]);
         if (p > peak) peak = p;
       }
+      for (int lane = 0; lane < 32; lane++)
+        for (int e = 0; e < 2; e++) phase_a(lane, e, w[lane], T, xr, xi);
       bool sat = force_sat < 0 ? peak > kNoSatPeak : force_sat != 0;
-      for (int lane = 0; lane < 32; lane++) { if (sat) phase_b<true>(lane, T, xr, xi); else phase_b<false>(lane, T, xr, xi); }
-      for (int lane = 0; lane < 32; lane++) { if (sat) phase_c<true>(lane, T, xr, xi, spect); else phase_c<false>(lane, T, xr, xi, spect); }
+      for (int lane = 0; lane < 32; lane++)
+        for (int e = 0; e < 2; e++) { if (sat) phase_b<true>(lane, e, T, xr, xi); else phase_b<false>(lane, e, T, xr, xi); }
+      for (int lane = 0; lane < 32; lane++)
+        for (int i = 0; i < 8; i++) { if (sat) phase_c<true>(lane, i, T, xr, xi, spect); else phase_c<false>(lane, i, T, xr, xi, spect); }
       for (int lane = 0; lane < 32; lane++) mel[32 * g + lane] = phase_mel(lane, T, spect);
     }
     I2 *z = reinterpret_cast<I2 *>(xr);
