@@ -1,5 +1,5 @@
 // nnom_q7_kernel.cu -- K2: the int8 NNoM keyword-spotting net (firmware/src/ai/nnom/kws_nnom/weights.h:138-161)
-// over a batch of 31x13 inputs.
+// over a batch of 31x13 inputs, as implicit GEMMs on the int8 tensor cores.
 //
 // Replaces model_run (firmware/src/ai/nnom/src/core/nnom.c:996-1041) for this graph:
 //   Input(31,13,1) -> Conv 16@5x5 -> ReLU -> MaxPool(2,1) -> Conv 32@3x3 -> ReLU -> MaxPool(2,1)
@@ -8,10 +8,18 @@
 // (nnom_local.c:425-484), local_maxpool_q7_HWC (nnom_local.c:117-160), arm_fully_connected_q7_opt
 // (weights de-interleaved at conversion time) and the three softmax variants:
 //   out = SSAT8( ((bias << bias_lshift) + (1 << (out_rshift-1)) + sum in*w) >> out_rshift )
-// int32 accumulation is exact and order independent, so any tiling gives the reference's bits.
+// int32 accumulation is exact and order independent (|acc| < 2^24), so any MMA tiling gives the
+// reference's bits.
 //
-// This revision keeps a tile of clips in shared memory through all layers (activations never touch
-// HBM: 403 B in, 10 + 10 B out per clip) and does the contractions with IDP.4A.
+// Layout: a CTA keeps a tile of 16 clips in shared memory through all layers (activations never
+// touch HBM: 403 B in, 10 + 10 B out per clip).  Every layer is D[M x N] = A[M x K] * B[K x N] with
+//   M = output pixels of the 16 clips (for the pooled layers: row g / g+8 of an m16 tile are the two
+//       conv rows under one pooled pixel, so max-pool happens inside a thread's accumulators),
+//   K = (ky, kx, c) in the reference's O,H,W,I weight order, N = output channels,
+// issued as mma.sync.m16n8k32.s8.s8.s32.  A fragments are 32-bit loads straight from the HWC
+// activation buffers (implicit im2col; C = 32 / 64 buffers are XOR-swizzled per pixel so those loads
+// are bank-conflict free), B fragments are pre-packed in fragment order at model load.
+// Epilogue, fused: >> out_rshift, SSAT8, ReLU, (2x1 max pool), int8 store in the next layer's layout.
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -21,113 +29,55 @@
 
 namespace edison {
 
-// topology this build has kernels for
 constexpr int kInH = 31, kInW = 13;
-struct LayerDesc { int cout, kh, kw, cin, rshift, lshift, relu, pool; };
 constexpr int kC1 = 16, kC2 = 32, kC3 = 64, kC4 = 32, kDenseIn = 96, kDenseOut = 10;
 
-// packed device model: weights in the reference's O,H,W,I order, int8
+// device model: B fragments [k-step][n-tile][lane] = (b0, b1) of mma.m16n8k32 and accumulator seeds
 struct NnomModel {
-  int8_t w1[kC1 * 5 * 5 * 1];
-  int8_t w2[kC2 * 3 * 3 * kC1];
-  int8_t w3[kC3 * 3 * 3 * kC2];
-  int8_t w4[kC4 * 3 * 3 * kC3];
-  int8_t wd[kDenseOut * kDenseIn];
-  int8_t b1[kC1], b2[kC2], b3[kC3], b4[kC4], bd[16];
-  int rs[5], ls[5];
-  int pad_[2];
+  uint2 f1[2][2][32];    // conv1: K = 5 rows x 8 (kx padded 5 -> 8) = 40 -> 64, N = 16
+  uint2 f2[5][4][32];    // conv2: K = 9 taps x 16 = 144 -> 160, N = 32
+  uint2 f3[9][8][32];    // conv3: K = 9 x 32 = 288, N = 64
+  uint2 f4[18][4][32];   // conv4: K = 9 x 64 = 576, N = 32
+  uint2 fd[3][2][32];    // dense: K = 96, N = 10 -> 16
+  int seed1[16], seed2[32], seed3[64], seed4[32], seedd[16];   // (bias << bias_lshift) + (1 << (rshift-1))
+  int rs[5];
+  int pad_[3];
 };
 static_assert(sizeof(NnomModel) % 16 == 0, "NnomModel is copied with 16-byte vectors");
 
-constexpr int kClipsPerCta = 8;
+constexpr int kNC = 16;            // clips per CTA tile
 constexpr int kNetThreads = 256;
-constexpr int kBuf0 = 1120;   // input (403 -> 404), conv2 pooled 5*7*32, conv4 1*3*32
-constexpr int kBuf1 = 1872;   // conv1 pooled 13*9*16, conv3 3*5*64, logits
+constexpr int kNetWarps = kNetThreads / 32;
+constexpr int kInStride = 416;     // 403 input bytes per clip, padded
+constexpr int kPix1 = 13 * 9, kPix2 = 5 * 7, kPix3 = 3 * 5, kPix4 = 3;   // pixels per clip after each conv(+pool)
+constexpr int kRegionX = kNC * kPix2 * kC2;   // holds: input [16][416] | act2 [16][35][32] | act4 [16][3][32]
+constexpr int kRegionY = kNC * kPix1 * kC1;   // holds: act1 [16][117][16] | act3 [16][15][64] | logits [16][16]
+static_assert(kRegionX >= kNC * kInStride + 64 && kRegionY >= kNC * kPix3 * kC3, "regions");
 
 struct NetSmem {
   NnomModel M;
-  int8_t buf0[kClipsPerCta][kBuf0];
-  int8_t buf1[kClipsPerCta][kBuf1];
+  alignas(16) int8_t X[kRegionX];
+  alignas(16) int8_t Y[kRegionY];
 };
 
 __device__ __forceinline__ int ssat8(int v) { return min(max(v, -128), 127); }
 __device__ __forceinline__ int usat(int v, int bits) { return min(max(v, 0), (1 << bits) - 1); }
 
-// valid, stride-1 HWC convolution + ReLU + (POOL x 1) max pool, 4 output channels per work item
-template <int H, int W, int C, int O, int KH, int KW, int POOL, int IN_STRIDE, int OUT_STRIDE>
-__device__ __forceinline__ void conv_layer(const int8_t *in, int8_t *out, const int8_t *w, const int8_t *bias,
-                                           int rs, int ls, int nclips) {
-  constexpr int Ho = H - KH + 1, Wo = W - KW + 1;
-  constexpr int Hp = POOL > 1 ? (Ho - POOL) / POOL + 1 : Ho;
-  constexpr int R = POOL > 1 ? POOL : 1;
-  constexpr int OG = O / 4;
-  const int items = nclips * Hp * Wo * OG;
-  for (int idx = threadIdx.x; idx < items; idx += kNetThreads) {
-    const int og = idx % OG;
-    int t = idx / OG;
-    const int x = t % Wo; t /= Wo;
-    const int yp = t % Hp;
-    const int clip = t / Hp;
-    const int8_t *ib = in + clip * IN_STRIDE;
-    int acc[R][4];
-#pragma unroll
-    for (int r = 0; r < R; r++)
-#pragma unroll
-      for (int o = 0; o < 4; o++) acc[r][o] = ((int)bias[4 * og + o] << ls) + (1 << (rs - 1));
-    if constexpr (C % 4 == 0) {
-      constexpr int C4 = C / 4;
-      const int *iw = reinterpret_cast<const int *>(ib);
-      const int *ww = reinterpret_cast<const int *>(w) + (4 * og) * KH * KW * C4;
-#pragma unroll 1
-      for (int ky = 0; ky < KH; ky++) {
-#pragma unroll
-        for (int kx = 0; kx < KW; kx++) {
-#pragma unroll
-          for (int c = 0; c < C4; c++) {
-            int wv[4];
-#pragma unroll
-            for (int o = 0; o < 4; o++) wv[o] = ww[(o * KH * KW + ky * KW + kx) * C4 + c];
-#pragma unroll
-            for (int r = 0; r < R; r++) {
-              const int a = iw[((yp * R + r + ky) * W + (x + kx)) * C4 + c];
-#pragma unroll
-              for (int o = 0; o < 4; o++) acc[r][o] = __dp4a(a, wv[o], acc[r][o]);
-            }
-          }
-        }
-      }
-    } else {
-      static_assert(C == 1 || C % 4 == 0, "channel count");
-      const int8_t *wb = w + (4 * og) * KH * KW;
-#pragma unroll 1
-      for (int ky = 0; ky < KH; ky++) {
-#pragma unroll
-        for (int kx = 0; kx < KW; kx++) {
-          int wv[4];
-#pragma unroll
-          for (int o = 0; o < 4; o++) wv[o] = wb[o * KH * KW + ky * KW + kx];
-#pragma unroll
-          for (int r = 0; r < R; r++) {
-            const int a = ib[(yp * R + r + ky) * W + (x + kx)];
-#pragma unroll
-            for (int o = 0; o < 4; o++) acc[r][o] += a * wv[o];
-          }
-        }
-      }
-    }
-    uint32_t packed = 0;
-#pragma unroll
-    for (int o = 0; o < 4; o++) {
-      int v = -128;
-#pragma unroll
-      for (int r = 0; r < R; r++) v = max(v, ssat8(acc[r][o] >> rs));
-      v = max(v, 0);  // ReLU tail (nnom_activation.c:118-126); commutes with the max pool
-      packed |= (uint32_t)(v & 0xff) << (8 * o);
-    }
-    *reinterpret_cast<uint32_t *>(out + clip * OUT_STRIDE + (yp * Wo + x) * O + 4 * og) = packed;
-  }
+__device__ __forceinline__ void mma_s8(int (&d)[4], const uint32_t (&a)[4], uint2 b) {
+  asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
 }
 
+// word index of 32-bit word w of pixel P in an HWC buffer with C channels; C = 32 / 64 are swizzled
+template <int C> __device__ __forceinline__ int act_word(int P, int w) {
+  if (C == 32) return P * 8 + (w ^ (((P >> 2) & 1) << 2));
+  if (C == 64) return P * 16 + (w ^ (((P >> 1) & 3) << 2));
+  return P * (C / 4) + w;
+}
+
+// clamp(acc >> rs) to [0, 127]: SSAT8 followed by ReLU (nnom_activation.c:118-126)
+__device__ __forceinline__ int q7_relu(int acc, int rs) { return min(max(acc >> rs, 0), 127); }
 // arm_softmax_q7 (reference :217-254, SIMD :83-215) and local_softmax_q7 (nnom_local.c:948-1003)
 __device__ void softmax_q7(const int8_t *in, int8_t *out, int mode) {
   constexpr int n = kDenseOut;
@@ -165,8 +115,128 @@ __device__ void softmax_q7(const int8_t *in, int8_t *out, int mode) {
   }
 }
 
-__global__ void __launch_bounds__(kNetThreads) nnom_q7_kernel(const NnomModel *model, const int8_t *net_in, long long n,
-                                                               int8_t *logits, int8_t *softmax, int softmax_mode) {
+
+// ---- 3x3 valid convolution (+ ReLU, + optional 2x1 max pool) as an implicit GEMM -----------------------
+// in : HWC int8, pixel index P = clip * PIXS_IN + y * W_IN + x, layout act_word<C>
+// out: pixel index Q = clip * (HP * WO) + yo * WO + x, layout act_word<O> when OUT_SWZ else plain HWC
+// POOL: an m16 tile = 8 pooled pixels; row g is conv row 2 yo, row g + 8 is conv row 2 yo + 1.
+template <int W_IN, int PIXS_IN, int C, int O, int HP, int WO, bool POOL, bool OUT_SWZ, int NSPLIT>
+__device__ __forceinline__ void conv3x3_mma(const int8_t *in, int8_t *out, const uint2 *frag, const int *seed, int rs,
+                                            int nclips) {
+  constexpr int NT = O / 8, NTG = NT / NSPLIT;
+  constexpr int KSTEPS = (9 * C + 31) / 32;
+  constexpr int PIXS_OUT = HP * WO;
+  constexpr int PER_TILE = POOL ? 8 : 16;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+  const int rows_total = nclips * PIXS_OUT;
+  const int n_items = ((rows_total + PER_TILE - 1) / PER_TILE) * NSPLIT;
+  const uint32_t *inw = reinterpret_cast<const uint32_t *>(in);
+  for (int item = warp; item < n_items; item += kNetWarps) {
+    const int tile = item / NSPLIT, nt0 = (item - tile * NSPLIT) * NTG;
+    const int q0 = tile * PER_TILE + g, q1 = POOL ? q0 : q0 + 8;
+    const bool v0 = q0 < rows_total, v1 = q1 < rows_total;
+    const int qa = v0 ? q0 : 0, qb = v1 ? q1 : 0;
+    const int ca = qa / PIXS_OUT, ra = qa - ca * PIXS_OUT, ya = ra / WO, xa = ra - ya * WO;
+    const int cb = qb / PIXS_OUT, rb = qb - cb * PIXS_OUT, yb = rb / WO, xb = rb - yb * WO;
+    const int Pa = ca * PIXS_IN + (POOL ? 2 * ya : ya) * W_IN + xa;
+    const int Pb = cb * PIXS_IN + (POOL ? 2 * yb + 1 : yb) * W_IN + xb;
+    int acc[NTG][4];
+#pragma unroll
+    for (int n = 0; n < NTG; n++) {
+      acc[n][0] = acc[n][2] = seed[8 * (nt0 + n) + 2 * t];
+      acc[n][1] = acc[n][3] = seed[8 * (nt0 + n) + 2 * t + 1];
+    }
+#pragma unroll
+    for (int ks = 0; ks < KSTEPS; ks++) {
+      uint32_t a[4];
+      if (C == 16) {  // two taps per k-step; the 10th (padding) tap has zero weights
+        const int tap0 = 2 * ks, tap1 = 2 * ks + 1 < 9 ? 2 * ks + 1 : 8;
+        const int o0 = (tap0 / 3) * W_IN + tap0 % 3, o1 = (tap1 / 3) * W_IN + tap1 % 3;
+        a[0] = inw[act_word<C>(Pa + o0, t)]; a[1] = inw[act_word<C>(Pb + o0, t)];
+        a[2] = inw[act_word<C>(Pa + o1, t)]; a[3] = inw[act_word<C>(Pb + o1, t)];
+      } else {
+        const int tap = C == 32 ? ks : ks >> 1, hb = C == 32 ? 0 : (ks & 1) * 8;
+        const int o0 = (tap / 3) * W_IN + tap % 3;
+        a[0] = inw[act_word<C>(Pa + o0, hb + t)];     a[1] = inw[act_word<C>(Pb + o0, hb + t)];
+        a[2] = inw[act_word<C>(Pa + o0, hb + 4 + t)]; a[3] = inw[act_word<C>(Pb + o0, hb + 4 + t)];
+      }
+#pragma unroll
+      for (int n = 0; n < NTG; n++) mma_s8(acc[n], a, frag[(ks * NT + nt0 + n) * 32 + lane]);
+    }
+    // epilogue: channels 8 nt + 2t, 2t + 1 of this thread's one (POOL) or two pixels
+#pragma unroll
+    for (int n = 0; n < NTG; n++) {
+      const int w = 2 * (nt0 + n) + (t >> 1), hoff = t & 1;
+      if (POOL) {
+        const int lo = q7_relu(max(acc[n][0], acc[n][2]), rs), hi = q7_relu(max(acc[n][1], acc[n][3]), rs);
+        if (v0) {
+          const int wi = OUT_SWZ ? act_word<O>(q0, w) : q0 * (O / 4) + w;
+          reinterpret_cast<uint16_t *>(out)[2 * wi + hoff] = (uint16_t)(lo | (hi << 8));
+        }
+      } else {
+        if (v0) {
+          const int wi = OUT_SWZ ? act_word<O>(q0, w) : q0 * (O / 4) + w;
+          reinterpret_cast<uint16_t *>(out)[2 * wi + hoff] = (uint16_t)(q7_relu(acc[n][0], rs) | (q7_relu(acc[n][1], rs) << 8));
+        }
+        if (v1) {
+          const int wi = OUT_SWZ ? act_word<O>(q1, w) : q1 * (O / 4) + w;
+          reinterpret_cast<uint16_t *>(out)[2 * wi + hoff] = (uint16_t)(q7_relu(acc[n][2], rs) | (q7_relu(acc[n][3], rs) << 8));
+        }
+      }
+    }
+  }
+}
+
+// ---- conv1: 5x5, one input channel, 16 outputs, ReLU, 2x1 max pool ---------------------------------------
+// K is re-indexed as ky * 8 + kx (kx padded 5 -> 8, ky padded 5 -> 8 with zero weights), so that the four
+// k of one A register are four consecutive input bytes of one row (an unaligned 32-bit fetch).
+__device__ __forceinline__ uint32_t ld_unaligned32(const uint32_t *words, int byte_addr) {
+  const int wa = byte_addr >> 2;
+  return __funnelshift_r(words[wa], words[wa + 1], (byte_addr & 3) * 8);
+}
+
+__device__ __forceinline__ void conv1_mma(const int8_t *in, int8_t *out, const uint2 *frag, const int *seed, int rs,
+                                          int nclips) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+  const int rows_total = nclips * kPix1;   // pooled pixels
+  const int n_tiles = (rows_total + 7) / 8;
+  const uint32_t *inw = reinterpret_cast<const uint32_t *>(in);
+  for (int tile = warp; tile < n_tiles; tile += kNetWarps) {
+    const int q0 = tile * 8 + g;
+    const bool v0 = q0 < rows_total;
+    const int qa = v0 ? q0 : 0;
+    const int ca = qa / kPix1, ra = qa - ca * kPix1, yp = ra / 9, x = ra - yp * 9;
+    const int base = ca * kInStride + (2 * yp) * kInW + x;   // byte address of in[2 yp][x]; row g + 8 is one row down
+    int acc[2][4];
+#pragma unroll
+    for (int n = 0; n < 2; n++) {
+      acc[n][0] = acc[n][2] = seed[8 * n + 2 * t];
+      acc[n][1] = acc[n][3] = seed[8 * n + 2 * t + 1];
+    }
+#pragma unroll
+    for (int ks = 0; ks < 2; ks++) {
+      uint32_t a[4];
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const int ky = 4 * ks + 2 * h + (t >> 1), kx0 = 4 * (t & 1);
+        a[2 * h] = ld_unaligned32(inw, base + ky * kInW + kx0);
+        a[2 * h + 1] = ld_unaligned32(inw, base + (ky + 1) * kInW + kx0);
+      }
+      mma_s8(acc[0], a, frag[(ks * 2 + 0) * 32 + lane]);
+      mma_s8(acc[1], a, frag[(ks * 2 + 1) * 32 + lane]);
+    }
+    if (v0) {
+#pragma unroll
+      for (int n = 0; n < 2; n++) {
+        const int lo = q7_relu(max(acc[n][0], acc[n][2]), rs), hi = q7_relu(max(acc[n][1], acc[n][3]), rs);
+        reinterpret_cast<uint16_t *>(out)[(q0 * kC1 + 8 * n + 2 * t) >> 1] = (uint16_t)(lo | (hi << 8));
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kNetThreads, 2) nnom_q7_kernel(const NnomModel *model, const int8_t *net_in, long long n,
+                                                                  int8_t *logits, int8_t *softmax, int softmax_mode) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   NetSmem &S = *reinterpret_cast<NetSmem *>(smem_raw);
   {
@@ -174,44 +244,58 @@ __global__ void __launch_bounds__(kNetThreads) nnom_q7_kernel(const NnomModel *m
     int4 *dst = reinterpret_cast<int4 *>(&S.M);
     for (int i = threadIdx.x; i < (int)(sizeof(NnomModel) / 16); i += kNetThreads) dst[i] = src[i];
   }
-  __syncthreads();
   const NnomModel &M = S.M;
-  const long long n_tiles = (n + kClipsPerCta - 1) / kClipsPerCta;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+  const long long n_tiles = (n + kNC - 1) / kNC;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const long long c0 = tile * kClipsPerCta;
-    const int nclips = (int)min((long long)kClipsPerCta, n - c0);
+    const long long c0 = tile * kNC;
+    const int nclips = (int)min((long long)kNC, n - c0);
+    __syncthreads();   // previous tile's readers are done (and, first time, the model copy is visible)
+    // input: 403 bytes per clip -> X[clip * 416 ..]; the pad bytes only ever meet zero weights
     for (int i = threadIdx.x; i < nclips * EDISON_NET_IN; i += kNetThreads) {
       const int clip = i / EDISON_NET_IN, j = i - clip * EDISON_NET_IN;
-      S.buf0[clip][j] = net_in[(c0 + clip) * EDISON_NET_IN + j];
+      S.X[clip * kInStride + j] = net_in[(c0 + clip) * EDISON_NET_IN + j];
     }
     __syncthreads();
-    conv_layer<31, 13, 1, kC1, 5, 5, 2, kBuf0, kBuf1>(&S.buf0[0][0], &S.buf1[0][0], M.w1, M.b1, M.rs[0], M.ls[0], nclips);
+    conv1_mma(S.X, S.Y, &M.f1[0][0][0], M.seed1, M.rs[0], nclips);                                          // -> act1 [13][9][16]
     __syncthreads();
-    conv_layer<13, 9, kC1, kC2, 3, 3, 2, kBuf1, kBuf0>(&S.buf1[0][0], &S.buf0[0][0], M.w2, M.b2, M.rs[1], M.ls[1], nclips);
+    conv3x3_mma<9, kPix1, kC1, kC2, 5, 7, true, true, 1>(S.Y, S.X, &M.f2[0][0][0], M.seed2, M.rs[1], nclips);   // -> act2 [5][7][32]
     __syncthreads();
-    conv_layer<5, 7, kC2, kC3, 3, 3, 0, kBuf0, kBuf1>(&S.buf0[0][0], &S.buf1[0][0], M.w3, M.b3, M.rs[2], M.ls[2], nclips);
+    conv3x3_mma<7, kPix2, kC2, kC3, 3, 5, false, true, 2>(S.X, S.Y, &M.f3[0][0][0], M.seed3, M.rs[2], nclips);  // -> act3 [3][5][64]
     __syncthreads();
-    conv_layer<3, 5, kC3, kC4, 3, 3, 0, kBuf1, kBuf0>(&S.buf1[0][0], &S.buf0[0][0], M.w4, M.b4, M.rs[3], M.ls[3], nclips);
+    conv3x3_mma<5, kPix3, kC3, kC4, 1, 3, false, false, 4>(S.Y, S.X, &M.f4[0][0][0], M.seed4, M.rs[3], nclips); // -> act4 [1][3][32]
     __syncthreads();
-    // Dense 96 -> 10 (nnom_dense.c:92-119), logits into buf1
-    for (int idx = threadIdx.x; idx < nclips * kDenseOut; idx += kNetThreads) {
-      const int clip = idx / kDenseOut, r = idx - clip * kDenseOut;
-      const int *a = reinterpret_cast<const int *>(&S.buf0[clip][0]);
-      const int *wr = reinterpret_cast<const int *>(M.wd + r * kDenseIn);
-      int acc = ((int)M.bd[r] << M.ls[4]) + (1 << (M.rs[4] - 1));
+    // Dense 96 -> 10 (nnom_dense.c:92-119): rows = clips, one m16 tile, two n8 tiles on warps 0 and 1
+    if (warp < 2) {
+      const uint32_t *aw = reinterpret_cast<const uint32_t *>(S.X);
+      const int r0 = g < nclips ? g : 0, r1 = g + 8 < nclips ? g + 8 : 0;
+      int acc[4];
+      acc[0] = acc[2] = M.seedd[8 * warp + 2 * t];
+      acc[1] = acc[3] = M.seedd[8 * warp + 2 * t + 1];
 #pragma unroll
-      for (int j = 0; j < kDenseIn / 4; j++) acc = __dp4a(a[j], wr[j], acc);
-      const int8_t v = (int8_t)ssat8(acc >> M.rs[4]);
-      S.buf1[clip][r] = v;
-      if (logits) logits[(c0 + clip) * kDenseOut + r] = v;
+      for (int ks = 0; ks < 3; ks++) {
+        uint32_t a[4];
+        a[0] = aw[r0 * 24 + 8 * ks + t];     a[1] = aw[r1 * 24 + 8 * ks + t];
+        a[2] = aw[r0 * 24 + 8 * ks + 4 + t]; a[3] = aw[r1 * 24 + 8 * ks + 4 + t];
+        mma_s8(acc, a, M.fd[ks][warp][lane]);
+      }
+      const int rs = M.rs[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int clip = g + 8 * (j >> 1), col = 8 * warp + 2 * t + (j & 1);
+        if (clip < nclips && col < kDenseOut) {
+          const int8_t v = (int8_t)ssat8(acc[j] >> rs);
+          S.Y[clip * 16 + col] = v;
+          if (logits) logits[(c0 + clip) * kDenseOut + col] = v;
+        }
+      }
     }
     __syncthreads();
     if (softmax && threadIdx.x < nclips) {
       int8_t sm[kDenseOut];
-      softmax_q7(&S.buf1[threadIdx.x][0], sm, softmax_mode);
+      softmax_q7(&S.Y[threadIdx.x * 16], sm, softmax_mode);
       for (int i = 0; i < kDenseOut; i++) softmax[(c0 + threadIdx.x) * kDenseOut + i] = sm[i];
     }
-    __syncthreads();
   }
 }
 
@@ -222,64 +306,105 @@ cudaError_t nnom_configure(void) {
 cudaError_t launch_nnom_q7(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax,
                            int softmax_mode, int sm_count, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
-  const long long n_tiles = (n + kClipsPerCta - 1) / kClipsPerCta;
-  long long ctas = n_tiles < (long long)sm_count * 3 ? n_tiles : (long long)sm_count * 3;
+  const long long n_tiles = (n + kNC - 1) / kNC;
+  long long ctas = n_tiles < (long long)sm_count * 2 ? n_tiles : (long long)sm_count * 2;
   nnom_q7_kernel<<<(unsigned)ctas, kNetThreads, sizeof(NetSmem), stream>>>(model, net_in, n, logits, softmax, softmax_mode);
   count_launch();
   return cudaGetLastError();
 }
 
-// ---- blob loader (tools/convert_nnom_weights.py) ------------------------------------------------
+// ---- blob loader (tools/convert_nnom_weights.py) -> fragment-ordered device model ---------------------
+namespace {
+struct HostLayer { uint32_t h[9]; const int8_t *w, *b; };
+
+// B[k][n] of one layer -> mma.m16n8k32 B fragments: lane (g = lane >> 2, t = lane & 3) holds
+// b0 = B[32 ks + 4t .. +3][8 nt + g], b1 = B[32 ks + 16 + 4t .. +3][8 nt + g]
+template <class F> void pack_frags(uint2 *dst, int ksteps, int ntiles, F weight) {
+  for (int ks = 0; ks < ksteps; ks++)
+    for (int nt = 0; nt < ntiles; nt++)
+      for (int lane = 0; lane < 32; lane++) {
+        const int g = lane >> 2, t = lane & 3;
+        uint32_t b[2] = {0, 0};
+        for (int half = 0; half < 2; half++)
+          for (int i = 0; i < 4; i++)
+            b[half] |= (uint32_t)(uint8_t)weight(32 * ks + 16 * half + 4 * t + i, 8 * nt + g) << (8 * i);
+        dst[(ks * ntiles + nt) * 32 + lane] = make_uint2(b[0], b[1]);
+      }
+}
+}  // namespace
+
 int nnom_load(const char *path, NnomModel **out_dev, int *in_scale, int *in_min, int *in_max, char *err, size_t errlen) {
   FILE *fh = fopen(path, "rb");
   if (!fh) { snprintf(err, errlen, "cannot open %s", path); return EDISON_E_DATA; }
   fseek(fh, 0, SEEK_END);
   long sz = ftell(fh);
   fseek(fh, 0, SEEK_SET);
-  unsigned char *blob = (unsigned char *)malloc((size_t)sz);
+  unsigned char *blob = (unsigned char *)malloc((size_t)sz + 1);
   if (!blob) { fclose(fh); return EDISON_E_NOMEM; }
   if (fread(blob, 1, (size_t)sz, fh) != (size_t)sz) { fclose(fh); free(blob); snprintf(err, errlen, "%s: short read", path); return EDISON_E_DATA; }
   fclose(fh);
-  if (sz < 16 || memcmp(blob, "EDNNQ7\0\0", 8)) { free(blob); snprintf(err, errlen, "%s: bad header", path); return EDISON_E_DATA; }
-  uint32_t ver, nl;
-  memcpy(&ver, blob + 8, 4); memcpy(&nl, blob + 12, 4);
-  if (ver != 1) { free(blob); snprintf(err, errlen, "%s: version %u", path, ver); return EDISON_E_DATA; }
-  // the graph this build has kernels for: kind, cout, kh, kw, cin, relu, pool
-  static const uint32_t expect[5][7] = {{1, kC1, 5, 5, 1, 1, 2}, {1, kC2, 3, 3, kC1, 1, 2}, {1, kC3, 3, 3, kC2, 1, 0},
-                                        {1, kC4, 3, 3, kC3, 1, 0}, {2, kDenseOut, 1, 1, kDenseIn, 0, 0}};
-  if (nl != 5) { free(blob); snprintf(err, errlen, "%s: %u layers, this build runs the 5-layer kws_conv graph", path, nl); return EDISON_E_MODEL; }
-  NnomModel *M = (NnomModel *)calloc(1, sizeof(NnomModel));
-  int8_t *wdst[5] = {M->w1, M->w2, M->w3, M->w4, M->wd};
-  int8_t *bdst[5] = {M->b1, M->b2, M->b3, M->b4, M->bd};
-  const unsigned char *p = blob + 16, *end = blob + sz;
-  for (int i = 0; i < 5; i++) {
-    uint32_t h[9];
-    if (p + 36 > end) { free(blob); free(M); snprintf(err, errlen, "%s: truncated", path); return EDISON_E_DATA; }
-    memcpy(h, p, 36); p += 36;
-    const uint32_t got[7] = {h[0], h[1], h[2], h[3], h[4], h[7], h[8]};
-    if (memcmp(got, expect[i], sizeof got)) { free(blob); free(M); snprintf(err, errlen, "%s: layer %d is not the kws_conv layer this build implements", path, i); return EDISON_E_MODEL; }
-    if (h[5] < 1 || h[5] > 24 || h[6] > 24) { free(blob); free(M); snprintf(err, errlen, "%s: layer %d shifts out of range", path, i); return EDISON_E_DATA; }
-    const size_t nw = (size_t)h[1] * h[2] * h[3] * h[4];
-    if (p + nw + h[1] > end) { free(blob); free(M); snprintf(err, errlen, "%s: truncated", path); return EDISON_E_DATA; }
-    memcpy(wdst[i], p, nw); p += nw;
-    memcpy(bdst[i], p, h[1]); p += h[1];
-    p += (size_t)(-(p - blob)) & 3;
-    M->rs[i] = (int)h[5]; M->ls[i] = (int)h[6];
-  }
-  if (p + 24 > end) { free(blob); free(M); snprintf(err, errlen, "%s: truncated trailer", path); return EDISON_E_DATA; }
-  int32_t t[3]; uint32_t s[3];
-  memcpy(t, p, 12); memcpy(s, p + 12, 12);
-  free(blob);
-  if (s[0] != (uint32_t)kInH || s[1] != (uint32_t)kInW || s[2] != 1 || t[0] == 0) { free(M); snprintf(err, errlen, "%s: input shape/scale unsupported", path); return EDISON_E_MODEL; }
-  *in_scale = t[0]; *in_min = t[1]; *in_max = t[2];
-  NnomModel *d = nullptr;
-  if (cudaMalloc(&d, sizeof(NnomModel)) != cudaSuccess) { free(M); return EDISON_E_CUDA; }
-  if (cudaMemcpy(d, M, sizeof(NnomModel), cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(d); free(M); return EDISON_E_CUDA; }
+  int rc = EDISON_OK;
+  NnomModel *M = nullptr;
+  do {
+    if (sz < 16 || memcmp(blob, "EDNNQ7\0\0", 8)) { snprintf(err, errlen, "%s: bad header", path); rc = EDISON_E_DATA; break; }
+    uint32_t ver, nl;
+    memcpy(&ver, blob + 8, 4); memcpy(&nl, blob + 12, 4);
+    if (ver != 1) { snprintf(err, errlen, "%s: version %u", path, ver); rc = EDISON_E_DATA; break; }
+    // the graph this build has kernels for: kind, cout, kh, kw, cin, relu, pool
+    static const uint32_t expect[5][7] = {{1, kC1, 5, 5, 1, 1, 2}, {1, kC2, 3, 3, kC1, 1, 2}, {1, kC3, 3, 3, kC2, 1, 0},
+                                          {1, kC4, 3, 3, kC3, 1, 0}, {2, kDenseOut, 1, 1, kDenseIn, 0, 0}};
+    if (nl != 5) { snprintf(err, errlen, "%s: %u layers, this build runs the 5-layer kws_conv graph", path, nl); rc = EDISON_E_MODEL; break; }
+    HostLayer L[5];
+    const unsigned char *p = blob + 16, *end = blob + sz;
+    for (int i = 0; i < 5 && rc == EDISON_OK; i++) {
+      if (p + 36 > end) { snprintf(err, errlen, "%s: truncated", path); rc = EDISON_E_DATA; break; }
+      memcpy(L[i].h, p, 36); p += 36;
+      const uint32_t *h = L[i].h;
+      const uint32_t got[7] = {h[0], h[1], h[2], h[3], h[4], h[7], h[8]};
+      if (memcmp(got, expect[i], sizeof got)) { snprintf(err, errlen, "%s: layer %d is not the kws_conv layer this build implements", path, i); rc = EDISON_E_MODEL; break; }
+      if (h[5] < 1 || h[5] > 24 || h[6] > 16) { snprintf(err, errlen, "%s: layer %d shifts out of range", path, i); rc = EDISON_E_DATA; break; }
+      const size_t nw = (size_t)h[1] * h[2] * h[3] * h[4];
+      if (p + nw + h[1] > end) { snprintf(err, errlen, "%s: truncated", path); rc = EDISON_E_DATA; break; }
+      L[i].w = (const int8_t *)p; p += nw;
+      L[i].b = (const int8_t *)p; p += h[1];
+      p += (size_t)(-(p - blob)) & 3;
+    }
+    if (rc) break;
+    if (p + 24 > end) { snprintf(err, errlen, "%s: truncated trailer", path); rc = EDISON_E_DATA; break; }
+    int32_t tq[3]; uint32_t sh[3];
+    memcpy(tq, p, 12); memcpy(sh, p + 12, 12);
+    if (sh[0] != (uint32_t)kInH || sh[1] != (uint32_t)kInW || sh[2] != 1 || tq[0] == 0) { snprintf(err, errlen, "%s: input shape/scale unsupported", path); rc = EDISON_E_MODEL; break; }
+    *in_scale = tq[0]; *in_min = tq[1]; *in_max = tq[2];
+    M = (NnomModel *)calloc(1, sizeof(NnomModel));
+    if (!M) { rc = EDISON_E_NOMEM; break; }
+    // conv1: k = ky * 8 + kx (zero outside the 5x5 window); weights [o][ky][kx]
+    pack_frags(&M->f1[0][0][0], 2, 2, [&](int k, int n) -> int8_t {
+      const int ky = k >> 3, kx = k & 7;
+      return (ky < 5 && kx < 5) ? L[0].w[(n * 5 + ky) * 5 + kx] : (int8_t)0;
+    });
+    // conv2..4: k = (ky * 3 + kx) * C + c == the reference's O,H,W,I order; zero beyond 9 C
+    pack_frags(&M->f2[0][0][0], 5, 4, [&](int k, int n) -> int8_t { return k < 144 ? L[1].w[n * 144 + k] : (int8_t)0; });
+    pack_frags(&M->f3[0][0][0], 9, 8, [&](int k, int n) -> int8_t { return L[2].w[n * 288 + k]; });
+    pack_frags(&M->f4[0][0][0], 18, 4, [&](int k, int n) -> int8_t { return L[3].w[n * 576 + k]; });
+    pack_frags(&M->fd[0][0][0], 3, 2, [&](int k, int n) -> int8_t { return n < kDenseOut ? L[4].w[n * kDenseIn + k] : (int8_t)0; });
+    int *seeds[5] = {M->seed1, M->seed2, M->seed3, M->seed4, M->seedd};
+    for (int i = 0; i < 5; i++) {
+      M->rs[i] = (int)L[i].h[5];
+      for (uint32_t o = 0; o < L[i].h[1]; o++)
+        seeds[i][o] = (int)((uint32_t)(int32_t)L[i].b[o] << L[i].h[6]) + (1 << (L[i].h[5] - 1));
+    }
+    NnomModel *d = nullptr;
+    if (cudaMalloc(&d, sizeof(NnomModel)) != cudaSuccess) { snprintf(err, errlen, "cudaMalloc(model)"); rc = EDISON_E_CUDA; break; }
+    if (cudaMemcpy(d, M, sizeof(NnomModel), cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(d); snprintf(err, errlen, "cudaMemcpy(model)"); rc = EDISON_E_CUDA; break; }
+    *out_dev = d;
+  } while (0);
   free(M);
-  *out_dev = d;
-  return EDISON_OK;
+  free(blob);
+  return rc;
 }
 
-void nnom_free(NnomModel *m) { if (m) cudaFree(m); }
+void nnom_free(NnomModel *m) {
+  if (m) cudaFree(m);
+}
 
 }  // namespace edison
