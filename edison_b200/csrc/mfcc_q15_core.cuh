@@ -34,11 +34,24 @@ constexpr int kNCoeff = 13;       // aiGetInputShape, firmware/src/ai/ai.c:205-2
 constexpr int kGroup = 8;         // frames per warp iteration (DCT batch)
 constexpr int kMelMaxW = 1024;    // capacity for melMtxCompact (915 in the reference header)
 
-// exchange buffer: two planes (re, im) of 1024 int32.  Position p = 64 q + 2 l + e is stored at
+// exchange buffer: 1024 packed complex points (re in the low, im in the high 16 bits of one word; the
+// FFT's intermediate values are q15 by construction).  Position p = 64 q + 2 l + e is stored at
 //   e * 544 + 34 q + l          (q = p >> 6, l = (p >> 1) & 31, e = p & 1)
 // so that every access pattern of the three phases is free of bank conflicts.
 constexpr int kXchHalf = 16 * 34;
-constexpr int kXchPlane = 2 * kXchHalf;
+constexpr int kXchWords = 2 * kXchHalf;
+ED_HD uint32_t pack_c(int re, int im) { return ((uint32_t)re & 0xffffu) | ((uint32_t)im << 16); }
+ED_HD int c_re(uint32_t w) { return (int)(int16_t)(w & 0xffffu); }
+ED_HD int c_im(uint32_t w) { return (int)w >> 16; }
+
+// magnitude spectrum of the 4 frames of a half-group, as two byte planes (low / high byte of the q15
+// magnitude) so that the mel filterbank can run on the u8 tensor cores: [plane][frame][bin], rows padded
+// to 528 bytes (132 words) which makes the B-fragment loads conflict-free.
+constexpr int kSub = 4;
+constexpr int kSpectRowWords = 132;
+constexpr int kSpectPlaneWords = kSub * kSpectRowWords;
+constexpr int kSpectWords = 2 * kSpectPlaneWords;
+constexpr int kMelPairsMax = 32;   // (16-filter tile, 32-bin k-step) pairs with a non-zero weight
 
 // ---- constant tables, one copy per CTA in shared memory -----------------------------------------
 struct MfccTables {
@@ -50,10 +63,11 @@ struct MfccTables {
   I2 realA[16];         // realCoefAQ15 at stride 512 (arm_rfft_init_q15.c:213-222, fftLenReal 32)
   I2 realB[16];
   uint32_t sqrt_exc[kSqrtExcWords];
-  int16_t mel_w[kMelMaxW];      // melMtxCompact   (firmware/src/audio/mel_constants.h:2586)
-  int16_t mel_start[kNMel];     // melCompFStarts
-  int16_t mel_cnt[kNMel];       // melCompFCount
-  int16_t mel_off[kNMel];       // prefix sum of counts
+  // mel weights (melMtxCompact, firmware/src/audio/mel_constants.h:2586) as mma.m16n8k32 A fragments:
+  // pair p covers filters 16 mt .. 16 mt + 15 and bins 32 ks .. 32 ks + 31; pairs with mt = 0 come first
+  I4 mel_a[kMelPairsMax][32];
+  uint8_t mel_ks[kMelPairsMax];
+  int mel_n0, mel_n1;           // number of pairs with mt = 0 / mt = 1
   int in_scale, in_min, in_max; // NNOM_INPUT_SCALE/MIN/MAX (weights.h:162-164)
   int pad_;
 };
@@ -93,7 +107,7 @@ constexpr int kNoSatPeak = 32000;
 
 // ---- phase A: stages 1 and 2 for the 16 points p = 64 q + 2 lane + e of one parity e ------------
 // w[q] = the 32-bit word holding samples 64q+2L (low half) and 64q+2L+1 (high half).
-ED_HD void phase_a(int lane, int e, const uint32_t w[16], const MfccTables &T, int *xr, int *xi) {
+ED_HD void phase_a(int lane, int e, const uint32_t w[16], const MfccTables &T, uint32_t *x) {
   int re[16], im[16];
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -124,31 +138,29 @@ ED_HD void phase_a(int lane, int e, const uint32_t w[16], const MfccTables &T, i
 #pragma unroll
 #endif
     for (int g = 0; g < 4; g++)
-      bfly_mid<false>(re[4 * g], im[4 * g], re[4 * g + 1], im[4 * g + 1], re[4 * g + 2], im[4 * g + 2], re[4 * g + 3],
-                      im[4 * g + 3], w1, w2, w3);
+      bfly_mid_raw<false>(re[4 * g], im[4 * g], re[4 * g + 1], im[4 * g + 1], re[4 * g + 2], im[4 * g + 2], re[4 * g + 3],
+                          im[4 * g + 3], w1, w2, w3);
   }
-  // exchange 1
+  // exchange 1 (q = 4g holds a finished value, the other three hold unshifted twiddle sums)
   const int base = e * kXchHalf + lane;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-  for (int q = 0; q < 16; q++) {
-    xr[base + 34 * q] = re[q];
-    xi[base + 34 * q] = im[q];
-  }
+  for (int q = 0; q < 16; q++) x[base + 34 * q] = (q & 3) ? pack_hi(re[q], im[q]) : pack_c(re[q], im[q]);
 }
 
 // ---- phase B: stages 3 and 4 for the 16 points p = 64 (L>>1) + 4 t + 2 (L&1) + e ----------------
 template <bool SAT>
-ED_HD void phase_b(int lane, int e, const MfccTables &T, int *xr, int *xi) {
+ED_HD void phase_b(int lane, int e, const MfccTables &T, uint32_t *x) {
   int re[16], im[16];  // index t = bits 5..2 of p
   const int base = e * kXchHalf + 34 * (lane >> 1) + (lane & 1);
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
   for (int t = 0; t < 16; t++) {
-    re[t] = xr[base + 2 * t];
-    im[t] = xi[base + 2 * t];
+    const uint32_t v = x[base + 2 * t];
+    re[t] = c_re(v);
+    im[t] = c_im(v);
   }
   // stage 3: n2 = 16, twiddle index j3 = p & 15 = 4 tl + 2 (L&1) + e
 #if defined(__CUDA_ARCH__)
@@ -167,49 +179,65 @@ ED_HD void phase_b(int lane, int e, const MfccTables &T, int *xr, int *xi) {
 #pragma unroll
 #endif
     for (int th = 0; th < 4; th++)
-      bfly_mid<SAT>(re[4 * th], im[4 * th], re[4 * th + 1], im[4 * th + 1], re[4 * th + 2], im[4 * th + 2],
-                    re[4 * th + 3], im[4 * th + 3], w1, w2, w3);
+      bfly_mid_raw<SAT>(re[4 * th], im[4 * th], re[4 * th + 1], im[4 * th + 1], re[4 * th + 2], im[4 * th + 2],
+                        re[4 * th + 3], im[4 * th + 3], w1, w2, w3);
   }
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-  for (int t = 0; t < 16; t++) {
-    xr[base + 2 * t] = re[t];
-    xi[base + 2 * t] = im[t];
-  }
+  for (int t = 0; t < 16; t++) x[base + 2 * t] = (t & 3) ? pack_hi(re[t], im[t]) : pack_c(re[t], im[t]);
 }
 
-ED_HD int rev3(int i) { return ((i & 1) << 2) | (i & 2) | ((i >> 2) & 1); }
+ED_HD int rev2(int i) { return ((i & 1) << 1) | ((i >> 1) & 1); }
 ED_HD int rev5(int i) {
   return ((i & 1) << 4) | ((i & 2) << 2) | (i & 4) | ((i >> 2) & 2) | ((i >> 4) & 1);
 }
 
 // ---- phase C: stage 5 (outputs 0 and 2 of each butterfly), cmpl_mag_q15 --------------------------
-// Butterfly j = 8 L + i sits at positions 4j..4j+3; its outputs 4j and 4j+2 are bins
-// r = rev8(j) = 32 rev3(i) + rev5(L) and r + 256.  Outputs 4j+1, 4j+3 are bins >= 512, which
-// nothing reads (the mel filters end at bin 486; audioprocessing.c:157-170).
+// Butterfly j sits at positions 4j..4j+3; its outputs 4j and 4j+2 are bins r = rev8(j) and r + 256.
+// Outputs 4j+1, 4j+3 are bins >= 512, which nothing reads (the mel filters end at bin 486;
+// audioprocessing.c:157-170).  Trip s (0, 1) of lane L handles the four butterflies
+// j = 64 rev2(v) + 2 rev5(L) + s, v = 0..3, i.e. the consecutive bins 4L + 128 s + v (and + 256),
+// whose magnitudes are packed four to a word into the two byte planes of this frame's row.
 template <bool SAT>
-ED_HD void phase_c(int lane, int i, const MfccTables &T, const int *xr, const int *xi, int *spect) {
-  // positions 4j+k, k = 0..3: (k = 0, 2) are adjacent words of the even half, (1, 3) of the odd half
-  const int a = 34 * (lane >> 1) + 16 * (lane & 1) + 2 * i;
-  const I2 ac_r = *reinterpret_cast<const I2 *>(xr + a), bd_r = *reinterpret_cast<const I2 *>(xr + kXchHalf + a);
-  const I2 ac_i = *reinterpret_cast<const I2 *>(xi + a), bd_i = *reinterpret_cast<const I2 *>(xi + kXchHalf + a);
-  const int Rr = qadd16<SAT>(ac_r.x, ac_r.y), Ri = qadd16<SAT>(ac_i.x, ac_i.y);
-  const int Sr = qsub16<SAT>(ac_r.x, ac_r.y), Si = qsub16<SAT>(ac_i.x, ac_i.y);
-  const int Tr = qadd16<SAT>(bd_r.x, bd_r.y), Ti = qadd16<SAT>(bd_i.x, bd_i.y);
-  const int Ur = qsub16<SAT>(bd_r.x, bd_r.y), Ui = qsub16<SAT>(bd_i.x, bd_i.y);
-  const int r = 32 * rev3(i) + rev5(lane);
-  spect[r] = mag_q15((Rr + Tr) >> 1, (Ri + Ti) >> 1, T.sqrt_exc);
-  spect[r + 256] = mag_q15((Sr + Ui) >> 1, (Si - Ur) >> 1, T.sqrt_exc);
+ED_HD void phase_c(int lane, int s, const MfccTables &T, const uint32_t *x, uint32_t *row) {
+  const int rho = rev5(lane);
+  int m0[4], m2[4];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int v = 0; v < 4; v++) {
+    // positions 4j+k: (k = 0, 2) are adjacent words of the even half, (1, 3) of the odd half
+    const int a = 34 * (4 * rev2(v) + (rho >> 3)) + 4 * (rho & 7) + 2 * s;
+    const I2 ac = *reinterpret_cast<const I2 *>(x + a), bd = *reinterpret_cast<const I2 *>(x + kXchHalf + a);
+    const int ar = c_re((uint32_t)ac.x), ai = c_im((uint32_t)ac.x), cr = c_re((uint32_t)ac.y), ci = c_im((uint32_t)ac.y);
+    const int br = c_re((uint32_t)bd.x), bi = c_im((uint32_t)bd.x), dr = c_re((uint32_t)bd.y), di = c_im((uint32_t)bd.y);
+    const int Rr = qadd16<SAT>(ar, cr), Ri = qadd16<SAT>(ai, ci);
+    const int Sr = qsub16<SAT>(ar, cr), Si = qsub16<SAT>(ai, ci);
+    const int Tr = qadd16<SAT>(br, dr), Ti = qadd16<SAT>(bi, di);
+    const int Ur = qsub16<SAT>(br, dr), Ui = qsub16<SAT>(bi, di);
+    m0[v] = mag_q15((Rr + Tr) >> 1, (Ri + Ti) >> 1, T.sqrt_exc);
+    m2[v] = mag_q15((Sr + Ui) >> 1, (Si - Ur) >> 1, T.sqrt_exc);
+  }
+  const int w = lane + 32 * s;
+  row[w] = (uint32_t)(m0[0] & 255) | ((uint32_t)(m0[1] & 255) << 8) | ((uint32_t)(m0[2] & 255) << 16) | ((uint32_t)m0[3] << 24);
+  row[w + 64] = (uint32_t)(m2[0] & 255) | ((uint32_t)(m2[1] & 255) << 8) | ((uint32_t)(m2[2] & 255) << 16) | ((uint32_t)m2[3] << 24);
+  row[kSpectPlaneWords + w] = (uint32_t)(m0[0] >> 8) | ((uint32_t)(m0[1] >> 8) << 8) | ((uint32_t)(m0[2] >> 8) << 16) | ((uint32_t)(m0[3] >> 8) << 24);
+  row[kSpectPlaneWords + w + 64] = (uint32_t)(m2[0] >> 8) | ((uint32_t)(m2[1] >> 8) << 8) | ((uint32_t)(m2[2] >> 8) << 16) | ((uint32_t)(m2[3] >> 8) << 24);
 }
 
-// ---- mel: lane m owns filter m (audioprocessing.c:157-170) ---------------------------------------
-ED_HD int phase_mel(int lane, const MfccTables &T, const int *spect) {
-  const int start = T.mel_start[lane], cnt = T.mel_cnt[lane], off = T.mel_off[lane];
-  int acc = 0;
-  for (int i = 0; i < cnt; i++) acc += spect[start + i] * (int)T.mel_w[off + i];
-  return (int)(int16_t)(acc / 128);  // C '/' truncates toward zero; the cast wraps like (q15_t)
+// ---- mel filterbank (audioprocessing.c:157-170) as a u8 x u8 tensor-core contraction ---------------
+//   D[filter][frame] = sum_bin W[filter][bin] * S[bin][frame],  S = low-byte plane, then high-byte plane
+//   mel = (q15)( (D_lo + 256 D_hi) / 128 )        (operands >= 0, so '/' is a shift; the cast wraps)
+// m16n8k32 fragments (g = lane >> 2, t = lane & 3): A = T.mel_a[pair][lane]; B word b0 = bins 32ks+4t..+3,
+// b1 = bins 32ks+16+4t..+3 of frame g & 3 (columns 4..7 of the tile are never read back).
+ED_HD int mel_b_word(int lane, int ks, int plane, int half) {
+  return plane * kSpectPlaneWords + ((lane >> 2) & 3) * kSpectRowWords + 8 * ks + 4 * half + (lane & 3);
 }
+// accumulator element j (0..3) of tile mt -> filter, frame-in-half-group (valid when the frame is < 4)
+ED_HD int mel_c_filter(int lane, int mt, int j) { return 16 * mt + (lane >> 2) + 8 * (j >> 1); }
+ED_HD int mel_c_frame(int lane, int j) { return 2 * (lane & 3) + (j & 1); }
+ED_HD int mel_finish(int lo, int hi) { return (int)(int16_t)(((unsigned)lo + ((unsigned)hi << 8)) >> 7); }
 
 // ---- dct2_q15 over the 8 frames of a group, 4 lanes per frame ------------------------------------
 // mel: [8][32] ints; z: [8][16] (re, im); out: [8][32] ints (q15 values)

@@ -21,13 +21,12 @@ constexpr int kWarpsPerCta = 16;
 constexpr int kThreads = kWarpsPerCta * 32;
 
 struct WarpSmem {
-  int xr[kXchPlane];
-  int xi[kXchPlane];
-  int spect[512];
+  uint32_t x[kXchWords];        // exchange buffer (packed complex); doubles as DCT scratch at group end
+  uint32_t spect[kSpectWords];  // byte planes of the magnitude spectrum, 4 frames
   int mel[kGroup * 32];
 };
-// the DCT scratch (z: 8*16 I2 = 1 KiB, out: 8*32 int = 1 KiB) aliases xr, which is idle by then
-static_assert(sizeof(I2) * kGroup * 16 + sizeof(int) * kGroup * 32 <= sizeof(int) * kXchPlane, "dct scratch");
+// the DCT scratch (z: 8*16 I2 = 1 KiB, out: 8*32 int = 1 KiB) aliases x, which is idle by then
+static_assert(sizeof(I2) * kGroup * 16 + sizeof(int) * kGroup * 32 <= sizeof(uint32_t) * kXchWords, "dct scratch");
 
 struct CtaSmem {
   MfccTables T;
@@ -45,6 +44,54 @@ __device__ __forceinline__ uint32_t ld_nc_u16(const uint16_t *p) {
   return v;
 }
 
+// the 16 words of frame f this lane owns: w[q] = samples 64q + 2 lane, 64q + 2 lane + 1
+// ALIGNED: every frame starts on a 4-byte boundary (pcm 4-byte aligned, even clip stride); decided at launch
+template <bool ALIGNED>
+__device__ __forceinline__ void load_frame(const MfccLaunch &P, long long f, int lane, uint32_t (&w)[16]) {
+  const long long clip = f / P.frames_per_clip;
+  const int fic = (int)(f - clip * P.frames_per_clip);
+  const int16_t *frame = P.pcm + clip * P.clip_stride + (long long)fic * kFrameLen;
+  if (ALIGNED) {
+    const uint32_t *fw = reinterpret_cast<const uint32_t *>(frame);
+#pragma unroll
+    for (int q = 0; q < 16; q++) w[q] = ld_nc_u32(fw + 32 * q + lane);
+  } else {  // odd sample offset (clip stride not a multiple of 2 samples)
+    const uint16_t *fh = reinterpret_cast<const uint16_t *>(frame);
+#pragma unroll
+    for (int q = 0; q < 16; q++)
+      w[q] = ld_nc_u16(fh + 64 * q + 2 * lane) | (ld_nc_u16(fh + 64 * q + 2 * lane + 1) << 16);
+  }
+}
+
+__device__ __forceinline__ void mma_u8(int (&d)[4], const I4 &a, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
+               : "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b0), "r"(b1));
+}
+
+// mel filterbank of the 4 frames whose magnitude planes sit in `spect` -> mel[(4 half + frame) * 32 + filter]
+__device__ __forceinline__ void mel_mma(int lane, int half, const MfccTables &T, const uint32_t *spect, int *mel) {
+  int p = 0;
+#pragma unroll
+  for (int mt = 0; mt < 2; mt++) {
+    int lo[4] = {0, 0, 0, 0}, hi[4] = {0, 0, 0, 0};
+    const int pend = p + (mt == 0 ? T.mel_n0 : T.mel_n1);
+#pragma unroll 2
+    for (; p < pend; p++) {
+      const int ks = T.mel_ks[p];
+      const I4 a = T.mel_a[p][lane];
+      mma_u8(lo, a, spect[mel_b_word(lane, ks, 0, 0)], spect[mel_b_word(lane, ks, 0, 1)]);
+      mma_u8(hi, a, spect[mel_b_word(lane, ks, 1, 0)], spect[mel_b_word(lane, ks, 1, 1)]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int fr = mel_c_frame(lane, j);
+      if (fr < kSub) mel[(kSub * half + fr) * 32 + mel_c_filter(lane, mt, j)] = mel_finish(lo[j], hi[j]);
+    }
+  }
+}
+
+template <bool ALIGNED>
 __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   CtaSmem &S = *reinterpret_cast<CtaSmem *>(smem_raw);
@@ -62,51 +109,57 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   const long long warp_global = (long long)blockIdx.x * kWarpsPerCta + warp;
   const long long warp_stride = (long long)gridDim.x * kWarpsPerCta;
 
-  for (long long grp = warp_global; grp < n_groups; grp += warp_stride) {
+  uint32_t w[16];
+  if (warp_global < n_groups) load_frame<ALIGNED>(P, warp_global * kGroup, lane, w);
+  // All warps of the CTA start every frame together (one bar.sync per frame): with the 16 warps inside the
+  // same ~20 KB of code at any time the instruction cache holds the working set (profiles/r01: +4 %).
+  // Every warp therefore runs the same trip count; trips past the end of its work only hit the barrier.
+  const long long n_iter = (n_groups + warp_stride - 1) / warp_stride;
+  for (long long it = 0, grp = warp_global; it < n_iter; it++, grp += warp_stride) {
+#pragma unroll 1
     for (int g = 0; g < kGroup; g++) {
       const long long f = grp * kGroup + g;
-      if (f >= n_frames) {  // ragged tail: the group's unused rows are never stored
-        W.mel[32 * g + lane] = 0;
-        continue;
-      }
-      const long long clip = f / P.frames_per_clip;
-      const int fic = (int)(f - clip * P.frames_per_clip);
-      const int16_t *frame = P.pcm + clip * P.clip_stride + (long long)fic * kFrameLen;
-      uint32_t w[16];
-      if ((reinterpret_cast<uintptr_t>(frame) & 3u) == 0) {
-        const uint32_t *fw = reinterpret_cast<const uint32_t *>(frame);
-#pragma unroll
-        for (int q = 0; q < 16; q++) w[q] = ld_nc_u32(fw + 32 * q + lane);
-      } else {  // odd sample offset (clip stride not a multiple of 2 samples)
-        const uint16_t *fh = reinterpret_cast<const uint16_t *>(frame);
-#pragma unroll
-        for (int q = 0; q < 16; q++)
-          w[q] = ld_nc_u16(fh + 64 * q + 2 * lane) | (ld_nc_u16(fh + 64 * q + 2 * lane + 1) << 16);
-      }
-      const bool sat = __reduce_max_sync(0xffffffffu, lane_peak(w)) > kNoSatPeak;
+      const bool valid = f < n_frames;  // ragged tail: unused rows are computed from stale data and never stored
+      bool sat = false;
+      uint32_t *row = W.spect + (g & (kSub - 1)) * kSpectRowWords;
+      __syncthreads();
+      if (valid) {
+        sat = __reduce_max_sync(0xffffffffu, lane_peak(w)) > kNoSatPeak;
 #pragma unroll 1
-      for (int e = 0; e < 2; e++) phase_a(lane, e, w, T, W.xr, W.xi);
+        for (int e = 0; e < 2; e++) phase_a(lane, e, w, T, W.x);
+        // prefetch the next frame this warp will process; it lands while phases B, C and mel run
+        const long long fn = g + 1 < kGroup ? f + 1 : (grp + warp_stride) * kGroup;
+        if (fn < n_frames) load_frame<ALIGNED>(P, fn, lane, w);
+      }
       __syncwarp();
-      if (sat) {
+      if (valid) {
+        if (sat) {
 #pragma unroll 1
-        for (int e = 0; e < 2; e++) phase_b<true>(lane, e, T, W.xr, W.xi);
+          for (int e = 0; e < 2; e++) phase_b<true>(lane, e, T, W.x);
+        } else {
+#pragma unroll 1
+          for (int e = 0; e < 2; e++) phase_b<false>(lane, e, T, W.x);
+        }
+      }
+      __syncwarp();
+      if (valid) {
+        if (sat) {
+#pragma unroll 1
+          for (int s = 0; s < 2; s++) phase_c<true>(lane, s, T, W.x, row);
+        } else {
+#pragma unroll 1
+          for (int s = 0; s < 2; s++) phase_c<false>(lane, s, T, W.x, row);
+        }
+      }
+      __syncwarp();
+      if ((g & (kSub - 1)) == kSub - 1) {
+        mel_mma(lane, g / kSub, T, W.spect, W.mel);
         __syncwarp();
-#pragma unroll 1
-        for (int i = 0; i < 8; i++) phase_c<true>(lane, i, T, W.xr, W.xi, W.spect);
-      } else {
-#pragma unroll 1
-        for (int e = 0; e < 2; e++) phase_b<false>(lane, e, T, W.xr, W.xi);
-        __syncwarp();
-#pragma unroll 1
-        for (int i = 0; i < 8; i++) phase_c<false>(lane, i, T, W.xr, W.xi, W.spect);
       }
-      __syncwarp();
-      W.mel[32 * g + lane] = phase_mel(lane, T, W.spect);
-      __syncwarp();
     }
     // dct2_q15 for the 8 frames of the group, 4 lanes per frame
-    I2 *z = reinterpret_cast<I2 *>(W.xr);
-    int *out = W.xr + 2 * kGroup * 16;
+    I2 *z = reinterpret_cast<I2 *>(W.x);
+    int *out = reinterpret_cast<int *>(W.x) + 2 * kGroup * 16;
     dct_stage1(lane, T, W.mel, z);
     __syncwarp();
     dct_stage2(lane, z);
@@ -138,7 +191,9 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
 }
 
 cudaError_t mfcc_q15_configure(void) {
-  return cudaFuncSetAttribute(mfcc_q15_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
+  cudaError_t e = cudaFuncSetAttribute(mfcc_q15_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(mfcc_q15_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
 }
 
 cudaError_t launch_mfcc_q15(const MfccLaunch &p, int sm_count, cudaStream_t stream) {
@@ -147,7 +202,9 @@ cudaError_t launch_mfcc_q15(const MfccLaunch &p, int sm_count, cudaStream_t stre
   const long long n_groups = (n_frames + kGroup - 1) / kGroup;
   long long ctas = (n_groups + kWarpsPerCta - 1) / kWarpsPerCta;
   if (ctas > sm_count) ctas = sm_count;
-  mfcc_q15_kernel<<<(unsigned)ctas, kThreads, sizeof(CtaSmem), stream>>>(p);
+  const bool aligned = (reinterpret_cast<uintptr_t>(p.pcm) & 3u) == 0 && (p.clip_stride & 1) == 0;
+  if (aligned) mfcc_q15_kernel<true><<<(unsigned)ctas, kThreads, sizeof(CtaSmem), stream>>>(p);
+  else mfcc_q15_kernel<false><<<(unsigned)ctas, kThreads, sizeof(CtaSmem), stream>>>(p);
   count_launch();
   return cudaGetLastError();
 }

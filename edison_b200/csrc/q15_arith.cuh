@@ -27,22 +27,54 @@ ED_HD int imax(int a, int b) { return a > b ? a : b; }
 // QADD16 / QSUB16 on one lane (arm_math.h:1368-1697 host emulations; ARMv7-M ARM A7.7.107).
 // SAT=false is used where interval analysis proves that saturation cannot trigger.
 template <bool SAT> ED_HD int qadd16(int a, int b) {
+#if defined(__CUDA_ARCH__)
+  if (SAT) return min(__viaddmax_s32(a, b, -32768), 32767);  // VIADDMNMX + VIMNMX
+  return a + b;
+#else
   int s = a + b;
   if (SAT) s = imin(imax(s, -32768), 32767);
   return s;
+#endif
 }
 template <bool SAT> ED_HD int qsub16(int a, int b) {
+#if defined(__CUDA_ARCH__)
+  if (SAT) return min(__viaddmax_s32(a, -b, -32768), 32767);
+  return a - b;
+#else
   int s = a - b;
   if (SAT) s = imin(imax(s, -32768), 32767);
   return s;
+#endif
 }
 
 // Complex multiply by a q15 twiddle the way the SIMD branch does it
 // (arm_cfft_radix4_q15.c:252-256):  re' = SMUAD(C, V) >> 16,  im' = SMUSDX(C, V) >> 16.
 // |co*re + si*im| <= 32768 * 65535 < 2^31, so plain int arithmetic never wraps.
+// The shift is issued as IMAD.HI (x * 65536 >> 32) on the device: the kernel is bound by the ALU pipe
+// (shifts, logic, min/max), the FMA pipe has room, and both give floor(x / 65536).
+ED_HD int asr16(int x) {
+#if defined(__CUDA_ARCH__)
+  return __mulhi(x, 65536);
+#else
+  return x >> 16;
+#endif
+}
 ED_HD void tw_mul(int co, int si, int re, int im, int &ore, int &oim) {
-  ore = (co * re + si * im) >> 16;
-  oim = (co * im - si * re) >> 16;
+  ore = asr16(co * re + si * im);
+  oim = asr16(co * im - si * re);
+}
+// the same without the final shift: X = co*re + si*im, Y = co*im - si*re; pack_hi(X, Y) packs
+// (X >> 16, Y >> 16) into one word with a single byte permute
+ED_HD void tw_mul_raw(int co, int si, int re, int im, int &X, int &Y) {
+  X = co * re + si * im;
+  Y = co * im - si * re;
+}
+ED_HD uint32_t pack_hi(int X, int Y) {
+#if defined(__CUDA_ARCH__)
+  return __byte_perm((uint32_t)X, (uint32_t)Y, 0x7632);
+#else
+  return (((uint32_t)X >> 16) & 0xffffu) | ((uint32_t)Y & 0xffff0000u);
+#endif
 }
 
 // One radix-4 DIF butterfly of a MIDDLE stage (arm_cfft_radix4_q15.c:333-479).
@@ -59,6 +91,22 @@ ED_HD void bfly_mid(int &ar, int &ai, int &br, int &bi, int &cr, int &ci, int &d
   tw_mul(w2.x, w2.y, (Rr - Tr) >> 1, (Ri - Ti) >> 1, br, bi);  // SHSUB16 :378
   tw_mul(w1.x, w1.y, (Sr + Ui) >> 1, (Si - Ur) >> 1, cr, ci);  // SHSAX :415
   tw_mul(w3.x, w3.y, (Sr - Ui) >> 1, (Si + Ur) >> 1, dr, di);  // SHASX :412
+}
+
+// bfly_mid whose three twiddled outputs are left unshifted (for the last stage of a phase, where they
+// go straight to shared memory through pack_hi)
+template <bool SAT>
+ED_HD void bfly_mid_raw(int &ar, int &ai, int &bX, int &bY, int &cX, int &cY, int &dX, int &dY, I2 w1, I2 w2, I2 w3) {
+  const int br = bX, bi = bY, cr = cX, ci = cY, dr = dX, di = dY;
+  int Rr = qadd16<SAT>(ar, cr), Ri = qadd16<SAT>(ai, ci);
+  int Sr = qsub16<SAT>(ar, cr), Si = qsub16<SAT>(ai, ci);
+  int Tr = qadd16<SAT>(br, dr), Ti = qadd16<SAT>(bi, di);
+  int Ur = qsub16<SAT>(br, dr), Ui = qsub16<SAT>(bi, di);
+  ar = (Rr + Tr) >> 2;
+  ai = (Ri + Ti) >> 2;
+  tw_mul_raw(w2.x, w2.y, (Rr - Tr) >> 1, (Ri - Ti) >> 1, bX, bY);
+  tw_mul_raw(w1.x, w1.y, (Sr + Ui) >> 1, (Si - Ur) >> 1, cX, cY);
+  tw_mul_raw(w3.x, w3.y, (Sr - Ui) >> 1, (Si + Ur) >> 1, dX, dY);
 }
 
 // FIRST stage (arm_cfft_radix4_q15.c:192-330): inputs >>2, sums not halved except x[i0].

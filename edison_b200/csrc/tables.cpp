@@ -87,17 +87,48 @@ int build_mfcc_tables(MfccTables *Tp, const char *mel_blob_path, char *err, size
   if (fread(hdr, 1, 24, fh) != 24 || memcmp(hdr, "EDMELQ15", 8)) { fclose(fh); snprintf(err, errlen, "%s: bad header", mel_blob_path); return EDISON_E_DATA; }
   memcpy(v, hdr + 8, 16);
   if (v[0] != 1 || v[1] != (uint32_t)kNMel || v[2] > (uint32_t)kMelMaxW || v[3] != 128) { fclose(fh); snprintf(err, errlen, "%s: unsupported mel table", mel_blob_path); return EDISON_E_DATA; }
-  bool ok = fread(T.mel_start, 2, kNMel, fh) == (size_t)kNMel && fread(T.mel_cnt, 2, kNMel, fh) == (size_t)kNMel &&
-            fread(T.mel_w, 2, v[2], fh) == v[2];
+  static int16_t mel_start[kNMel], mel_cnt[kNMel], mel_w[kMelMaxW];
+  bool ok = fread(mel_start, 2, kNMel, fh) == (size_t)kNMel && fread(mel_cnt, 2, kNMel, fh) == (size_t)kNMel &&
+            fread(mel_w, 2, v[2], fh) == v[2];
   fclose(fh);
   if (!ok) { snprintf(err, errlen, "%s: truncated", mel_blob_path); return EDISON_E_DATA; }
+  // dense [filter][bin] u8 matrix from the compact form, then the non-zero (16 filters x 32 bins) tiles as
+  // mma.m16n8k32 A fragments: lane (g, t) holds a0 = W[16mt+g][32ks+4t..+3], a1 = W[16mt+g+8][same],
+  // a2 = W[16mt+g][32ks+16+4t..+3], a3 = W[16mt+g+8][same]
+  static uint8_t dense[kNMel][512];
+  memset(dense, 0, sizeof dense);
   int off = 0;
   for (int m = 0; m < kNMel; m++) {
-    T.mel_off[m] = (int16_t)off;
-    if (T.mel_start[m] < 0 || T.mel_cnt[m] < 0 || T.mel_start[m] + T.mel_cnt[m] > 512) { snprintf(err, errlen, "mel filter %d reaches past bin 511", m); return EDISON_E_DATA; }
-    off += T.mel_cnt[m];
+    if (mel_start[m] < 0 || mel_cnt[m] < 0 || mel_start[m] + mel_cnt[m] > 512) { snprintf(err, errlen, "mel filter %d reaches past bin 511", m); return EDISON_E_DATA; }
+    for (int i = 0; i < mel_cnt[m]; i++) {
+      const int wv = mel_w[off + i];
+      if (wv < 0 || wv > 255) { snprintf(err, errlen, "mel weight %d of filter %d does not fit u8", wv, m); return EDISON_E_DATA; }
+      dense[m][mel_start[m] + i] = (uint8_t)wv;
+    }
+    off += mel_cnt[m];
   }
   if (off != (int)v[2]) { snprintf(err, errlen, "mel counts do not sum to the weight count"); return EDISON_E_DATA; }
+  int np = 0;
+  T.mel_n0 = T.mel_n1 = 0;
+  for (int mt = 0; mt < 2; mt++)
+    for (int ks = 0; ks < 16; ks++) {
+      bool any = false;
+      for (int m = 0; m < 16 && !any; m++)
+        for (int k = 0; k < 32; k++) any |= dense[16 * mt + m][32 * ks + k] != 0;
+      if (!any) continue;
+      for (int lane = 0; lane < 32; lane++) {
+        const int g = lane >> 2, t = lane & 3;
+        auto word = [&](int row, int k0) {
+          uint32_t w = 0;
+          for (int i = 0; i < 4; i++) w |= (uint32_t)dense[16 * mt + row][32 * ks + k0 + i] << (8 * i);
+          return (int)w;
+        };
+        T.mel_a[np][lane] = I4{word(g, 4 * t), word(g + 8, 4 * t), word(g, 16 + 4 * t), word(g + 8, 16 + 4 * t)};
+      }
+      T.mel_ks[np] = (uint8_t)ks;
+      (mt == 0 ? T.mel_n0 : T.mel_n1)++;
+      np++;
+    }
   T.in_scale = 1; T.in_min = -128; T.in_max = 127;  // overwritten from the model blob's trailer
   return EDISON_OK;
 }
