@@ -17,7 +17,7 @@
 
 namespace edison {
 
-constexpr int kWarpsPerCta = 16;
+constexpr int kWarpsPerCta = 20;
 constexpr int kThreads = kWarpsPerCta * 32;
 
 struct WarpSmem {
