@@ -28,6 +28,10 @@ CFG2_CLIPS, CFG2_FPC, CFG2_STRIDE = 65536, 15, 16000
 E2E_CLIPS = 32768               # host-buffer leg: 2.08 GB of pinned PCM per step
 CLIP = 31 * 1024
 K1_BYTES_PER_FRAME = 2048 + 13  # algorithmic: PCM read + int8 net-input row written
+N_STREAMS = 100000              # config #5
+# dram__bytes_read.sum + dram__bytes_write.sum of one mfcc_q15_kernel launch over 131,072 x 31 frames, from the ncu
+# --set full capture summarised in profiles/ (8.32 GB read + 10 MB written): no re-reads.
+K1_NCU_DRAM_BYTES = 8.33e9
 
 
 def peaks():
@@ -39,33 +43,56 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons while the timed region runs"""
+    """SM clock and throttle reasons while the timed region runs (NVML every 5 ms; nvidia-smi as a fallback)"""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.mhz, self.reasons, self.max_mhz, self.stop_flag = index, [], set(), None, False
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
 
     def run(self):
+        n = self.nvml
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                if n:
+                    self.mhz.append(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM))
+                    r = n.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(n, "nvmlDeviceGetCurrentClocksEventReasons") \
+                        else n.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    for name, bit in (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("sw_thermal_slowdown", 0x20),
+                                      ("hw_thermal_slowdown", 0x40)):
+                        if r & bit:
+                            self.reasons.add(name)
+                    time.sleep(0.005)
+                else:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout.strip()
+                    c = [v.strip() for v in out.split(",")]
+                    if c and c[0].isdigit():
+                        self.mhz.append(int(c[0]))
+                        self.max_mhz = int(c[1])
+                        for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], c[2:6]):
+                            if v.lower().startswith("active"):
+                                self.reasons.add(name)
+                    time.sleep(0.05)
             except Exception:
-                pass
-            time.sleep(0.1)
+                time.sleep(0.05)
 
     def summary(self):
         self.stop_flag = True
         self.join(timeout=6)
-        mhz = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
-        mx = max((int(r[1]) for r in self.rows if r[1].isdigit()), default=None)
-        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(mhz)}
+        m = sorted(self.mhz)
+        return {"sm_mhz": m[len(m) // 2] if m else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(m), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
 def synth_clips_gpu(torch, n_clips, stride, seed, dev):
@@ -122,6 +149,7 @@ def run_reference(args, rank, world):
 def run_ours(args, rank, world, local_rank):
     import torch
     import edison_b200 as ed
+    from edison_b200 import shard
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     dist = None
@@ -152,9 +180,7 @@ def run_ours(args, rank, world, local_rank):
         if ev: ev[2].record(st)
         if world > 1:  # the path's only exchange: final gather of logits + class counts
             dist.all_gather_into_tensor(gathered, logits)
-            c = torch.bincount(logits.argmax(dim=1), minlength=10)
-            dist.all_reduce(c)
-            counts.copy_(c)
+            counts.copy_(shard.class_counts(dist, logits))
 
     def barrier():
         torch.cuda.synchronize()
@@ -222,6 +248,32 @@ def run_ours(args, rank, world, local_rank):
     e2e_val = world * ne / e2e_s
     same = bool((h_logits.to(dev) == logits[:ne]).all().item())
 
+    # ---- streaming (config #5): N_STREAMS concurrent streams, one hop = 1024 new samples per stream, device resident.
+    # Hop latency = K1 (one frame per stream) + window push + K2 (full window per stream) + filter/argmax.
+    stream_stats = None
+    if world == 1:
+        ns = N_STREAMS
+        d_sm = torch.empty(ns, 10, dtype=torch.int8, device=dev)
+        d_fl = torch.empty(ns, 10, dtype=torch.float32, device=dev)
+        d_dt = torch.empty(ns, dtype=torch.int32, device=dev)
+        with ed.Streams(ns) as ss:
+            hop = lambda h: chk(L.edison_streams_push_hop_dev(ss.handle, P(pcm[(h % 36) * ns * 1024:]), P(d_sm), P(d_fl), P(d_dt), sp))
+            for h in range(34):   # fill the 31-row windows, then two full hops as warm-up
+                hop(h)
+            torch.cuda.synchronize()
+            n_hops = 200
+            hev = [torch.cuda.Event(enable_timing=True) for _ in range(n_hops + 1)]
+            hev[0].record(st)
+            for h in range(n_hops):
+                hop(34 + h)
+                hev[h + 1].record(st)
+            torch.cuda.synchronize()
+            lat = sorted(hev[i].elapsed_time(hev[i + 1]) for i in range(n_hops))
+            p50, p99 = lat[n_hops // 2], lat[min(n_hops - 1, int(n_hops * 0.99))]
+            stream_stats = {"workload": "config#5: %d concurrent streams, hop 1024 samples (64 ms), window 31 rows, device resident" % ns,
+                            "hop_ms_p50": p50, "hop_ms_p99": p99, "hops_timed": n_hops,
+                            "stream_hops_per_s": ns / (p50 / 1e3), "realtime_streams_per_gpu": int(ns * 64.0 / p99)}
+
     if rank == 0:
         peak, peak_kind = peaks()
         k1_bytes = n * 31 * K1_BYTES_PER_FRAME
@@ -237,10 +289,12 @@ def run_ours(args, rank, world, local_rank):
                 "cfg2_mfcc": {"workload": "config#2: 65,536 x 1 s clips (15 frames each), q15 MFCC only, 1 GPU",
                               "frames_per_s": cfg2_fps, "clips_per_s": CFG2_CLIPS / (cfg2_ms / 1e3), "ms": cfg2_ms},
                 "roofline": {"kernel": "mfcc_q15_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": None, "bytes_per_launch": k1_bytes},
+                             "frac": achieved / peak, "traffic": K1_NCU_DRAM_BYTES * (k1_bytes / (131072 * 31 * K1_BYTES_PER_FRAME)), "bytes_per_launch": k1_bytes},
                 "e2e": {"value": e2e_val, "unit": "clips/s", "h2d_bytes_per_step": ne * CLIP * 2, "d2h_bytes_per_step": ne * 20,
                         "clips_per_step": ne, "matches_device_path": same},
                 "gpu_launches": int(launches), "clocks": clocks}
+        if stream_stats:
+            line["streaming"] = stream_stats
         if world == 1 and not args.no_cpu:
             sys.path.insert(0, os.path.join(ROOT, "oracle"))
             import cpu_baseline
@@ -255,7 +309,7 @@ def run_ours(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

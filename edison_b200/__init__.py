@@ -16,6 +16,7 @@ from .capi import (  # noqa: F401
     SOFTMAX_CMSIS_REF,
     SOFTMAX_CMSIS_SIMD,
     SOFTMAX_NNOM_LOCAL,
+    Streams,
     infer_q7_batch,
     init,
     kws_batch,

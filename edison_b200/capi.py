@@ -48,6 +48,14 @@ def lib():
         L.edison_infer_q7_batch_dev.argtypes = [vp, sz, vp, vp, vp]
         L.edison_kws_batch_dev.argtypes = [vp, sz, sz, vp, vp, vp, vp]
         L.edison_sync.argtypes = [vp]
+        L.edison_streams_open.argtypes = [sz, ctypes.POINTER(vp)]
+        L.edison_streams_close.argtypes = [vp]
+        L.edison_streams_close.restype = None
+        L.edison_streams_push_hop.argtypes = [vp, vp, vp, vp, vp]
+        L.edison_streams_push_hop_dev.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.edison_streams_hops.argtypes = [vp]
+        L.edison_streams_hops.restype = ctypes.c_ulonglong
+        L.edison_streams_window.argtypes = [vp, sz, vp]
         L.edison_debug_sqrt_q31.argtypes = [vp, sz, vp]
         L.edison_debug_mag_sweep.argtypes = [ctypes.c_uint32, ctypes.c_uint32, vp, vp]
         L.edison_set_softmax_mode.argtypes = [ci]
@@ -130,3 +138,48 @@ def infer_q7_batch(net_in, want_softmax=True):
     sm = np.empty((n, N_CLASSES), dtype=np.int8) if want_softmax else None
     check(lib().edison_infer_q7_batch(_p(net_in), n, _p(lg), _p(sm)), "edison_infer_q7_batch")
     return lg, sm
+
+
+class Streams:
+    """n concurrent keyword-spotting streams (appMicMfccInfereContinuous, firmware/src/app.c:288-394).
+    push_hop(pcm[n,1024]) -> (softmax int8 [n,10], filt float32 [n,10], detect int32 [n]); detect is the class index when
+    the filtered maximum exceeds 0.5, -1 when it does not, -2 while the 31-row window is still filling."""
+
+    def __init__(self, n):
+        self.n = int(n)
+        self._h = ctypes.c_void_p()
+        check(lib().edison_streams_open(self.n, ctypes.byref(self._h)), "edison_streams_open")
+
+    def close(self):
+        if self._h:
+            lib().edison_streams_close(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    @property
+    def handle(self):
+        return self._h
+
+    @property
+    def hops(self):
+        return int(lib().edison_streams_hops(self._h))
+
+    def push_hop(self, pcm):
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
+        if pcm.size != self.n * FRAME_LEN:
+            raise ValueError("a hop is %d x 1024 samples, got %d" % (self.n, pcm.size))
+        sm = np.empty((self.n, N_CLASSES), dtype=np.int8)
+        fl = np.empty((self.n, N_CLASSES), dtype=np.float32)
+        dt = np.empty(self.n, dtype=np.int32)
+        check(lib().edison_streams_push_hop(self._h, _p(pcm), _p(sm), _p(fl), _p(dt)), "edison_streams_push_hop")
+        return sm, fl, dt
+
+    def window(self, i):
+        w = np.empty(NET_IN, dtype=np.int8)
+        check(lib().edison_streams_window(self._h, i, _p(w)), "edison_streams_window")
+        return w.reshape(N_FRAMES, N_COEFF)

@@ -252,6 +252,28 @@ static int infer_host_chunks(const int8_t *net_in, size_t n, int8_t *logits, int
   return EDISON_OK;
 }
 
+int ctx_fail(int code, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(t_err, sizeof t_err, fmt, ap);
+  va_end(ap);
+  return code;
+}
+void ctx_lock(void) { g_mu.lock(); }
+void ctx_unlock(void) { g_mu.unlock(); }
+int ctx_acquire(CtxView *out) {  // caller holds ctx_lock()
+  if (!g.ready) {
+    int r = do_init(nullptr);
+    if (r) return r;
+  }
+  out->tables = g.d_tables;
+  out->model = g.d_model;
+  out->sm_count = g.sm_count;
+  out->softmax_mode = g.softmax_mode;
+  out->stream = g.slot[0].stream;
+  return EDISON_OK;
+}
+
 }  // namespace edison
 
 using namespace edison;

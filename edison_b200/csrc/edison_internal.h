@@ -40,4 +40,17 @@ cudaError_t launch_debug_mag_sweep(uint32_t lo, uint32_t hi, const uint32_t *d_e
 
 void count_launch(void);
 
+// ---- shared context (edison_api.cu) for the other translation units of the C ABI ----------------------
+struct CtxView {
+  const MfccTables *tables;   // device
+  const NnomModel *model;     // device
+  int sm_count;
+  int softmax_mode;
+  cudaStream_t stream;        // the library's default stream
+};
+int ctx_acquire(CtxView *out);                     // initialises the library on first use; EDISON_OK or an error code
+int ctx_fail(int code, const char *fmt, ...);      // records the thread's last-error text, returns code
+void ctx_lock(void);
+void ctx_unlock(void);
+
 }  // namespace edison

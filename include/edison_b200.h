@@ -120,6 +120,26 @@ int edison_kws_batch_dev(const int16_t *d_pcm, size_t n_clips, size_t clip_strid
                          int8_t *d_logits, int8_t *d_softmax, int8_t *d_net_in, void *stream);
 int edison_sync(void *stream);
 
+/* ---- section 3b: continuous streaming (appMicMfccInfereContinuous, firmware/src/app.c:288-394, and its ISR
+ *      appAudioEvent app.c:635-661) over n concurrent streams pinned to this GPU.  Per hop of 1024 new samples
+ *      per stream: one MFCC row, mfccToNetInputPush (window of 31 rows shifts up by one), one full inference,
+ *      netOutFilt = 0.9 netOutFilt + (1.0 - 0.9) out (double arithmetic, stored as float; app.c:35-39, 342),
+ *      argmax (arm_max_f32: first maximum), "spotted" when the maximum exceeds 0.5 (app.c:34, 344-350).
+ *      Like the firmware, inference and the filter start once the window has been filled and one more hop
+ *      has arrived (hop count >= 32); before that detect[] is -2 and filt[] stays 0. ------------------------ */
+typedef struct edison_streams edison_streams;
+int edison_streams_open(size_t n_streams, edison_streams **out);
+void edison_streams_close(edison_streams *s);
+/* hop_pcm[n_streams][1024] host or device.  Outputs (host or device like hop_pcm, any may be NULL):
+ * softmax[n][10] int8, filt[n][10] float, detect[n] int32 = class index if spotted, -1 if not, -2 while filling. */
+int edison_streams_push_hop(edison_streams *s, const int16_t *hop_pcm, int8_t *softmax, float *filt, int32_t *detect);
+/* device pointers + stream, asynchronous */
+int edison_streams_push_hop_dev(edison_streams *s, const int16_t *d_hop_pcm, int8_t *d_softmax, float *d_filt,
+                                int32_t *d_detect, void *stream);
+unsigned long long edison_streams_hops(const edison_streams *s);
+/* copy one stream's 31x13 window (netInput, app.c:71-93) to the host, for inspection */
+int edison_streams_window(edison_streams *s, size_t stream_index, int8_t *window403);
+
 /* ---- section 4: self-checks used by the tests (device arithmetic against itself) ------------- */
 /* arm_sqrt_q31 (arm_sqrt_q31.c:50-135) evaluated on the device for n host values */
 int edison_debug_sqrt_q31(const int32_t *in, size_t n, int32_t *out);

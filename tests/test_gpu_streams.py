@@ -1,0 +1,75 @@
+"""Streaming scheduler (include/edison_b200.h section 3b) against a simulation of the firmware loop
+(appAudioEvent app.c:635-661 + appMicMfccInfereContinuous app.c:288-394) built from the oracle's pieces."""
+import numpy as np
+import pytest
+
+from common import synth_frames
+
+pytestmark = pytest.mark.gpu
+
+
+def simulate(oracle, pcm_hops, mode=0):
+    """pcm_hops: int16 [hops, n, 1024].  Returns per hop (softmax, filt, detect) as the firmware would compute them."""
+    hops, n, _ = pcm_hops.shape
+    window = np.zeros((n, 31, 13), dtype=np.int8)
+    filt = np.zeros((n, 10), dtype=np.float32)
+    sm = np.zeros((n, 10), dtype=np.int8)
+    out = []
+    for h in range(hops):
+        rows = oracle.net_input(oracle.mfcc(pcm_hops[h]))          # audioCalcMFCCs + clip to int8
+        window[:, :-1] = window[:, 1:].copy()                      # mfccToNetInputPush
+        window[:, -1] = rows
+        if h + 1 > 31:
+            _, sm = oracle.forward(window.reshape(n, 403), mode)
+            # double arithmetic with the double literals 0.9 and (1.0 - 0.9), stored to float (app.c:35-39, 342)
+            filt = (0.9 * filt.astype(np.float64) + (1.0 - 0.9) * sm.astype(np.float32).astype(np.float64)).astype(np.float32)
+            idx = np.argmax(filt, axis=1)                          # arm_max_f32: first maximum, like np.argmax
+            det = np.where(filt[np.arange(n), idx] > np.float32(0.5), idx, -1).astype(np.int32)
+        else:
+            det = np.full(n, -2, dtype=np.int32)
+        out.append((sm.copy(), filt.copy(), det, window.copy()))
+    return out
+
+
+@pytest.mark.parametrize("n", [1, 37])
+def test_streams_vs_firmware_loop(edison, oracle, n):
+    hops = 40
+    pcm = synth_frames(hops * n, seed=77).reshape(hops, n, 1024)
+    want = simulate(oracle, pcm)
+    with edison.Streams(n) as st:
+        for h in range(hops):
+            sm, fl, dt = st.push_hop(pcm[h])
+            w_sm, w_fl, w_dt, w_win = want[h]
+            assert np.array_equal(dt, w_dt), "detect, hop %d" % h
+            if h + 1 > 31:
+                assert np.array_equal(sm, w_sm), "softmax, hop %d" % h
+            assert np.array_equal(fl.view(np.uint32), w_fl.view(np.uint32)), "filter bits, hop %d" % h
+            if h in (0, 12, 30, 31, 39):
+                for i in (0, n - 1):
+                    assert np.array_equal(st.window(i), w_win[i]), "window, hop %d stream %d" % (h, i)
+        assert st.hops == hops
+
+
+def test_streams_detects_when_softmax_saturates(edison, oracle):
+    """Feed the same loud frame for many hops: the filter converges to the softmax output, so some class crosses 0.5
+    exactly when the simulation says so (exercises the detect >= 0 branch)."""
+    n, hops = 4, 80
+    one = synth_frames(n, seed=5)
+    pcm = np.broadcast_to(one, (hops, n, 1024)).copy()
+    want = simulate(oracle, pcm)
+    seen = False
+    with edison.Streams(n) as st:
+        for h in range(hops):
+            _, fl, dt = st.push_hop(pcm[h])
+            assert np.array_equal(dt, want[h][2])
+            assert np.array_equal(fl.view(np.uint32), want[h][1].view(np.uint32))
+            seen = seen or bool((dt >= 0).any())
+    assert seen, "test input never crossed the threshold; pick another seed"
+
+
+def test_streams_bad_arguments(edison):
+    import ctypes
+    L = edison.lib()
+    h = ctypes.c_void_p()
+    assert L.edison_streams_open(0, ctypes.byref(h)) == -1
+    assert L.edison_streams_push_hop(None, None, None, None, None) == -1
