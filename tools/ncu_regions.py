@@ -7,7 +7,12 @@ rep, units = sys.argv[1], float(sys.argv[2])
 thr = float(sys.argv[3]) if len(sys.argv) > 3 else 5
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
-hdr, data = rows[1], rows[2:]
+hdr, data = rows[1], []
+for r in rows[2:]:   # first kernel of the report only
+    if r and r[0] == 'Kernel Name':
+        break
+    if len(r) == len(hdr):
+        data.append(r)
 iA, iS, iSrc = hdr.index('Instructions Executed'), hdr.index('# Samples'), hdr.index('Source')
 groups, cur = [], None
 for k, r in enumerate(data):
