@@ -228,6 +228,24 @@ def run_ours(args, rank, world, local_rank):
     cfg2_ms = a.elapsed_time(b) / args.steps
     cfg2_fps = CFG2_CLIPS * CFG2_FPC / (cfg2_ms / 1e3)
 
+    # ---- float MFCC (K3; config #1's arithmetic at config #2's size), device resident: fp64 parity kernel and fp32 fast kernel
+    float_stats = {}
+    for name, fn, tdt in (("f64", L.edison_mfcc_f64_clips_dev, torch.float64), ("f32", L.edison_mfcc_f32_clips_dev, torch.float32)):
+        outf = torch.empty(CFG2_CLIPS * CFG2_FPC, 32, dtype=tdt, device=dev)
+        for _ in range(3):
+            chk(fn(P(pcm2), CFG2_CLIPS, CFG2_FPC, CFG2_STRIDE, P(outf), 0, sp))
+        torch.cuda.synchronize()
+        a.record(st)
+        for _ in range(args.steps):
+            chk(fn(P(pcm2), CFG2_CLIPS, CFG2_FPC, CFG2_STRIDE, P(outf), 0, sp))
+        b.record(st)
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / args.steps
+        nfr = CFG2_CLIPS * CFG2_FPC
+        float_stats[name] = {"frames_per_s": nfr / (ms / 1e3), "ms": ms,
+                             "hbm_gbs": nfr * (2048 + 32 * outf.element_size()) / (ms / 1e3) / 1e9}
+        del outf
+
     # ---- e2e: edison_kws_batch() on pinned HOST buffers, H2D + D2H inside the timed region
     ne = E2E_CLIPS
     h_pcm = torch.empty(ne * CLIP, dtype=torch.int16).pin_memory()
@@ -295,6 +313,7 @@ def run_ours(args, rank, world, local_rank):
                 "gpu_launches": int(launches), "clocks": clocks}
         if stream_stats:
             line["streaming"] = stream_stats
+        line["float_mfcc"] = dict(float_stats, workload="mfcc_utils.mfcc arithmetic on 65,536 x 1 s clips (15 frames each), 1 GPU")
         if world == 1 and not args.no_cpu:
             sys.path.insert(0, os.path.join(ROOT, "oracle"))
             import cpu_baseline

@@ -11,6 +11,9 @@ from .capi import (  # noqa: F401
     N_CLASSES,
     N_COEFF,
     N_FRAMES,
+    MFCC_F32_HOST,
+    MFCC_F32_MCU,
+    MFCC_F32_MCU_LOG,
     N_MEL,
     NET_IN,
     SOFTMAX_CMSIS_REF,
@@ -23,6 +26,8 @@ from .capi import (  # noqa: F401
     launch_count,
     lib,
     lib_path,
+    mfcc_float_batch,
+    mfcc_float_clips,
     mfcc_q15_batch,
     mfcc_q15_clips,
     set_softmax_mode,

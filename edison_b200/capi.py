@@ -7,6 +7,7 @@ import numpy as np
 FRAME_LEN, N_MEL, N_COEFF, N_FRAMES, N_CLASSES = 1024, 32, 13, 31, 10
 NET_IN = N_FRAMES * N_COEFF
 SOFTMAX_CMSIS_REF, SOFTMAX_CMSIS_SIMD, SOFTMAX_NNOM_LOCAL = 0, 1, 2
+MFCC_F32_HOST, MFCC_F32_MCU, MFCC_F32_MCU_LOG = 0, 1, 2
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _lib = None
@@ -48,6 +49,10 @@ def lib():
         L.edison_infer_q7_batch_dev.argtypes = [vp, sz, vp, vp, vp]
         L.edison_kws_batch_dev.argtypes = [vp, sz, sz, vp, vp, vp, vp]
         L.edison_sync.argtypes = [vp]
+        for t in ("f32", "f64"):
+            getattr(L, "edison_mfcc_%s_batch" % t).argtypes = [vp, sz, vp, ci]
+            getattr(L, "edison_mfcc_%s_clips" % t).argtypes = [vp, sz, sz, sz, vp, ci]
+            getattr(L, "edison_mfcc_%s_clips_dev" % t).argtypes = [vp, sz, sz, sz, vp, ci, vp]
         L.edison_streams_open.argtypes = [sz, ctypes.POINTER(vp)]
         L.edison_streams_close.argtypes = [vp]
         L.edison_streams_close.restype = None
@@ -138,6 +143,29 @@ def infer_q7_batch(net_in, want_softmax=True):
     sm = np.empty((n, N_CLASSES), dtype=np.int8) if want_softmax else None
     check(lib().edison_infer_q7_batch(_p(net_in), n, _p(lg), _p(sm)), "edison_infer_q7_batch")
     return lg, sm
+
+
+def mfcc_float_clips(pcm, n_clips, frames_per_clip, clip_stride, mode=MFCC_F32_HOST, dtype=np.float64):
+    """float MFCC (mfcc_utils.mfcc / mfcc_mcu of the reference) -> [n_clips*frames_per_clip, 32].
+    dtype float64 = the fp64 parity kernel (numpy-equivalent), float32 = the fp32 fast kernel."""
+    pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
+    need = (n_clips - 1) * clip_stride + frames_per_clip * FRAME_LEN if n_clips and frames_per_clip else 0
+    if pcm.size < need:
+        raise ValueError("pcm holds %d samples, need %d" % (pcm.size, need))
+    dtype = np.dtype(dtype)
+    if dtype not in (np.dtype(np.float32), np.dtype(np.float64)):
+        raise ValueError("dtype must be float32 or float64")
+    out = np.empty((n_clips * frames_per_clip, N_MEL), dtype=dtype)
+    fn = lib().edison_mfcc_f64_clips if dtype == np.float64 else lib().edison_mfcc_f32_clips
+    check(fn(_p(pcm), n_clips, frames_per_clip, clip_stride, _p(out), mode), "edison_mfcc_float_clips")
+    return out
+
+
+def mfcc_float_batch(pcm, mode=MFCC_F32_HOST, dtype=np.float64):
+    """Consecutive 1024-sample frames of pcm; trailing samples that do not fill a frame are ignored, as
+    mfcc_utils.mfcc does (frame_count = 1 + (n - 1024) // 1024)."""
+    pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
+    return mfcc_float_clips(pcm, pcm.size // FRAME_LEN, 1, FRAME_LEN, mode, dtype)
 
 
 class Streams:

@@ -1,0 +1,487 @@
+// mfcc_float.cu -- K3: the reference's host-side float MFCCs on the GPU (include/edison_b200.h section 2b).
+//
+// Reference (audio/edison/mfcc/mfcc_utils.py): mfcc() :134-199 = |FFT| of the raw int16 chunk, first 512 bins, 32 mel bins
+// on linspace(0, 8000, 512) -> log(. + 1e-6) -> scipy DCT-II / sqrt(64);  mfcc_mcu() :255-323 = fft/1024, |.|/sqrt(2),
+// 513 bins, weights 128 W then /128, optional log, DCT-II / 64.  The reference computes in float64 (numpy).
+//
+// Two instantiations of one kernel template:
+//   R = double  (edison_mfcc_f64_*): the whole chain in fp64 like numpy -- B200 issues DFMA at half the FFMA rate, so this
+//               is the default parity path; agrees with numpy to ~1e-9 on ordinary input and stays inside the stated
+//               tolerance (max-abs 1e-3, rmse 1e-4) on degenerate frames, where log(mel + 1e-6) sees rounding noise only.
+//   R = float   (edison_mfcc_f32_*): fp32 throughout, ~2x less shared-memory traffic; its error is relative to the
+//               frame's total energy, so the tolerance holds for frames whose mel-band energies lie within 1e4 of
+//               each other (any recorded audio) but not for synthetic pure tones.
+//
+// One warp per 1024-sample frame.  The real FFT is a 512-point complex FFT of z[n] = x[2n] + j x[2n+1] (the int16 pairs
+// are loaded as 32-bit words, coalesced) followed by the real-input split.  512 = 8 x 8 x 8: three radix-8 DIF passes, two
+// butterflies per lane per pass, all 16 complex values of a lane in registers, three exchanges through a per-warp
+// shared-memory buffer whose layouts are conflict-free (tools/proto/f32_fft_flow.py checks the index flow and the
+// wavefront counts).  Magnitudes go to shared memory; the mel filterbank runs 4 lanes per filter, 8 filters at a time;
+// log and the 32x32 DCT matrix finish in registers; the 32 coefficients of a frame leave as one coalesced store.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "edison_internal.h"
+#include "../../include/edison_b200.h"
+
+namespace edison {
+
+constexpr int kXchStride = 72;                 // complex units per radix-8 row: 64 + 8 keeps both transposes conflict-free
+constexpr int kXchLen = 8 * kXchStride;        // 576 >= 513
+constexpr int kMagLen = 520;
+constexpr int kMelWMax = 1024;
+
+template <typename R> struct alignas(2 * sizeof(R)) Cx { R x, y; };   // one 64- / 128-bit shared-memory access
+template <typename R> struct RealTraits;
+template <> struct RealTraits<float> { static constexpr int kWarps = 16; };
+template <> struct RealTraits<double> { static constexpr int kWarps = 12; };
+
+template <typename R>
+struct alignas(16) FloatTables {
+  Cx<R> tw1[7][2][32];         // W512^{(l + 32h) r}, r = 1..7      (pass 1)
+  Cx<R> tw2[7][8];             // W64^{m0 r'}, r' = 1..7            (pass 2)
+  Cx<R> tws[8][32];            // W1024^{l + 32 j}                  (real split)
+  R dct_t[32][32];             // [n][k] = scale * 2 cos(pi k (2n+1) / 64)
+  R mel_w[kMelWMax];           // non-zero weights filter by filter, times the spectrum scale of the mode (and the 1/2
+                               // the split leaves out)
+  R log_eps;
+  int mel_start[32], mel_count[32], mel_off[32];
+  int use_log;
+  int pad_[3];
+};
+
+template <typename R>
+struct FloatLaunch {
+  const int16_t *pcm;
+  long long n_clips;
+  int frames_per_clip;
+  long long clip_stride;
+  R *mfcc;                     // [n_clips * frames_per_clip][32]
+  const FloatTables<R> *tables;
+};
+
+template <typename R>
+struct alignas(16) WarpFloat {
+  Cx<R> xch[kXchLen];
+  R mag[kMagLen];
+  R mel[32];
+  R lm[32];
+};
+template <typename R>
+struct CtaFloat {
+  FloatTables<R> T;
+  WarpFloat<R> w[RealTraits<R>::kWarps];
+};
+
+template <typename R> __device__ __forceinline__ Cx<R> cadd(Cx<R> a, Cx<R> b) { return Cx<R>{a.x + b.x, a.y + b.y}; }
+template <typename R> __device__ __forceinline__ Cx<R> csub(Cx<R> a, Cx<R> b) { return Cx<R>{a.x - b.x, a.y - b.y}; }
+template <typename R> __device__ __forceinline__ Cx<R> cmul(Cx<R> a, Cx<R> w) {
+  return Cx<R>{a.x * w.x - a.y * w.y, a.x * w.y + a.y * w.x};
+}
+template <typename R> __device__ __forceinline__ Cx<R> mul_mj(Cx<R> a) { return Cx<R>{a.y, -a.x}; }   // a * (-j)
+
+// |z| from the power p = re^2 + im^2
+__device__ __forceinline__ float mag_from_power(float p) {   // MUFU.SQRT, relative error <= 2^-22
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(p));
+  return r;
+}
+__device__ __forceinline__ double mag_from_power(double p) {
+  // fp32 reciprocal-sqrt seed (relative error ~2^-22), one Newton step in fp64 -> relative error ~1e-13
+  if (p < 1e-30) return 0.0;      // |X|^2 of int16 data is 0 or >= ~1e-20 (rounding noise); keeps the seed finite
+  float r0;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"((float)p));
+  const double r = (double)r0;
+  const double s0 = p * r;
+  const double e = fma(-s0, s0, p);
+  return fma(e, 0.5 * r, s0);
+}
+__device__ __forceinline__ float log_r(float x) { return logf(x); }
+__device__ __forceinline__ double log_r(double x) { return log(x); }
+
+// 8-point DFT, decimation in frequency, natural order out: v[r] = sum_n v[n] W8^{n r}
+template <typename R>
+__device__ __forceinline__ void radix8(Cx<R> (&v)[8]) {
+  const R s = (R)0.70710678118654752440;
+  Cx<R> a[4], b[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) { a[i] = cadd(v[i], v[i + 4]); b[i] = csub(v[i], v[i + 4]); }
+  b[1] = Cx<R>{(b[1].x + b[1].y) * s, (b[1].y - b[1].x) * s};       // * W8^1
+  b[2] = mul_mj(b[2]);                                              // * W8^2
+  b[3] = Cx<R>{(b[3].y - b[3].x) * s, -(b[3].x + b[3].y) * s};      // * W8^3
+  {
+    const Cx<R> e0 = cadd(a[0], a[2]), e1 = csub(a[0], a[2]), e2 = cadd(a[1], a[3]), e3 = mul_mj(csub(a[1], a[3]));
+    v[0] = cadd(e0, e2); v[4] = csub(e0, e2); v[2] = cadd(e1, e3); v[6] = csub(e1, e3);
+  }
+  {
+    const Cx<R> e0 = cadd(b[0], b[2]), e1 = csub(b[0], b[2]), e2 = cadd(b[1], b[3]), e3 = mul_mj(csub(b[1], b[3]));
+    v[1] = cadd(e0, e2); v[5] = csub(e0, e2); v[3] = cadd(e1, e3); v[7] = csub(e1, e3);
+  }
+}
+
+// (lo, hi) int16 pair -> two reals without the conversion pipe.
+//   float : 0x4B000000 | (x ^ 0x8000)  is 2^23 + x + 2^15
+//   double: 0x43300000:(x ^ 0x8000)    is 2^52 + x + 2^15
+__device__ __forceinline__ Cx<float> pcm_pair(uint32_t w, float) {
+  const uint32_t t = w ^ 0x80008000u;
+  const float lo = __uint_as_float(__byte_perm(t, 0x4B00u, 0x5410)) - 8421376.0f;
+  const float hi = __uint_as_float(__byte_perm(t, 0x4B00u, 0x5432)) - 8421376.0f;
+  return Cx<float>{lo, hi};
+}
+__device__ __forceinline__ Cx<double> pcm_pair(uint32_t w, double) {
+  const uint32_t t = w ^ 0x80008000u;
+  const double bias = 4503599627370496.0 + 32768.0;
+  const double lo = __hiloint2double(0x43300000, (int)(t & 0xFFFFu)) - bias;
+  const double hi = __hiloint2double(0x43300000, (int)(t >> 16)) - bias;
+  return Cx<double>{lo, hi};
+}
+
+template <bool ALIGNED>
+__device__ __forceinline__ void load_frame_words(const int16_t *base, int lane, uint32_t (&w)[16]) {
+  if (ALIGNED) {
+    const uint32_t *p = reinterpret_cast<const uint32_t *>(base);
+#pragma unroll
+    for (int k = 0; k < 16; k++) w[k] = __ldg(p + lane + 32 * k);
+  } else {
+    const uint16_t *p = reinterpret_cast<const uint16_t *>(base);
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      const int n = 2 * (lane + 32 * k);
+      w[k] = (uint32_t)__ldg(p + n) | ((uint32_t)__ldg(p + n + 1) << 16);
+    }
+  }
+}
+
+template <typename R, bool ALIGNED>
+__global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kernel(FloatLaunch<R> P) {
+  constexpr int kWarps = RealTraits<R>::kWarps;
+  using C = Cx<R>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  CtaFloat<R> &S = *reinterpret_cast<CtaFloat<R> *>(smem_raw);
+  {
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(P.tables);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(&S.T);
+    for (int i = threadIdx.x; i < (int)(sizeof(FloatTables<R>) / 4); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  const FloatTables<R> &T = S.T;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  WarpFloat<R> &W = S.w[warp];
+  const long long n_frames = P.n_clips * P.frames_per_clip;
+  const long long stride = (long long)gridDim.x * kWarps;
+  long long f = (long long)blockIdx.x * kWarps + warp;
+  if (f >= n_frames) return;
+
+  auto frame_base = [&](long long fr) {
+    const long long clip = fr / P.frames_per_clip;
+    return P.pcm + clip * P.clip_stride + (fr - clip * P.frames_per_clip) * (long long)EDISON_FRAME_LEN;
+  };
+  uint32_t pw[16];
+  load_frame_words<ALIGNED>(frame_base(f), lane, pw);
+
+  for (; f < n_frames; f += stride) {
+    C v[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) v[k] = pcm_pair(pw[k], R());
+    if (f + stride < n_frames) load_frame_words<ALIGNED>(frame_base(f + stride), lane, pw);   // lands during the FFT
+
+    // ---- pass 1: over n2 (stride 64); lane holds m = lane + 32h, n2 = 0..7 in v[2 n2 + h]
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      C t[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) t[i] = v[2 * i + h];
+      radix8(t);
+      W.xch[lane + 32 * h] = t[0];
+#pragma unroll
+      for (int r = 1; r < 8; r++) W.xch[kXchStride * r + lane + 32 * h] = cmul(t[r], T.tw1[r - 1][h][lane]);
+    }
+    __syncwarp();
+    // ---- pass 2: over m1; this lane takes m0 = lane & 7 and r = (lane >> 3) + 4h
+    const int lo3 = lane & 7, hi2 = lane >> 3;
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+#pragma unroll
+      for (int i = 0; i < 8; i++) v[8 * h + i] = W.xch[kXchStride * (hi2 + 4 * h) + 8 * i + lo3];
+    __syncwarp();
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      C t[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) t[i] = v[8 * h + i];
+      radix8(t);
+      const int r = hi2 + 4 * h;
+      const int col = 8 * r + (lo3 ^ r);
+      W.xch[col] = t[0];
+#pragma unroll
+      for (int rp = 1; rp < 8; rp++) W.xch[kXchStride * rp + col] = cmul(t[rp], T.tw2[rp - 1][lo3]);
+    }
+    __syncwarp();
+    // ---- pass 3: over m0; this lane takes r = lane & 7 and r' = (lane >> 3) + 4h; outputs k = 64 q + lane + 32 h
+#pragma unroll
+    for (int h = 0; h < 2; h++)
+#pragma unroll
+      for (int i = 0; i < 8; i++) v[8 * h + i] = W.xch[kXchStride * (hi2 + 4 * h) + 8 * lo3 + (i ^ lo3)];
+    __syncwarp();
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      C t[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) t[i] = v[8 * h + i];
+      radix8(t);
+#pragma unroll
+      for (int q = 0; q < 8; q++) W.xch[64 * q + lane + 32 * h] = t[q];
+      if (h == 0 && lane == 0) W.xch[512] = t[0];      // Z[512] = Z[0] for the k = 0 pair
+    }
+    __syncwarp();
+    // ---- real-input split on pairs (k, 512 - k), k = lane + 32 j; magnitudes are 2|X| (the 1/2 lives in mel_w)
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const int k = lane + 32 * j;
+      const C a = W.xch[k], bc = W.xch[512 - k];
+      const C w = T.tws[j][lane];
+      const R er = a.x + bc.x, ei = a.y - bc.y;        // A + conj(Z[512-k])
+      const R dr = a.x - bc.x, di = a.y + bc.y;        // A - conj(Z[512-k])
+      const R tr = w.x * di + w.y * dr, ti = w.y * di - w.x * dr;   // W^k * (-j D)
+      const R x1r = er + tr, x1i = ei + ti, x2r = er - tr, x2i = ei - ti;
+      W.mag[k] = mag_from_power(x1r * x1r + x1i * x1i);
+      W.mag[512 - k] = mag_from_power(x2r * x2r + x2i * x2i);
+    }
+    if (lane == 0) {
+      const C c = W.xch[256];
+      W.mag[256] = (R)2 * mag_from_power(c.x * c.x + c.y * c.y);
+    }
+    __syncwarp();
+    // ---- mel: 4 lanes per filter, 8 filters per round
+    {
+      const int q = lane & 3;
+#pragma unroll
+      for (int round = 0; round < 4; round++) {
+        const int m = 8 * round + (lane >> 2);
+        const int cnt = T.mel_count[m];
+        const R *mg = W.mag + T.mel_start[m];
+        const R *wt = T.mel_w + T.mel_off[m];
+        R acc = (R)0;
+        for (int i = q; i < cnt; i += 4) acc = fma(mg[i], wt[i], acc);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        if (q == 0) W.mel[m] = acc;
+      }
+    }
+    __syncwarp();
+    {
+      R x = W.mel[lane];
+      if (T.use_log) x = log_r(x + T.log_eps);
+      W.lm[lane] = x;
+    }
+    __syncwarp();
+    {
+      R acc = (R)0;
+#pragma unroll 8
+      for (int n = 0; n < 32; n++) acc = fma(W.lm[n], T.dct_t[n][lane], acc);
+      P.mfcc[f * 32 + lane] = acc;
+    }
+    __syncwarp();
+  }
+}
+
+// ---- tables ------------------------------------------------------------------------------------------------------------
+// gen_mel_weight_matrix (mfcc_utils.py:36-73) with the constants of audio/config.py:16-21, 33-34; everything is built in
+// double and rounded once to R
+template <typename R>
+static int fill_tables(FloatTables<R> &T, int mode) {
+  memset(&T, 0, sizeof T);
+  const double tau = 6.283185307179586476925286766559;
+  for (int r = 1; r < 8; r++)
+    for (int h = 0; h < 2; h++)
+      for (int l = 0; l < 32; l++) {
+        const double a = -tau * (double)(((l + 32 * h) * r) % 512) / 512.0;
+        T.tw1[r - 1][h][l] = Cx<R>{(R)cos(a), (R)sin(a)};
+      }
+  for (int r = 1; r < 8; r++)
+    for (int m0 = 0; m0 < 8; m0++) {
+      const double a = -tau * (double)((m0 * r) % 64) / 64.0;
+      T.tw2[r - 1][m0] = Cx<R>{(R)cos(a), (R)sin(a)};
+    }
+  for (int j = 0; j < 8; j++)
+    for (int l = 0; l < 32; l++) {
+      const double a = -tau * (double)(l + 32 * j) / 1024.0;
+      T.tws[j][l] = Cx<R>{(R)cos(a), (R)sin(a)};
+    }
+  const int n_bins = mode == EDISON_MFCC_F32_HOST ? 512 : 513;
+  const double spec_scale = mode == EDISON_MFCC_F32_HOST ? 1.0 : 1.0 / 1024.0 / sqrt(2.0);
+  const double dct_scale = mode == EDISON_MFCC_F32_HOST ? 1.0 / sqrt(64.0) : 1.0 / 64.0;
+  T.use_log = mode != EDISON_MFCC_F32_MCU;
+  T.log_eps = (R)1e-6;
+  auto mel = [](double f) { return 1127.0 * log(1.0 + f / 700.0); };
+  const double e_lo = mel(80.0), e_hi = mel(7600.0);
+  double edges[34];
+  for (int i = 0; i < 34; i++) edges[i] = e_lo + (e_hi - e_lo) * (double)i / 33.0;
+  int off = 0;
+  for (int m = 0; m < 32; m++) {
+    int start = -1, count = 0;
+    std::vector<double> w;
+    for (int b = 1; b < n_bins; b++) {
+      const double x = mel(8000.0 * (double)b / (double)(n_bins - 1));
+      const double lower = (x - edges[m]) / (edges[m + 1] - edges[m]);
+      const double upper = (edges[m + 2] - x) / (edges[m + 2] - edges[m + 1]);
+      const double v = fmax(0.0, fmin(lower, upper));
+      if (v > 0.0) {
+        if (start < 0) start = b;
+        if (b != start + count) return -1;   // a filter's support is one run of bins
+        w.push_back(v);
+        count++;
+      }
+    }
+    if (start < 0) start = 0;
+    if (off + count > kMelWMax) return -1;
+    T.mel_start[m] = start; T.mel_count[m] = count; T.mel_off[m] = off;
+    for (int i = 0; i < count; i++) T.mel_w[off + i] = (R)(w[i] * spec_scale * 0.5);
+    off += count;
+  }
+  for (int n = 0; n < 32; n++)
+    for (int k = 0; k < 32; k++)
+      T.dct_t[n][k] = (R)(dct_scale * 2.0 * cos(3.14159265358979323846 * (double)k * (double)(2 * n + 1) / 64.0));
+  return 0;
+}
+
+template <typename R>
+struct FloatState {
+  FloatTables<R> *tables[3] = {nullptr, nullptr, nullptr};   // device, built on first use (under the ctx lock)
+  bool configured = false;
+};
+static FloatState<float> g_f32;
+static FloatState<double> g_f64;
+template <typename R> static FloatState<R> &state();
+template <> FloatState<float> &state<float>() { return g_f32; }
+template <> FloatState<double> &state<double>() { return g_f64; }
+
+template <typename R>
+static int float_tables(int mode, const FloatTables<R> **out) {
+  FloatState<R> &st = state<R>();
+  if (mode < 0 || mode > 2) return ctx_fail(EDISON_E_ARG, "float MFCC mode %d unknown", mode);
+  if (!st.configured) {
+    cudaError_t e = cudaFuncSetAttribute(mfcc_float_kernel<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)sizeof(CtaFloat<R>));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(mfcc_float_kernel<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaFloat<R>));
+    if (e != cudaSuccess) return ctx_fail(EDISON_E_CUDA, "mfcc_float shared memory opt-in: %s", cudaGetErrorString(e));
+    st.configured = true;
+  }
+  if (!st.tables[mode]) {
+    FloatTables<R> *h = new FloatTables<R>;
+    if (fill_tables(*h, mode)) { delete h; return ctx_fail(EDISON_E_DATA, "mel table construction failed"); }
+    FloatTables<R> *d = nullptr;
+    cudaError_t e = cudaMalloc(&d, sizeof *h);
+    if (e == cudaSuccess) e = cudaMemcpy(d, h, sizeof *h, cudaMemcpyHostToDevice);
+    delete h;
+    if (e != cudaSuccess) { if (d) cudaFree(d); return ctx_fail(EDISON_E_CUDA, "float MFCC tables: %s", cudaGetErrorString(e)); }
+    st.tables[mode] = d;
+  }
+  *out = st.tables[mode];
+  return EDISON_OK;
+}
+
+template <typename R>
+static int launch_float(const CtxView &c, const int16_t *d_pcm, size_t n_clips, size_t fpc, size_t stride, R *d_out, int mode,
+                        cudaStream_t st) {
+  constexpr int kWarps = RealTraits<R>::kWarps;
+  const FloatTables<R> *tb;
+  int rc = float_tables<R>(mode, &tb);
+  if (rc) return rc;
+  const long long n_frames = (long long)n_clips * (long long)fpc;
+  if (n_frames == 0) return EDISON_OK;
+  FloatLaunch<R> L{d_pcm, (long long)n_clips, (int)fpc, (long long)stride, d_out, tb};
+  const long long ctas = (n_frames + kWarps - 1) / kWarps;
+  const unsigned grid = (unsigned)(ctas < c.sm_count ? ctas : c.sm_count);
+  const bool aligned = ((uintptr_t)d_pcm % 4 == 0) && (stride % 2 == 0);
+  if (aligned) mfcc_float_kernel<R, true><<<grid, kWarps * 32, sizeof(CtaFloat<R>), st>>>(L);
+  else mfcc_float_kernel<R, false><<<grid, kWarps * 32, sizeof(CtaFloat<R>), st>>>(L);
+  count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return ctx_fail(EDISON_E_CUDA, "mfcc_float_kernel: %s", cudaGetErrorString(e));
+  return EDISON_OK;
+}
+
+static bool float_dev_ptr(const void *p) {
+  cudaPointerAttributes a;
+  if (!p || cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+template <typename R>
+static int clips_dev(const int16_t *d_pcm, size_t n_clips, size_t fpc, size_t stride, R *d_mfcc, int mode, void *stream) {
+  if ((n_clips && fpc) && (!d_pcm || !d_mfcc)) return ctx_fail(EDISON_E_ARG, "float MFCC: null pointer");
+  ctx_lock();
+  CtxView c;
+  int rc = ctx_acquire(&c);
+  if (!rc) rc = launch_float<R>(c, d_pcm, n_clips, fpc, stride, d_mfcc, mode, stream ? (cudaStream_t)stream : c.stream);
+  ctx_unlock();
+  return rc;
+}
+
+template <typename R>
+static int clips_any(const int16_t *pcm, size_t n_clips, size_t fpc, size_t stride, R *mfcc, int mode) {
+  const size_t n_frames = n_clips * fpc;
+  if (n_frames && (!pcm || !mfcc)) return ctx_fail(EDISON_E_ARG, "float MFCC: null pointer");
+  if (float_dev_ptr(pcm)) {
+    int rc = clips_dev<R>(pcm, n_clips, fpc, stride, mfcc, mode, nullptr);
+    return rc ? rc : edison_sync(nullptr);
+  }
+  ctx_lock();
+  CtxView c;
+  int rc = ctx_acquire(&c);
+  int16_t *d_pcm = nullptr;
+  R *d_out = nullptr;
+  if (!rc && n_frames) {
+    const size_t samples = (n_clips - 1) * stride + fpc * EDISON_FRAME_LEN;
+    cudaError_t e = cudaMalloc(&d_pcm, samples * sizeof(int16_t));
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, n_frames * 32 * sizeof(R));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_pcm, pcm, samples * sizeof(int16_t), cudaMemcpyHostToDevice, c.stream);
+    if (e != cudaSuccess) rc = ctx_fail(EDISON_E_NOMEM, "float MFCC staging: %s", cudaGetErrorString(e));
+    if (!rc) rc = launch_float<R>(c, d_pcm, n_clips, fpc, stride, d_out, mode, c.stream);
+    if (!rc) {
+      e = cudaMemcpyAsync(mfcc, d_out, n_frames * 32 * sizeof(R), cudaMemcpyDeviceToHost, c.stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
+      if (e != cudaSuccess) rc = ctx_fail(EDISON_E_CUDA, "float MFCC: %s", cudaGetErrorString(e));
+    }
+    if (d_pcm) cudaFree(d_pcm);
+    if (d_out) cudaFree(d_out);
+  }
+  ctx_unlock();
+  return rc;
+}
+
+}  // namespace edison
+
+using namespace edison;
+
+extern "C" {
+
+int edison_mfcc_f64_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples,
+                              double *d_mfcc, int mode, void *stream) {
+  return clips_dev<double>(d_pcm, n_clips, frames_per_clip, clip_stride_samples, d_mfcc, mode, stream);
+}
+int edison_mfcc_f64_clips(const int16_t *pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples, double *mfcc,
+                          int mode) {
+  return clips_any<double>(pcm, n_clips, frames_per_clip, clip_stride_samples, mfcc, mode);
+}
+int edison_mfcc_f64_batch(const int16_t *pcm, size_t n_frames, double *mfcc, int mode) {
+  return clips_any<double>(pcm, n_frames, 1, EDISON_FRAME_LEN, mfcc, mode);
+}
+int edison_mfcc_f32_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples,
+                              float *d_mfcc, int mode, void *stream) {
+  return clips_dev<float>(d_pcm, n_clips, frames_per_clip, clip_stride_samples, d_mfcc, mode, stream);
+}
+int edison_mfcc_f32_clips(const int16_t *pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples, float *mfcc,
+                          int mode) {
+  return clips_any<float>(pcm, n_clips, frames_per_clip, clip_stride_samples, mfcc, mode);
+}
+int edison_mfcc_f32_batch(const int16_t *pcm, size_t n_frames, float *mfcc, int mode) {
+  return clips_any<float>(pcm, n_frames, 1, EDISON_FRAME_LEN, mfcc, mode);
+}
+
+}  // extern "C"

@@ -109,6 +109,27 @@ int edison_infer_q7_batch(const int8_t *net_in, size_t n, int8_t *logits, int8_t
 int edison_mfcc_q15_clips(const int16_t *pcm, size_t n_clips, size_t frames_per_clip,
                           size_t clip_stride_samples, int16_t *mfcc, int8_t *net_in);
 
+/* ---- section 2b: the reference's host-side float MFCCs (audio/edison/mfcc/mfcc_utils.py) ----------------------------
+ * Fixed to the reference's configuration (audio/config.py:12-36): fs 16 kHz, 1024-sample frames, hop 1024, 32 mel bins
+ * 80..7600 Hz.  Output [n][32].  The reference computes in float64 (numpy):
+ *   edison_mfcc_f64_*: fp64 on the device, the parity path: max-abs <= 1e-3 / rmse <= 1e-4 on ANY input (observed ~1e-9
+ *                      on ordinary audio; the slack is for frames where log(mel + 1e-6) sees only rounding noise);
+ *   edison_mfcc_f32_*: fp32 on the device, the fast path: same tolerance on frames whose mel-band energies lie within
+ *                      1e4 of each other (recorded audio); synthetic pure tones exceed it. */
+#define EDISON_MFCC_F32_HOST     0  /* mfcc():     |FFT| bins 0..511 -> mel -> log(.+1e-6) -> DCT-II / sqrt(64), :134-199 */
+#define EDISON_MFCC_F32_MCU      1  /* mfcc_mcu(): fft/1024, |.|/sqrt 2, 513 bins, 128 W then /128, DCT-II / 64, :255-323  */
+#define EDISON_MFCC_F32_MCU_LOG  2  /* mfcc_mcu(use_log=True)                                                              */
+int edison_mfcc_f64_batch(const int16_t *pcm, size_t n_frames, double *mfcc, int mode);
+int edison_mfcc_f64_clips(const int16_t *pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples,
+                          double *mfcc, int mode);
+int edison_mfcc_f64_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples,
+                              double *d_mfcc, int mode, void *stream);
+int edison_mfcc_f32_batch(const int16_t *pcm, size_t n_frames, float *mfcc, int mode);
+int edison_mfcc_f32_clips(const int16_t *pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples,
+                          float *mfcc, int mode);
+int edison_mfcc_f32_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples,
+                              float *d_mfcc, int mode, void *stream);
+
 /* ---- section 3: device-resident variants (all pointers are device pointers; stream is a
  *      cudaStream_t passed as void*, NULL = the library's stream; asynchronous) --------------- */
 int edison_mfcc_q15_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip,
