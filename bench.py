@@ -246,6 +246,24 @@ def run_ours(args, rank, world, local_rank):
                              "hbm_gbs": nfr * (2048 + 32 * outf.element_size()) / (ms / 1e3) / 1e9}
         del outf
 
+    # ---- float CNN (K4; config #4: 262,144 clips x 403 float32 = 422.6 MB in, device resident)
+    n4 = 262144
+    x4 = net_in[: n4 // 2 * 403].to(torch.float32).repeat(2)     # int8 MFCC rows of the KWS step, as floats
+    lg4 = torch.empty(n4, 10, dtype=torch.float32, device=dev)
+    sm4 = torch.empty(n4, 10, dtype=torch.float32, device=dev)
+    for _ in range(3):
+        chk(L.edison_infer_f32_batch_dev(P(x4), n4, P(lg4), P(sm4), sp))
+    torch.cuda.synchronize()
+    a.record(st)
+    for _ in range(args.steps):
+        chk(L.edison_infer_f32_batch_dev(P(x4), n4, P(lg4), P(sm4), sp))
+    b.record(st)
+    torch.cuda.synchronize()
+    cfg4_ms = a.elapsed_time(b) / args.steps
+    cfg4 = {"workload": "config#4: float CNN (Cube.AI kws_conv) on 262,144 clips x 403 float32, 1 GPU", "ms": cfg4_ms,
+            "clips_per_s": n4 / (cfg4_ms / 1e3), "fp32_tflops": n4 * 1569504 / (cfg4_ms / 1e3) / 1e12}
+    del x4, lg4, sm4
+
     # ---- e2e: edison_kws_batch() on pinned HOST buffers, H2D + D2H inside the timed region
     ne = E2E_CLIPS
     h_pcm = torch.empty(ne * CLIP, dtype=torch.int16).pin_memory()
@@ -313,6 +331,7 @@ def run_ours(args, rank, world, local_rank):
                 "gpu_launches": int(launches), "clocks": clocks}
         if stream_stats:
             line["streaming"] = stream_stats
+        line["cfg4_float_cnn"] = cfg4
         line["float_mfcc"] = dict(float_stats, workload="mfcc_utils.mfcc arithmetic on 65,536 x 1 s clips (15 frames each), 1 GPU")
         if world == 1 and not args.no_cpu:
             sys.path.insert(0, os.path.join(ROOT, "oracle"))

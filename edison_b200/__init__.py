@@ -20,6 +20,7 @@ from .capi import (  # noqa: F401
     SOFTMAX_CMSIS_SIMD,
     SOFTMAX_NNOM_LOCAL,
     Streams,
+    infer_f32_batch,
     infer_q7_batch,
     init,
     kws_batch,

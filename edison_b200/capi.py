@@ -49,6 +49,8 @@ def lib():
         L.edison_infer_q7_batch_dev.argtypes = [vp, sz, vp, vp, vp]
         L.edison_kws_batch_dev.argtypes = [vp, sz, sz, vp, vp, vp, vp]
         L.edison_sync.argtypes = [vp]
+        L.edison_infer_f32_batch.argtypes = [vp, sz, vp, vp]
+        L.edison_infer_f32_batch_dev.argtypes = [vp, sz, vp, vp, vp]
         for t in ("f32", "f64"):
             getattr(L, "edison_mfcc_%s_batch" % t).argtypes = [vp, sz, vp, ci]
             getattr(L, "edison_mfcc_%s_clips" % t).argtypes = [vp, sz, sz, sz, vp, ci]
@@ -142,6 +144,16 @@ def infer_q7_batch(net_in, want_softmax=True):
     lg = np.empty((n, N_CLASSES), dtype=np.int8)
     sm = np.empty((n, N_CLASSES), dtype=np.int8) if want_softmax else None
     check(lib().edison_infer_q7_batch(_p(net_in), n, _p(lg), _p(sm)), "edison_infer_q7_batch")
+    return lg, sm
+
+
+def infer_f32_batch(net_in):
+    """float CNN (Cube.AI build of kws_conv): float32 [n, 403] (MFCC values as floats) -> (logits [n,10], softmax [n,10])"""
+    net_in = np.ascontiguousarray(net_in, dtype=np.float32).reshape(-1, NET_IN)
+    n = net_in.shape[0]
+    lg = np.empty((n, N_CLASSES), dtype=np.float32)
+    sm = np.empty((n, N_CLASSES), dtype=np.float32)
+    check(lib().edison_infer_f32_batch(_p(net_in), n, _p(lg), _p(sm)), "edison_infer_f32_batch")
     return lg, sm
 
 

@@ -1,0 +1,330 @@
+// cube_f32_kernel.cu -- K4: the reference's float CNN (Cube.AI build of kws_conv) in fp32 FFMA.
+//
+// Reference: topology audio/edison/train/kws_keras.py:371-397; generated network firmware/src/ai/cube/kws/kws.c:306-420
+// (conv2d_nl_pool x2, conv2d x2, dense, forward_sm), tensors :213-291, weight offsets :488-516; entry ai_kws_run via
+// cubeNetRun firmware/src/ai/ai.c:354-378; input = MFCC values cast to float, unscaled (app.c:679-683).
+// The arithmetic of ST's closed runtime is unknown beyond "float32 MACs": parity is tolerance-based against the fp64
+// restatement oracle/cube_float.py and UNPINNED at the keras boundary.
+//
+// A CTA keeps a tile of 12 clips in shared memory through all layers (1,612 B in, 40 + 40 B out per clip).  Each thread owns
+// a register tile of 2 pixels x 16 output channels: for the two pooled layers the 2 pixels are the two conv rows under one
+// pooled pixel (max pool = max of the thread's own accumulators), for the others the same pixel of two clips.  Activations are
+// H,W,C with every pixel's channel vector padded by 4 floats, so the 128-bit reads of a warp (one pixel per lane) spread
+// over all banks; weights are re-laid [ky][kx][c][o] at load so a warp's weight reads are uniform 128-bit loads served by
+// L1/L2 (the 172 KB model is shared by every CTA).  Why FFMA and not tensor cores: at fp32 accuracy the alternatives are
+// 3xTF32 / 3xBF16 splits on mma.sync; 0.78 MMAC per clip puts this kernel at ~1/3 of K1's time per clip already.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "edison_internal.h"
+#include "../../include/edison_b200.h"
+
+namespace edison {
+
+constexpr int kCubeClips = 12;       // clips per CTA tile (even: the unpooled layers pair clip b with b + 6)
+constexpr int kCubeThreads = 384;
+constexpr int kPad = 4;              // floats appended to every pixel's channel vector
+
+// activation geometry (H, W, C) after each layer
+constexpr int kA1 = 13 * 9 * (16 + kPad);     // conv1 + pool
+constexpr int kA2 = 5 * 7 * (32 + kPad);      // conv2 + pool
+constexpr int kA3 = 3 * 5 * (64 + kPad);      // conv3
+constexpr int kA4 = 1 * 3 * 32;               // conv4 (flattened H,W,C = dense input, unpadded)
+constexpr int kBufA = kA2 > EDISON_NET_IN ? kA2 : EDISON_NET_IN;   // input / conv2 out / conv4 out
+constexpr int kBufB = kA1;                                         // conv1 out / conv3 out
+
+struct CubeModel {
+  float w1[5 * 5 * 1 * 16], b1[16];
+  float w2[3 * 3 * 16 * 32], b2[32];
+  float w3[3 * 3 * 32 * 64], b3[64];
+  float w4[3 * 3 * 64 * 32], b4[32];
+  float wd[10 * 96], bd[10];         // dense stays [out][in]
+  float pad_[2];
+};
+
+struct CubeSmem {
+  float a[kCubeClips][kBufA];
+  float b[kCubeClips][kBufB];
+  float logits[kCubeClips][12];
+};
+
+// One conv layer over the tile.  in: [clip][HIN][WIN][C + pad] (C == 1: unpadded scalars), out: [clip][HP][WO][O + opad].
+template <int HIN, int WIN, int C, int KH, int KW, int O, bool POOL, int IN_STRIDE, int OUT_STRIDE, int OPAD>
+__device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *__restrict__ out, const float *__restrict__ wgt,
+                                           const float *__restrict__ bias) {
+  constexpr int HO = HIN - KH + 1, WO = WIN - KW + 1;
+  constexpr int HP = POOL ? HO / 2 : HO;
+  constexpr int Q = 16, G = O / Q;
+  constexpr int CP = C == 1 ? 1 : C + kPad;
+  constexpr int OP = O + OPAD;
+  constexpr int NPIX = HP * WO;
+  constexpr int NB = POOL ? kCubeClips : kCubeClips / 2;
+  constexpr int NITEMS = G * NB * NPIX;
+  for (int item = threadIdx.x; item < NITEMS; item += kCubeThreads) {
+    const int g = item / (NB * NPIX);
+    const int rest = item - g * (NB * NPIX);
+    const int b = rest / NPIX, pix = rest - b * NPIX;
+    const int py = pix / WO, x = pix - py * WO;
+    // the two pixels of this thread
+    const float *p0, *p1;
+    if (POOL) {
+      p0 = in + b * IN_STRIDE + ((2 * py) * WIN + x) * CP;
+      p1 = p0 + WIN * CP;
+    } else {
+      p0 = in + b * IN_STRIDE + (py * WIN + x) * CP;
+      p1 = p0 + (kCubeClips / 2) * IN_STRIDE;
+    }
+    float acc0[Q], acc1[Q];
+#pragma unroll
+    for (int q = 0; q < Q; q++) acc0[q] = acc1[q] = __ldg(bias + g * Q + q);
+    const float *wg = wgt + g * Q;
+#pragma unroll 1
+    for (int ky = 0; ky < KH; ky++) {
+#pragma unroll 1
+      for (int kx = 0; kx < KW; kx++) {
+        const float *q0 = p0 + (ky * WIN + kx) * CP, *q1 = p1 + (ky * WIN + kx) * CP;
+        const float *wk = wg + (ky * KW + kx) * C * O;
+        if (C == 1) {
+          const float a0 = q0[0], a1 = q1[0];
+#pragma unroll
+          for (int q4 = 0; q4 < Q / 4; q4++) {
+            const float4 w = __ldg(reinterpret_cast<const float4 *>(wk) + q4);
+            acc0[4 * q4 + 0] = fmaf(a0, w.x, acc0[4 * q4 + 0]); acc1[4 * q4 + 0] = fmaf(a1, w.x, acc1[4 * q4 + 0]);
+            acc0[4 * q4 + 1] = fmaf(a0, w.y, acc0[4 * q4 + 1]); acc1[4 * q4 + 1] = fmaf(a1, w.y, acc1[4 * q4 + 1]);
+            acc0[4 * q4 + 2] = fmaf(a0, w.z, acc0[4 * q4 + 2]); acc1[4 * q4 + 2] = fmaf(a1, w.z, acc1[4 * q4 + 2]);
+            acc0[4 * q4 + 3] = fmaf(a0, w.w, acc0[4 * q4 + 3]); acc1[4 * q4 + 3] = fmaf(a1, w.w, acc1[4 * q4 + 3]);
+          }
+        } else {
+#pragma unroll 2
+          for (int c4 = 0; c4 < C / 4; c4++) {
+            const float4 v0 = *reinterpret_cast<const float4 *>(q0 + 4 * c4);
+            const float4 v1 = *reinterpret_cast<const float4 *>(q1 + 4 * c4);
+            const float a0[4] = {v0.x, v0.y, v0.z, v0.w}, a1[4] = {v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+            for (int cc = 0; cc < 4; cc++) {
+              const float4 *wr = reinterpret_cast<const float4 *>(wk + (4 * c4 + cc) * O);
+#pragma unroll
+              for (int q4 = 0; q4 < Q / 4; q4++) {
+                const float4 w = __ldg(wr + q4);
+                acc0[4 * q4 + 0] = fmaf(a0[cc], w.x, acc0[4 * q4 + 0]); acc1[4 * q4 + 0] = fmaf(a1[cc], w.x, acc1[4 * q4 + 0]);
+                acc0[4 * q4 + 1] = fmaf(a0[cc], w.y, acc0[4 * q4 + 1]); acc1[4 * q4 + 1] = fmaf(a1[cc], w.y, acc1[4 * q4 + 1]);
+                acc0[4 * q4 + 2] = fmaf(a0[cc], w.z, acc0[4 * q4 + 2]); acc1[4 * q4 + 2] = fmaf(a1[cc], w.z, acc1[4 * q4 + 2]);
+                acc0[4 * q4 + 3] = fmaf(a0[cc], w.w, acc0[4 * q4 + 3]); acc1[4 * q4 + 3] = fmaf(a1[cc], w.w, acc1[4 * q4 + 3]);
+              }
+            }
+          }
+        }
+      }
+    }
+    // ReLU (nl_func_relu_array_f32) then max pool (pool_func_mp_array_f32), or two separate pixels
+    float *o0 = out + b * OUT_STRIDE + (py * WO + x) * OP + g * Q;
+    if (POOL) {
+#pragma unroll
+      for (int q4 = 0; q4 < Q / 4; q4++) {
+        float4 r;
+        r.x = fmaxf(fmaxf(acc0[4 * q4 + 0], acc1[4 * q4 + 0]), 0.f);
+        r.y = fmaxf(fmaxf(acc0[4 * q4 + 1], acc1[4 * q4 + 1]), 0.f);
+        r.z = fmaxf(fmaxf(acc0[4 * q4 + 2], acc1[4 * q4 + 2]), 0.f);
+        r.w = fmaxf(fmaxf(acc0[4 * q4 + 3], acc1[4 * q4 + 3]), 0.f);
+        *reinterpret_cast<float4 *>(o0 + 4 * q4) = r;
+      }
+    } else {
+      float *o1 = o0 + (kCubeClips / 2) * OUT_STRIDE;
+#pragma unroll
+      for (int q4 = 0; q4 < Q / 4; q4++) {
+        *reinterpret_cast<float4 *>(o0 + 4 * q4) = make_float4(fmaxf(acc0[4 * q4 + 0], 0.f), fmaxf(acc0[4 * q4 + 1], 0.f),
+                                                               fmaxf(acc0[4 * q4 + 2], 0.f), fmaxf(acc0[4 * q4 + 3], 0.f));
+        *reinterpret_cast<float4 *>(o1 + 4 * q4) = make_float4(fmaxf(acc1[4 * q4 + 0], 0.f), fmaxf(acc1[4 * q4 + 1], 0.f),
+                                                               fmaxf(acc1[4 * q4 + 2], 0.f), fmaxf(acc1[4 * q4 + 3], 0.f));
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kCubeThreads, 1)
+cube_f32_kernel(const CubeModel *__restrict__ M, const float *__restrict__ net_in, long long n, float *__restrict__ logits,
+                float *__restrict__ softmax) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  CubeSmem &S = *reinterpret_cast<CubeSmem *>(smem_raw);
+  const long long n_tiles = (n + kCubeClips - 1) / kCubeClips;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long c0 = tile * kCubeClips;
+    const int nc = (int)((n - c0) < kCubeClips ? (n - c0) : kCubeClips);
+    for (int i = threadIdx.x; i < kCubeClips * EDISON_NET_IN; i += kCubeThreads) {
+      const int b = i / EDISON_NET_IN, j = i - b * EDISON_NET_IN;
+      S.a[b][j] = b < nc ? __ldg(net_in + (c0 + b) * EDISON_NET_IN + j) : 0.f;
+    }
+    __syncthreads();
+    conv_layer<31, 13, 1, 5, 5, 16, true, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], M->w1, M->b1);
+    __syncthreads();
+    conv_layer<13, 9, 16, 3, 3, 32, true, kBufB, kBufA, kPad>(&S.b[0][0], &S.a[0][0], M->w2, M->b2);
+    __syncthreads();
+    conv_layer<5, 7, 32, 3, 3, 64, false, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], M->w3, M->b3);
+    __syncthreads();
+    conv_layer<3, 5, 64, 3, 3, 32, false, kBufB, kBufA, 0>(&S.b[0][0], &S.a[0][0], M->w4, M->b4);
+    __syncthreads();
+    // dense (forward_dense): one thread per (clip, class)
+    if (threadIdx.x < kCubeClips * EDISON_N_CLASSES) {
+      const int b = threadIdx.x / EDISON_N_CLASSES, o = threadIdx.x - b * EDISON_N_CLASSES;
+      float acc = __ldg(M->bd + o);
+      const float *x = &S.a[b][0], *w = M->wd + o * 96;
+#pragma unroll 8
+      for (int j = 0; j < 96; j++) acc = fmaf(x[j], __ldg(w + j), acc);
+      S.logits[b][o] = acc;
+    }
+    __syncthreads();
+    // softmax, natural e (forward_sm)
+    if (threadIdx.x < nc) {
+      const int b = threadIdx.x;
+      float mx = S.logits[b][0];
+#pragma unroll
+      for (int o = 1; o < EDISON_N_CLASSES; o++) mx = fmaxf(mx, S.logits[b][o]);
+      float e[EDISON_N_CLASSES], sum = 0.f;
+#pragma unroll
+      for (int o = 0; o < EDISON_N_CLASSES; o++) { e[o] = expf(S.logits[b][o] - mx); sum += e[o]; }
+      const float inv = 1.0f / sum;
+#pragma unroll
+      for (int o = 0; o < EDISON_N_CLASSES; o++) {
+        if (logits) logits[(c0 + b) * EDISON_N_CLASSES + o] = S.logits[b][o];
+        if (softmax) softmax[(c0 + b) * EDISON_N_CLASSES + o] = e[o] * inv;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- model load ----------------------------------------------------------------------------------------------------------
+static CubeModel *g_cube = nullptr;   // device; loaded on first use under the ctx lock
+static bool g_cube_cfg = false;
+
+static int cube_load(const char *path) {
+  FILE *f = fopen(path, "rb");
+  if (!f) return ctx_fail(EDISON_E_DATA, "cannot open %s", path);
+  std::vector<unsigned char> raw;
+  unsigned char buf[65536];
+  size_t got;
+  while ((got = fread(buf, 1, sizeof buf, f)) > 0) raw.insert(raw.end(), buf, buf + got);
+  fclose(f);
+  if (raw.size() < 16 || memcmp(raw.data(), "EDCUBEF\0", 8) != 0) return ctx_fail(EDISON_E_DATA, "%s: not a float model blob", path);
+  uint32_t ver, nl;
+  memcpy(&ver, &raw[8], 4); memcpy(&nl, &raw[12], 4);
+  if (ver != 1 || nl != 5) return ctx_fail(EDISON_E_MODEL, "%s: version %u / %u layers unsupported", path, ver, nl);
+  static const uint32_t want[5][7] = {{1, 16, 5, 5, 1, 1, 2}, {1, 32, 3, 3, 16, 1, 2}, {1, 64, 3, 3, 32, 1, 0},
+                                      {1, 32, 3, 3, 64, 1, 0}, {2, 10, 1, 1, 96, 0, 0}};
+  CubeModel *h = new CubeModel;
+  memset(h, 0, sizeof *h);
+  float *wdst[5] = {h->w1, h->w2, h->w3, h->w4, h->wd}, *bdst[5] = {h->b1, h->b2, h->b3, h->b4, h->bd};
+  size_t off = 16;
+  for (int l = 0; l < 5; l++) {
+    uint32_t hd[7];
+    if (off + 28 > raw.size()) { delete h; return ctx_fail(EDISON_E_DATA, "%s: truncated", path); }
+    memcpy(hd, &raw[off], 28); off += 28;
+    if (memcmp(hd, want[l], 28) != 0) { delete h; return ctx_fail(EDISON_E_MODEL, "%s: layer %d is not the kws_conv graph", path, l); }
+    const size_t co = hd[1], kh = hd[2], kw = hd[3], ci = hd[4], nw = co * kh * kw * ci;
+    if (off + 4 * (nw + co) > raw.size()) { delete h; return ctx_fail(EDISON_E_DATA, "%s: truncated", path); }
+    const float *w = reinterpret_cast<const float *>(&raw[off]);
+    if (hd[0] == 1) {
+      for (size_t o = 0; o < co; o++)          // O,H,W,I (kws.c strides) -> [ky][kx][c][o]
+        for (size_t k = 0; k < kh * kw; k++)
+          for (size_t c = 0; c < ci; c++) wdst[l][(k * ci + c) * co + o] = w[(o * kh * kw + k) * ci + c];
+    } else {
+      memcpy(wdst[l], w, 4 * nw);
+    }
+    off += 4 * nw;
+    memcpy(bdst[l], &raw[off], 4 * co);
+    off += 4 * co;
+  }
+  CubeModel *d = nullptr;
+  cudaError_t e = cudaMalloc(&d, sizeof *h);
+  if (e == cudaSuccess) e = cudaMemcpy(d, h, sizeof *h, cudaMemcpyHostToDevice);
+  delete h;
+  if (e != cudaSuccess) { if (d) cudaFree(d); return ctx_fail(EDISON_E_CUDA, "float model upload: %s", cudaGetErrorString(e)); }
+  g_cube = d;
+  return EDISON_OK;
+}
+
+static int cube_launch(const CtxView &c, const float *d_in, size_t n, float *d_logits, float *d_softmax, cudaStream_t st) {
+  if (!g_cube_cfg) {
+    cudaError_t e = cudaFuncSetAttribute(cube_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CubeSmem));
+    if (e != cudaSuccess) return ctx_fail(EDISON_E_CUDA, "cube_f32 shared memory opt-in: %s", cudaGetErrorString(e));
+    g_cube_cfg = true;
+  }
+  if (!g_cube) {
+    char path[1024];
+    snprintf(path, sizeof path, "%s/kws_cube_f32.bin", c.data_dir);
+    int rc = cube_load(path);
+    if (rc) return rc;
+  }
+  if (!n) return EDISON_OK;
+  const long long tiles = ((long long)n + kCubeClips - 1) / kCubeClips;
+  const unsigned grid = (unsigned)(tiles < c.sm_count ? tiles : c.sm_count);
+  cube_f32_kernel<<<grid, kCubeThreads, sizeof(CubeSmem), st>>>(g_cube, d_in, (long long)n, d_logits, d_softmax);
+  count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return ctx_fail(EDISON_E_CUDA, "cube_f32_kernel: %s", cudaGetErrorString(e));
+  return EDISON_OK;
+}
+
+void cube_release(void) {
+  if (g_cube) cudaFree(g_cube);
+  g_cube = nullptr;
+}
+
+static bool cube_dev_ptr(const void *p) {
+  cudaPointerAttributes a;
+  if (!p || cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+}  // namespace edison
+
+using namespace edison;
+
+extern "C" {
+
+int edison_infer_f32_batch_dev(const float *d_net_in, size_t n, float *d_logits, float *d_softmax, void *stream) {
+  if (n && !d_net_in) return ctx_fail(EDISON_E_ARG, "edison_infer_f32_batch_dev: null input");
+  ctx_lock();
+  CtxView c;
+  int rc = ctx_acquire(&c);
+  if (!rc) rc = cube_launch(c, d_net_in, n, d_logits, d_softmax, stream ? (cudaStream_t)stream : c.stream);
+  ctx_unlock();
+  return rc;
+}
+
+int edison_infer_f32_batch(const float *net_in, size_t n, float *logits, float *softmax) {
+  if (n && !net_in) return ctx_fail(EDISON_E_ARG, "edison_infer_f32_batch: null input");
+  if (cube_dev_ptr(net_in)) {
+    int rc = edison_infer_f32_batch_dev(net_in, n, logits, softmax, nullptr);
+    return rc ? rc : edison_sync(nullptr);
+  }
+  ctx_lock();
+  CtxView c;
+  int rc = ctx_acquire(&c);
+  float *d_in = nullptr, *d_lg = nullptr, *d_sm = nullptr;
+  if (!rc && n) {
+    cudaError_t e = cudaMalloc(&d_in, n * EDISON_NET_IN * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&d_lg, n * EDISON_N_CLASSES * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&d_sm, n * EDISON_N_CLASSES * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, net_in, n * EDISON_NET_IN * sizeof(float), cudaMemcpyHostToDevice, c.stream);
+    if (e != cudaSuccess) rc = ctx_fail(EDISON_E_NOMEM, "edison_infer_f32_batch staging: %s", cudaGetErrorString(e));
+    if (!rc) rc = cube_launch(c, d_in, n, d_lg, d_sm, c.stream);
+    if (!rc) {
+      if (logits) e = cudaMemcpyAsync(logits, d_lg, n * EDISON_N_CLASSES * sizeof(float), cudaMemcpyDeviceToHost, c.stream);
+      if (e == cudaSuccess && softmax)
+        e = cudaMemcpyAsync(softmax, d_sm, n * EDISON_N_CLASSES * sizeof(float), cudaMemcpyDeviceToHost, c.stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
+      if (e != cudaSuccess) rc = ctx_fail(EDISON_E_CUDA, "edison_infer_f32_batch: %s", cudaGetErrorString(e));
+    }
+    if (d_in) cudaFree(d_in);
+    if (d_lg) cudaFree(d_lg);
+    if (d_sm) cudaFree(d_sm);
+  }
+  ctx_unlock();
+  return rc;
+}
+
+}  // extern "C"

@@ -271,6 +271,7 @@ int ctx_acquire(CtxView *out) {  // caller holds ctx_lock()
   out->sm_count = g.sm_count;
   out->softmax_mode = g.softmax_mode;
   out->stream = g.slot[0].stream;
+  out->data_dir = g.data_dir.c_str();
   return EDISON_OK;
 }
 
@@ -307,6 +308,8 @@ void edison_shutdown(void) {
   }
   if (g.d_tables) cudaFree(g.d_tables);
   nnom_free(g.d_model);
+  mfcc_float_release();
+  cube_release();
   g.d_tables = nullptr;
   g.d_model = nullptr;
   g.ready = false;

@@ -39,6 +39,8 @@ cudaError_t launch_debug_mag_sweep(uint32_t lo, uint32_t hi, const uint32_t *d_e
                                    cudaStream_t stream);
 
 void count_launch(void);
+void mfcc_float_release(void);   // frees the lazily built tables of K3 (mfcc_float.cu); caller holds the ctx lock
+void cube_release(void);         // frees the float model of K4 (cube_f32_kernel.cu)
 
 // ---- shared context (edison_api.cu) for the other translation units of the C ABI ----------------------
 struct CtxView {
@@ -47,6 +49,7 @@ struct CtxView {
   int sm_count;
   int softmax_mode;
   cudaStream_t stream;        // the library's default stream
+  const char *data_dir;       // directory of the model / table blobs (valid until edison_shutdown)
 };
 int ctx_acquire(CtxView *out);                     // initialises the library on first use; EDISON_OK or an error code
 int ctx_fail(int code, const char *fmt, ...);      // records the thread's last-error text, returns code

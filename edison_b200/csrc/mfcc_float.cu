@@ -406,6 +406,15 @@ static int launch_float(const CtxView &c, const int16_t *d_pcm, size_t n_clips, 
   return EDISON_OK;
 }
 
+void mfcc_float_release(void) {
+  for (int m = 0; m < 3; m++) {
+    if (g_f32.tables[m]) cudaFree(g_f32.tables[m]);
+    if (g_f64.tables[m]) cudaFree(g_f64.tables[m]);
+    g_f32.tables[m] = nullptr;
+    g_f64.tables[m] = nullptr;
+  }
+}
+
 static bool float_dev_ptr(const void *p) {
   cudaPointerAttributes a;
   if (!p || cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }

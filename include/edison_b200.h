@@ -130,6 +130,13 @@ int edison_mfcc_f32_clips(const int16_t *pcm, size_t n_clips, size_t frames_per_
 int edison_mfcc_f32_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples,
                               float *d_mfcc, int mode, void *stream);
 
+/* ---- section 2c: the float CNN (Cube.AI build of kws_conv; ai_kws_run via cubeNetRun, firmware/src/ai/ai.c:354-378) ----
+ * net_in[n][403] float = MFCC values cast to float, unscaled (firmware/src/app.c:679-683) -> logits[n][10] (dense output)
+ * and softmax[n][10] (natural e); either output may be NULL.  fp32 FFMA; tolerance-checked against an fp64 restatement
+ * (max-abs 1e-4 on softmax); parity with keras / ST's closed runtime is unpinned. */
+int edison_infer_f32_batch(const float *net_in, size_t n, float *logits, float *softmax);
+int edison_infer_f32_batch_dev(const float *d_net_in, size_t n, float *d_logits, float *d_softmax, void *stream);
+
 /* ---- section 3: device-resident variants (all pointers are device pointers; stream is a
  *      cudaStream_t passed as void*, NULL = the library's stream; asynchronous) --------------- */
 int edison_mfcc_q15_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip,
