@@ -4,7 +4,7 @@
 // (conv2d_nl_pool x2, conv2d x2, dense, forward_sm), tensors :213-291, weight offsets :488-516; entry ai_kws_run via
 // cubeNetRun firmware/src/ai/ai.c:354-378; input = MFCC values cast to float, unscaled (app.c:679-683).
 // The arithmetic of ST's closed runtime is unknown beyond "float32 MACs": parity is tolerance-based against the fp64
-// restatement oracle/cube_float.py and UNPINNED at the keras boundary.
+// restatement in the test tree (cube_float.py) and UNPINNED at the keras boundary.
 //
 // A CTA keeps a tile of 12 clips in shared memory through all layers (1,612 B in, 40 + 40 B out per clip).  Each thread owns
 // a register tile of 2 pixels x 16 output channels: for the two pooled layers the 2 pixels are the two conv rows under one
