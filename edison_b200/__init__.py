@@ -12,6 +12,7 @@ from .capi import (  # noqa: F401
     N_COEFF,
     N_FRAMES,
     MFCC_F32_HOST,
+    MfccC,
     MFCC_F32_MCU,
     MFCC_F32_MCU_LOG,
     N_MEL,

@@ -49,6 +49,18 @@ def lib():
         L.edison_infer_q7_batch_dev.argtypes = [vp, sz, vp, vp, vp]
         L.edison_kws_batch_dev.argtypes = [vp, sz, sz, vp, vp, vp, vp]
         L.edison_sync.argtypes = [vp]
+        L.edison_mfccf_create.argtypes = [ci, ci, ci, ci, ctypes.c_float, ctypes.POINTER(vp)]
+        L.edison_mfccf_delete.argtypes = [vp]
+        L.edison_mfccf_delete.restype = None
+        L.edison_mfccf_n_out.argtypes = [vp]
+        L.edison_mfccf_compute_batch.argtypes = [vp, vp, sz, sz, vp]
+        L.edison_mfccf_compute_batch_dev.argtypes = [vp, vp, sz, sz, vp, vp]
+        L.mfcc_create.argtypes = [ci, ci, ci, ci, ctypes.c_float]
+        L.mfcc_create.restype = vp
+        L.mfcc_compute.argtypes = [vp, vp, vp]
+        L.mfcc_compute.restype = None
+        L.mfcc_delete.argtypes = [vp]
+        L.mfcc_delete.restype = None
         L.edison_infer_f32_batch.argtypes = [vp, sz, vp, vp]
         L.edison_infer_f32_batch_dev.argtypes = [vp, sz, vp, vp, vp]
         for t in ("f32", "f64"):
@@ -178,6 +190,39 @@ def mfcc_float_batch(pcm, mode=MFCC_F32_HOST, dtype=np.float64):
     mfcc_utils.mfcc does (frame_count = 1 + (n - 1024) // 1024)."""
     pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
     return mfcc_float_clips(pcm, pcm.size // FRAME_LEN, 1, FRAME_LEN, mode, dtype)
+
+
+class MfccC:
+    """The firmware's float MFCC in C (firmware/src/audio/mfcc.c): mfcc_create(num, offset, frame_len, dec_bits, preemph).
+    compute(pcm, n_frames, hop) -> int8 [n_frames, num - offset]."""
+
+    def __init__(self, num_mfcc=13, offset=1, frame_len=512, dec_bits=8, preemph=0.97):
+        self._h = ctypes.c_void_p()
+        self.frame_len = frame_len
+        check(lib().edison_mfccf_create(num_mfcc, offset, frame_len, dec_bits, preemph, ctypes.byref(self._h)), "edison_mfccf_create")
+        self.n_out = int(lib().edison_mfccf_n_out(self._h))
+
+    def compute(self, pcm, n_frames=None, hop=None):
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
+        hop = self.frame_len if hop is None else hop
+        if n_frames is None:
+            n_frames = 1 + (pcm.size - self.frame_len) // hop if pcm.size >= self.frame_len else 0
+        if n_frames and pcm.size < (n_frames - 1) * hop + self.frame_len:
+            raise ValueError("pcm too short for %d frames" % n_frames)
+        out = np.empty((n_frames, self.n_out), dtype=np.int8)
+        check(lib().edison_mfccf_compute_batch(self._h, _p(pcm), n_frames, hop, _p(out)), "edison_mfccf_compute_batch")
+        return out
+
+    def close(self):
+        if self._h:
+            lib().edison_mfccf_delete(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
 
 
 class Streams:

@@ -99,3 +99,17 @@ void mfccToNetInputPush(int16_t *mfcc, uint16_t in_x, uint16_t in_y) {
   memmove(netInput, netInput + in_x, keep);
   mfccToNetInput(mfcc, in_x, in_y, (uint32_t)(in_y - 1));
 }
+
+/* ---- firmware/src/audio/mfcc.h:64-67: float MFCC handle API (mfcc_t is opaque: the state lives on the device) -------------- */
+mfcc_t *mfcc_create(int num_mfcc_features, int feature_offset, int frame_len, int mfcc_dec_bits, float preemph) {
+  edison_mfccf *h = NULL;
+  if (edison_mfccf_create(num_mfcc_features, feature_offset, frame_len, mfcc_dec_bits, preemph, &h)) return NULL;  /* mfcc_malloc -> NULL */
+  return (mfcc_t *)h;
+}
+
+void mfcc_delete(mfcc_t *mfcc) { edison_mfccf_delete((edison_mfccf *)mfcc); }
+
+void mfcc_compute(mfcc_t *mfcc, const int16_t *audio_data, int8_t *mfcc_out) {
+  int rc = edison_mfccf_compute_batch((edison_mfccf *)mfcc, audio_data, 1, 1, mfcc_out);
+  if (rc) fatal("mfcc_compute", rc);
+}

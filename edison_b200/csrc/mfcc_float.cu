@@ -48,8 +48,14 @@ struct alignas(16) FloatTables {
   R mel_w[kMelWMax];           // non-zero weights filter by filter, times the spectrum scale of the mode (and the 1/2
                                // the split leaves out)
   R log_eps;
+  R window[1024];              // mfcc.c mode: Hann window of frame_len samples (mfcc.c:67-68), zero beyond
+  R preemph, q_scale;          // mfcc.c mode: pre-emphasis factor (:180-184) and 2^dec_bits (:241)
   int mel_start[32], mel_count[32], mel_off[32];
   int use_log;
+  int c_mode;                  // 1: firmware/src/audio/mfcc.c semantics (pre-emphasis, window, FLT_MIN guard, q7 output)
+  int frame_len;               // samples read per frame (<= 1024); the rest of the 1024-point transform is zero padding
+  int bin_step;                // 1024 / padded frame length: bin i of the reference's FFT is bin i * bin_step here
+  int q7_count;                // mfcc.c mode: number of coefficients written (num - offset)
   int pad_[3];
 };
 
@@ -60,6 +66,7 @@ struct FloatLaunch {
   int frames_per_clip;
   long long clip_stride;
   R *mfcc;                     // [n_clips * frames_per_clip][32]
+  int8_t *q7;                  // mfcc.c mode: [n_clips * frames_per_clip][q7_count]
   const FloatTables<R> *tables;
 };
 
@@ -140,22 +147,24 @@ __device__ __forceinline__ Cx<double> pcm_pair(uint32_t w, double) {
 }
 
 template <bool ALIGNED>
-__device__ __forceinline__ void load_frame_words(const int16_t *base, int lane, uint32_t (&w)[16]) {
-  if (ALIGNED) {
+__device__ __forceinline__ void load_frame_words(const int16_t *base, int lane, int frame_len, uint32_t (&w)[16]) {
+  if (ALIGNED) {   // base 4-byte aligned and frame_len even
     const uint32_t *p = reinterpret_cast<const uint32_t *>(base);
 #pragma unroll
-    for (int k = 0; k < 16; k++) w[k] = __ldg(p + lane + 32 * k);
+    for (int k = 0; k < 16; k++) w[k] = 2 * (lane + 32 * k) < frame_len ? __ldg(p + lane + 32 * k) : 0u;
   } else {
     const uint16_t *p = reinterpret_cast<const uint16_t *>(base);
 #pragma unroll
     for (int k = 0; k < 16; k++) {
       const int n = 2 * (lane + 32 * k);
-      w[k] = (uint32_t)__ldg(p + n) | ((uint32_t)__ldg(p + n + 1) << 16);
+      const uint32_t lo = n < frame_len ? (uint32_t)__ldg(p + n) : 0u;
+      const uint32_t hi = n + 1 < frame_len ? (uint32_t)__ldg(p + n + 1) : 0u;
+      w[k] = lo | (hi << 16);
     }
   }
 }
 
-template <typename R, bool ALIGNED>
+template <typename R, bool ALIGNED, bool CMODE>
 __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kernel(FloatLaunch<R> P) {
   constexpr int kWarps = RealTraits<R>::kWarps;
   using C = Cx<R>;
@@ -180,13 +189,33 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
     return P.pcm + clip * P.clip_stride + (fr - clip * P.frames_per_clip) * (long long)EDISON_FRAME_LEN;
   };
   uint32_t pw[16];
-  load_frame_words<ALIGNED>(frame_base(f), lane, pw);
+  const int frame_len = CMODE ? T.frame_len : 1024;
+  load_frame_words<ALIGNED>(frame_base(f), lane, frame_len, pw);
 
   for (; f < n_frames; f += stride) {
     C v[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) v[k] = pcm_pair(pw[k], R());
-    if (f + stride < n_frames) load_frame_words<ALIGNED>(frame_base(f + stride), lane, pw);   // lands during the FFT
+    if (CMODE) {
+      // mfcc.c:176-192: frame[0] = x[0] (unscaled, as the reference has it), frame[i] = (x[i] - 0.97 x[i-1]) / 2^15, then the
+      // window; samples beyond frame_len are the zero padding.  x[2n-1] is the neighbouring lane's high half.
+      const uint16_t *ps = reinterpret_cast<const uint16_t *>(frame_base(f));
+#pragma unroll
+      for (int k = 0; k < 16; k++) {
+        const int n = lane + 32 * k, s0 = 2 * n;
+        if (s0 < frame_len) {
+          const R prev = n ? (R)(int16_t)__ldg(ps + s0 - 1) : (R)0;
+          const R x0 = v[k].x, x1 = v[k].y;
+          const R f0 = n ? (x0 - prev * T.preemph) * (R)(1.0 / 32768.0) : x0;
+          const R f1 = (x1 - x0 * T.preemph) * (R)(1.0 / 32768.0);
+          v[k].x = f0 * T.window[s0];
+          v[k].y = s0 + 1 < frame_len ? f1 * T.window[s0 + 1] : (R)0;
+        } else {
+          v[k].x = v[k].y = (R)0;
+        }
+      }
+    }
+    if (f + stride < n_frames) load_frame_words<ALIGNED>(frame_base(f + stride), lane, frame_len, pw);   // lands during the FFT
 
     // ---- pass 1: over n2 (stride 64); lane holds m = lane + 32h, n2 = 0..7 in v[2 n2 + h]
 #pragma unroll
@@ -262,10 +291,11 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
       for (int round = 0; round < 4; round++) {
         const int m = 8 * round + (lane >> 2);
         const int cnt = T.mel_count[m];
-        const R *mg = W.mag + T.mel_start[m];
+        const int bs = CMODE ? T.bin_step : 1;
+        const R *mg = W.mag + T.mel_start[m] * bs;
         const R *wt = T.mel_w + T.mel_off[m];
         R acc = (R)0;
-        for (int i = q; i < cnt; i += 4) acc = fma(mg[i], wt[i], acc);
+        for (int i = q; i < cnt; i += 4) acc = fma(mg[i * bs], wt[i], acc);
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
         if (q == 0) W.mel[m] = acc;
@@ -274,7 +304,8 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
     __syncwarp();
     {
       R x = W.mel[lane];
-      if (T.use_log) x = log_r(x + T.log_eps);
+      if (CMODE) x = log_r(x == (R)0 ? (R)1.17549435e-38 : x);     // FLT_MIN for empty bands, mfcc.c:225-231
+      else if (T.use_log) x = log_r(x + T.log_eps);
       W.lm[lane] = x;
     }
     __syncwarp();
@@ -282,7 +313,16 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
       R acc = (R)0;
 #pragma unroll 8
       for (int n = 0; n < 32; n++) acc = fma(W.lm[n], T.dct_t[n][lane], acc);
-      P.mfcc[f * 32 + lane] = acc;
+      if (CMODE) {
+        // mfcc.c:240-250: sum * 2^dec_bits, round() (half away from zero), saturate to q7
+        if (lane < T.q7_count) {
+          R r = acc * T.q_scale;
+          r = r < (R)0 ? -floor((R)0.5 - r) : floor(r + (R)0.5);
+          P.q7[f * T.q7_count + lane] = (int8_t)(r >= (R)127 ? 127 : (r <= (R)-128 ? -128 : (int)r));
+        }
+      } else {
+        P.mfcc[f * 32 + lane] = acc;
+      }
     }
     __syncwarp();
   }
@@ -316,6 +356,8 @@ static int fill_tables(FloatTables<R> &T, int mode) {
   const double dct_scale = mode == EDISON_MFCC_F32_HOST ? 1.0 / sqrt(64.0) : 1.0 / 64.0;
   T.use_log = mode != EDISON_MFCC_F32_MCU;
   T.log_eps = (R)1e-6;
+  T.frame_len = 1024;
+  T.bin_step = 1;
   auto mel = [](double f) { return 1127.0 * log(1.0 + f / 700.0); };
   const double e_lo = mel(80.0), e_hi = mel(7600.0);
   double edges[34];
@@ -364,10 +406,10 @@ static int float_tables(int mode, const FloatTables<R> **out) {
   FloatState<R> &st = state<R>();
   if (mode < 0 || mode > 2) return ctx_fail(EDISON_E_ARG, "float MFCC mode %d unknown", mode);
   if (!st.configured) {
-    cudaError_t e = cudaFuncSetAttribute(mfcc_float_kernel<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(mfcc_float_kernel<R, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)sizeof(CtaFloat<R>));
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(mfcc_float_kernel<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaFloat<R>));
+      e = cudaFuncSetAttribute(mfcc_float_kernel<R, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaFloat<R>));
     if (e != cudaSuccess) return ctx_fail(EDISON_E_CUDA, "mfcc_float shared memory opt-in: %s", cudaGetErrorString(e));
     st.configured = true;
   }
@@ -394,12 +436,12 @@ static int launch_float(const CtxView &c, const int16_t *d_pcm, size_t n_clips, 
   if (rc) return rc;
   const long long n_frames = (long long)n_clips * (long long)fpc;
   if (n_frames == 0) return EDISON_OK;
-  FloatLaunch<R> L{d_pcm, (long long)n_clips, (int)fpc, (long long)stride, d_out, tb};
+  FloatLaunch<R> L{d_pcm, (long long)n_clips, (int)fpc, (long long)stride, d_out, nullptr, tb};
   const long long ctas = (n_frames + kWarps - 1) / kWarps;
   const unsigned grid = (unsigned)(ctas < c.sm_count ? ctas : c.sm_count);
   const bool aligned = ((uintptr_t)d_pcm % 4 == 0) && (stride % 2 == 0);
-  if (aligned) mfcc_float_kernel<R, true><<<grid, kWarps * 32, sizeof(CtaFloat<R>), st>>>(L);
-  else mfcc_float_kernel<R, false><<<grid, kWarps * 32, sizeof(CtaFloat<R>), st>>>(L);
+  if (aligned) mfcc_float_kernel<R, true, false><<<grid, kWarps * 32, sizeof(CtaFloat<R>), st>>>(L);
+  else mfcc_float_kernel<R, false, false><<<grid, kWarps * 32, sizeof(CtaFloat<R>), st>>>(L);
   count_launch();
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return ctx_fail(EDISON_E_CUDA, "mfcc_float_kernel: %s", cudaGetErrorString(e));
@@ -464,11 +506,166 @@ static int clips_any(const int16_t *pcm, size_t n_clips, size_t fpc, size_t stri
   return rc;
 }
 
+// ---- firmware/src/audio/mfcc.c: table construction in float32 exactly as mfcc_create / create_mel_fbank /
+// create_dct_matrix do it (mfcc.c:47-171), so that bin membership of the filters matches the reference build on this host
+static int fill_tables_c(FloatTables<float> &T, int num, int offset, int frame_len, int dec_bits, float preemph) {
+  if (fill_tables(T, EDISON_MFCC_F32_HOST)) return -1;     // FFT twiddles; everything else is overwritten below
+  const int padded = (int)powf(2, ceilf((logf((float)frame_len) / logf(2))));   // mfcc.c:60
+  if (frame_len < 2 || padded > 1024 || num < 1 || num > 26 || offset < 0 || offset >= num || dec_bits < 0 || dec_bits > 24) return -2;
+  memset(T.dct_t, 0, sizeof T.dct_t);
+  memset(T.mel_w, 0, sizeof T.mel_w);
+  memset(T.window, 0, sizeof T.window);
+  T.c_mode = 1; T.use_log = 1; T.frame_len = frame_len; T.bin_step = 1024 / padded; T.q7_count = num - offset;
+  T.preemph = preemph; T.q_scale = (float)(1 << dec_bits);
+  for (int i = 0; i < frame_len; i++)
+    T.window[i] = 0.5f - 0.5f * cosf((float)6.283185307179586476925286766559005 * ((float)i) / (frame_len));   // :67-68
+  auto mel_scale = [](float f) { return 1127.0f * logf(1.0f + f / 700.0f); };                                 // mfcc.h:53-55
+  const int nb = padded / 2;
+  const float width = ((float)16000) / padded;
+  const float mel_lo = mel_scale(20), mel_hi = mel_scale(4000);
+  const float delta = (mel_hi - mel_lo) / (26 + 1);
+  int off = 0;
+  for (int bin = 0; bin < 32; bin++) {
+    T.mel_start[bin] = 0; T.mel_count[bin] = 0; T.mel_off[bin] = off;
+    if (bin >= 26) continue;
+    const float left = mel_lo + bin * delta, center = mel_lo + (bin + 1) * delta, right = mel_lo + (bin + 2) * delta;
+    int first = -1, last = -1;
+    std::vector<float> w(nb, 0.0f);
+    for (int i = 0; i < nb; i++) {
+      const float mel = mel_scale(width * i);
+      if (mel > left && mel < right) {
+        w[i] = mel <= center ? (mel - left) / (center - left) : (right - mel) / (right - center);
+        if (first == -1) first = i;
+        last = i;
+      }
+    }
+    if (first < 0) continue;          // (the reference would index [-1] here; no configuration <= 1024 reaches it)
+    const int count = last - first + 1;
+    if (off + count > kMelWMax) return -3;
+    T.mel_start[bin] = first; T.mel_count[bin] = count;
+    for (int i = 0; i < count; i++) T.mel_w[off + i] = w[first + i] * 0.5f;
+    off += count;
+  }
+  const float normalizer = sqrtf(2.0f / (float)26);                                                           // :101-115
+  for (int k = offset; k < num; k++)
+    for (int n = 0; n < 26; n++) T.dct_t[n][k - offset] = normalizer * cosf(((float)3.14159265358979323846264338327950288) / 26 * (n + 0.5f) * k);
+  return 0;
+}
+
+}  // namespace edison
+
+struct edison_mfccf {
+  edison::FloatTables<float> *d_tables;
+  int n_out, frame_len;
+};
+
+namespace edison {
+
+static int mfccf_launch(const CtxView &c, edison_mfccf *h, const int16_t *d_pcm, size_t n_frames, size_t hop, int8_t *d_out,
+                        cudaStream_t st) {
+  constexpr int kWarps = RealTraits<float>::kWarps;
+  static bool configured = false;      // under the ctx lock
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(mfcc_float_kernel<float, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)sizeof(CtaFloat<float>));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(mfcc_float_kernel<float, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)sizeof(CtaFloat<float>));
+    if (e != cudaSuccess) return ctx_fail(EDISON_E_CUDA, "mfcc_float (mfcc.c mode) shared memory opt-in: %s", cudaGetErrorString(e));
+    configured = true;
+  }
+  if (!n_frames) return EDISON_OK;
+  FloatLaunch<float> L{d_pcm, (long long)n_frames, 1, (long long)hop, nullptr, d_out, h->d_tables};
+  const long long ctas = ((long long)n_frames + kWarps - 1) / kWarps;
+  const unsigned grid = (unsigned)(ctas < c.sm_count ? ctas : c.sm_count);
+  const bool aligned = ((uintptr_t)d_pcm % 4 == 0) && (hop % 2 == 0) && (h->frame_len % 2 == 0);
+  if (aligned) mfcc_float_kernel<float, true, true><<<grid, kWarps * 32, sizeof(CtaFloat<float>), st>>>(L);
+  else mfcc_float_kernel<float, false, true><<<grid, kWarps * 32, sizeof(CtaFloat<float>), st>>>(L);
+  count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return ctx_fail(EDISON_E_CUDA, "mfcc_float_kernel (mfcc.c mode): %s", cudaGetErrorString(e));
+  return EDISON_OK;
+}
+
 }  // namespace edison
 
 using namespace edison;
 
 extern "C" {
+
+int edison_mfccf_create(int num_mfcc_features, int feature_offset, int frame_len, int mfcc_dec_bits, float preemph,
+                        edison_mfccf **out) {
+  if (!out) return ctx_fail(EDISON_E_ARG, "edison_mfccf_create: null out");
+  ctx_lock();
+  CtxView c;
+  int rc = ctx_acquire(&c);
+  if (!rc) {
+    FloatTables<float> *h = new FloatTables<float>;
+    const int r = fill_tables_c(*h, num_mfcc_features, feature_offset, frame_len, mfcc_dec_bits, preemph);
+    if (r) rc = ctx_fail(EDISON_E_ARG, "edison_mfccf_create(%d, %d, %d, %d): unsupported configuration (frames pad to <= 1024, <= 26 "
+                         "coefficients)", num_mfcc_features, feature_offset, frame_len, mfcc_dec_bits);
+    FloatTables<float> *d = nullptr;
+    if (!rc) {
+      cudaError_t e = cudaMalloc(&d, sizeof *h);
+      if (e == cudaSuccess) e = cudaMemcpy(d, h, sizeof *h, cudaMemcpyHostToDevice);
+      if (e != cudaSuccess) { if (d) cudaFree(d); rc = ctx_fail(EDISON_E_CUDA, "edison_mfccf_create: %s", cudaGetErrorString(e)); }
+    }
+    delete h;
+    if (!rc) *out = new edison_mfccf{d, num_mfcc_features - feature_offset, frame_len};
+  }
+  ctx_unlock();
+  return rc;
+}
+
+void edison_mfccf_delete(edison_mfccf *h) {
+  if (!h) return;
+  cudaDeviceSynchronize();
+  if (h->d_tables) cudaFree(h->d_tables);
+  delete h;
+}
+
+int edison_mfccf_n_out(const edison_mfccf *h) { return h ? h->n_out : 0; }
+
+int edison_mfccf_compute_batch_dev(edison_mfccf *h, const int16_t *d_pcm, size_t n_frames, size_t hop_samples, int8_t *d_out,
+                                   void *stream) {
+  if (!h || (n_frames && (!d_pcm || !d_out || !hop_samples))) return ctx_fail(EDISON_E_ARG, "edison_mfccf_compute_batch_dev: bad arguments");
+  ctx_lock();
+  CtxView c;
+  int rc = ctx_acquire(&c);
+  if (!rc) rc = mfccf_launch(c, h, d_pcm, n_frames, hop_samples, d_out, stream ? (cudaStream_t)stream : c.stream);
+  ctx_unlock();
+  return rc;
+}
+
+int edison_mfccf_compute_batch(edison_mfccf *h, const int16_t *pcm, size_t n_frames, size_t hop_samples, int8_t *out) {
+  if (!h || (n_frames && (!pcm || !out || !hop_samples))) return ctx_fail(EDISON_E_ARG, "edison_mfccf_compute_batch: bad arguments");
+  if (float_dev_ptr(pcm)) {
+    int rc = edison_mfccf_compute_batch_dev(h, pcm, n_frames, hop_samples, out, nullptr);
+    return rc ? rc : edison_sync(nullptr);
+  }
+  ctx_lock();
+  CtxView c;
+  int rc = ctx_acquire(&c);
+  int16_t *d_pcm = nullptr;
+  int8_t *d_out = nullptr;
+  if (!rc && n_frames) {
+    const size_t samples = (n_frames - 1) * hop_samples + (size_t)h->frame_len;
+    cudaError_t e = cudaMalloc(&d_pcm, samples * sizeof(int16_t));
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, n_frames * (size_t)h->n_out);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_pcm, pcm, samples * sizeof(int16_t), cudaMemcpyHostToDevice, c.stream);
+    if (e != cudaSuccess) rc = ctx_fail(EDISON_E_NOMEM, "edison_mfccf_compute_batch staging: %s", cudaGetErrorString(e));
+    if (!rc) rc = mfccf_launch(c, h, d_pcm, n_frames, hop_samples, d_out, c.stream);
+    if (!rc) {
+      e = cudaMemcpyAsync(out, d_out, n_frames * (size_t)h->n_out, cudaMemcpyDeviceToHost, c.stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
+      if (e != cudaSuccess) rc = ctx_fail(EDISON_E_CUDA, "edison_mfccf_compute_batch: %s", cudaGetErrorString(e));
+    }
+    if (d_pcm) cudaFree(d_pcm);
+    if (d_out) cudaFree(d_out);
+  }
+  ctx_unlock();
+  return rc;
+}
 
 int edison_mfcc_f64_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples,
                               double *d_mfcc, int mode, void *stream) {

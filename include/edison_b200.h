@@ -130,6 +130,25 @@ int edison_mfcc_f32_clips(const int16_t *pcm, size_t n_clips, size_t frames_per_
 int edison_mfcc_f32_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples,
                               float *d_mfcc, int mode, void *stream);
 
+/* ---- section 2b': the firmware's float MFCC in C (firmware/src/audio/mfcc.c; mfcc.h:64-67) -------------------------------
+ * mfcc_create(num, offset, frame_len, dec_bits, preemph) / mfcc_compute / mfcc_delete keep their names and signatures
+ * (section 1'); these are the batched forms.  Frame f starts at pcm + f * hop_samples and holds frame_len samples
+ * (frame_len pads to a power of two <= 1024); out[f][num - offset] q7.  fp32 on the device; agreement with the reference
+ * build is exact up to ties of round() (<= 1 LSB) on frames whose bands are not empty. */
+typedef struct edison_mfccf edison_mfccf;
+int edison_mfccf_create(int num_mfcc_features, int feature_offset, int frame_len, int mfcc_dec_bits, float preemph,
+                        edison_mfccf **out);
+void edison_mfccf_delete(edison_mfccf *h);
+int edison_mfccf_n_out(const edison_mfccf *h);
+int edison_mfccf_compute_batch(edison_mfccf *h, const int16_t *pcm, size_t n_frames, size_t hop_samples, int8_t *out);
+int edison_mfccf_compute_batch_dev(edison_mfccf *h, const int16_t *d_pcm, size_t n_frames, size_t hop_samples, int8_t *d_out,
+                                   void *stream);
+/* section 1': firmware/src/audio/mfcc.h:64-67.  mfcc_t is opaque here; mfcc_compute is a batch-of-one wrapper. */
+typedef struct _mfcc_t mfcc_t;
+mfcc_t *mfcc_create(int num_mfcc_features, int feature_offset, int frame_len, int mfcc_dec_bits, float preemph);
+void mfcc_delete(mfcc_t *mfcc);
+void mfcc_compute(mfcc_t *mfcc, const int16_t *audio_data, int8_t *mfcc_out);
+
 /* ---- section 2c: the float CNN (Cube.AI build of kws_conv; ai_kws_run via cubeNetRun, firmware/src/ai/ai.c:354-378) ----
  * net_in[n][403] float = MFCC values cast to float, unscaled (firmware/src/app.c:679-683) -> logits[n][10] (dense output)
  * and softmax[n][10] (natural e); either output may be NULL.  fp32 FFMA; tolerance-checked against an fp64 restatement

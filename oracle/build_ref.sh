@@ -57,6 +57,24 @@ build_mfcc () {  # $1 = variant name, $2 = extra flags for the CMSIS sources
 build_mfcc simd "-include arm_math.h -include $HERE/shim/define_dsp.h"
 build_mfcc c ""
 
+# ---- float MFCC of firmware/src/audio/mfcc.c: mfcc.c + CMSIS f32 real FFT, compiled where they lie
+build_mfccf () {
+  local d="$TMP/mfccf" objs=""
+  mkdir -p "$d"
+  local F32_SRCS="TransformFunctions/arm_rfft_fast_f32.c TransformFunctions/arm_rfft_fast_init_f32.c TransformFunctions/arm_cfft_f32.c TransformFunctions/arm_cfft_init_f32.c
+                  TransformFunctions/arm_cfft_radix8_f32.c TransformFunctions/arm_bitreversal2.c CommonTables/arm_const_structs.c"
+  for s in $F32_SRCS; do
+    o="$d/$(basename "$s" .c).o"
+    $CC $COMMON -O2 -ffp-contract=off -c "$DSP/Source/$s" -o "$o"; objs="$objs $o"
+  done
+  $CC $COMMON -O2 -ffp-contract=off -Dmalloc=ref_pad_malloc -U_FORTIFY_SOURCE -D_FORTIFY_SOURCE=0 -I"$FW/audio" -c "$FW/audio/mfcc.c" -o "$d/mfcc.o"
+  $CC $COMMON -O2 -c "$TMP/cmsis_tables.c" -o "$d/cmsis_tables.o"
+  $CC $COMMON -O2 -I"$FW/audio" -c "$HERE/drivers/ref_mfccf_driver.c" -o "$d/driver.o"
+  $CC -shared -o "$OUT/libref_mfcc_f32.so" $objs "$d/mfcc.o" "$d/cmsis_tables.o" "$d/driver.o" \
+      -Wl,--gc-sections -Wl,--version-script="$HERE/drivers/exports.map" -Wl,-z,defs -lm
+}
+build_mfccf
+
 NNOM="$FW/ai/nnom"
 NNOM_SRCS="$(ls "$NNOM"/src/core/*.c "$NNOM"/src/layers/*.c "$NNOM"/src/backends/*.c)"
 NN_SRCS="ConvolutionFunctions/arm_convolve_HWC_q7_basic_nonsquare.c ConvolutionFunctions/arm_convolve_HWC_q7_fast_nonsquare.c
