@@ -32,11 +32,11 @@ namespace edison {
 constexpr int kXchStride = 72;                 // complex units per radix-8 row: 64 + 8 keeps both transposes conflict-free
 constexpr int kXchLen = 8 * kXchStride;        // 576 >= 513
 constexpr int kMagLen = 520;
-constexpr int kMelWMax = 1024;
+constexpr int kMelWMax = 1280;
 
 template <typename R> struct alignas(2 * sizeof(R)) Cx { R x, y; };   // one 64- / 128-bit shared-memory access
 template <typename R> struct RealTraits;
-template <> struct RealTraits<float> { static constexpr int kWarps = 16; };
+template <> struct RealTraits<float> { static constexpr int kWarps = 20; };
 template <> struct RealTraits<double> { static constexpr int kWarps = 12; };
 
 template <typename R>
@@ -48,7 +48,7 @@ struct alignas(16) FloatTables {
   R mel_w[kMelWMax];           // non-zero weights filter by filter, times the spectrum scale of the mode (and the 1/2
                                // the split leaves out)
   R log_eps;
-  R window[1024];              // mfcc.c mode: Hann window of frame_len samples (mfcc.c:67-68), zero beyond
+  float window[1024];          // mfcc.c mode (fp32 only): Hann window of frame_len samples (mfcc.c:67-68), zero beyond
   R preemph, q_scale;          // mfcc.c mode: pre-emphasis factor (:180-184) and 2^dec_bits (:241)
   int mel_start[32], mel_count[32], mel_off[32];
   int use_log;
@@ -105,6 +105,14 @@ __device__ __forceinline__ double mag_from_power(double p) {
   const double s0 = p * r;
   const double e = fma(-s0, s0, p);
   return fma(e, 0.5 * r, s0);
+}
+__device__ __forceinline__ void load4(const float *p, float (&o)[4]) {
+  const float4 v = *reinterpret_cast<const float4 *>(p);
+  o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+}
+__device__ __forceinline__ void load4(const double *p, double (&o)[4]) {
+  const double2 a = *reinterpret_cast<const double2 *>(p), b = *reinterpret_cast<const double2 *>(p + 2);
+  o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
 }
 __device__ __forceinline__ float log_r(float x) { return logf(x); }
 __device__ __forceinline__ double log_r(double x) { return log(x); }
@@ -188,6 +196,7 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
     const long long clip = fr / P.frames_per_clip;
     return P.pcm + clip * P.clip_stride + (fr - clip * P.frames_per_clip) * (long long)EDISON_FRAME_LEN;
   };
+  if (lane < kMagLen - 512) W.mag[512 + lane] = (R)0;    // the padded mel chunks may read past bin 512
   uint32_t pw[16];
   const int frame_len = CMODE ? T.frame_len : 1024;
   load_frame_words<ALIGNED>(frame_base(f), lane, frame_len, pw);
@@ -284,18 +293,29 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
       W.mag[256] = (R)2 * mag_from_power(c.x * c.x + c.y * c.y);
     }
     __syncwarp();
-    // ---- mel: 4 lanes per filter, 8 filters per round
+    // ---- mel: 4 lanes per filter, 8 filters per round.  Each lane takes aligned chunks of 4 bins (128-bit reads of the
+    //      magnitudes and of the zero-padded weights); the mfcc.c mode strides through the bins and stays scalar.
     {
       const int q = lane & 3;
 #pragma unroll
       for (int round = 0; round < 4; round++) {
         const int m = 8 * round + (lane >> 2);
         const int cnt = T.mel_count[m];
-        const int bs = CMODE ? T.bin_step : 1;
-        const R *mg = W.mag + T.mel_start[m] * bs;
         const R *wt = T.mel_w + T.mel_off[m];
         R acc = (R)0;
-        for (int i = q; i < cnt; i += 4) acc = fma(mg[i * bs], wt[i], acc);
+        if (CMODE) {
+          const int bs = T.bin_step;
+          const R *mg = W.mag + T.mel_start[m] * bs;
+          for (int i = q; i < cnt; i += 4) acc = fma(mg[i * bs], wt[i], acc);
+        } else {
+          const R *mg = W.mag + T.mel_start[m];
+          for (int i = 4 * q; i < cnt; i += 16) {
+            R a[4], w[4];
+            load4(mg + i, a);
+            load4(wt + i, w);
+            acc = fma(a[0], w[0], acc); acc = fma(a[1], w[1], acc); acc = fma(a[2], w[2], acc); acc = fma(a[3], w[3], acc);
+          }
+        }
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
         if (q == 0) W.mel[m] = acc;
@@ -379,10 +399,12 @@ static int fill_tables(FloatTables<R> &T, int mode) {
       }
     }
     if (start < 0) start = 0;
-    if (off + count > kMelWMax) return -1;
-    T.mel_start[m] = start; T.mel_count[m] = count; T.mel_off[m] = off;
-    for (int i = 0; i < count; i++) T.mel_w[off + i] = (R)(w[i] * spec_scale * 0.5);
-    off += count;
+    const int a_start = start & ~3;                                  // chunks of 4 bins, 16-byte aligned in mag[]
+    const int a_count = ((start + count - a_start) + 3) & ~3;
+    if (off + a_count > kMelWMax || a_start + a_count > kMagLen) return -1;
+    T.mel_start[m] = a_start; T.mel_count[m] = a_count; T.mel_off[m] = off;
+    for (int i = 0; i < count; i++) T.mel_w[off + (start - a_start) + i] = (R)(w[i] * spec_scale * 0.5);
+    off += a_count;
   }
   for (int n = 0; n < 32; n++)
     for (int k = 0; k < 32; k++)
