@@ -7,10 +7,10 @@
 // restatement in the test tree (cube_float.py) and UNPINNED at the keras boundary.
 //
 // A CTA keeps a tile of 12 clips in shared memory through all layers (1,612 B in, 40 + 40 B out per clip).  Each thread owns
-// a register tile of 2 pixels x 16 output channels: for the two pooled layers the 2 pixels are the two conv rows under one
+// a register tile of 2 pixels x 8 output channels (4 in the last, tiny conv): for the two pooled layers the 2 pixels are the two conv rows under one
 // pooled pixel (max pool = max of the thread's own accumulators), for the others the same pixel of two clips.  Activations are
 // H,W,C with every pixel's channel vector padded by 4 floats, so the 128-bit reads of a warp (one pixel per lane) spread
-// over all banks; weights are re-laid [ky][kx][c][o] at load so a warp's weight reads are uniform 128-bit loads served by
+// over all banks; weights are re-laid [ky][kx][c][q4][g][4] at load so a warp's weight read is one contiguous 128-byte line served by
 // L1/L2 (the 172 KB model is shared by every CTA).  Why FFMA and not tensor cores: at fp32 accuracy the alternatives are
 // 3xTF32 / 3xBF16 splits on mma.sync; 0.78 MMAC per clip puts this kernel at ~1/3 of K1's time per clip already.
 #include <math.h>
@@ -25,7 +25,7 @@
 namespace edison {
 
 constexpr int kCubeClips = 12;       // clips per CTA tile (even: the unpooled layers pair clip b with b + 6)
-constexpr int kCubeThreads = 384;
+constexpr int kCubeThreads = 512;
 constexpr int kPad = 4;              // floats appended to every pixel's channel vector
 
 // activation geometry (H, W, C) after each layer
@@ -52,20 +52,20 @@ struct CubeSmem {
 };
 
 // One conv layer over the tile.  in: [clip][HIN][WIN][C + pad] (C == 1: unpadded scalars), out: [clip][HP][WO][O + opad].
-template <int HIN, int WIN, int C, int KH, int KW, int O, bool POOL, int IN_STRIDE, int OUT_STRIDE, int OPAD>
+template <int HIN, int WIN, int C, int KH, int KW, int O, int Q, bool POOL, int IN_STRIDE, int OUT_STRIDE, int OPAD>
 __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *__restrict__ out, const float *__restrict__ wgt,
                                            const float *__restrict__ bias) {
   constexpr int HO = HIN - KH + 1, WO = WIN - KW + 1;
   constexpr int HP = POOL ? HO / 2 : HO;
-  constexpr int Q = 16, G = O / Q;
+  constexpr int G = O / Q;
   constexpr int CP = C == 1 ? 1 : C + kPad;
   constexpr int OP = O + OPAD;
   constexpr int NPIX = HP * WO;
   constexpr int NB = POOL ? kCubeClips : kCubeClips / 2;
   constexpr int NITEMS = G * NB * NPIX;
   for (int item = threadIdx.x; item < NITEMS; item += kCubeThreads) {
-    const int g = item / (NB * NPIX);
-    const int rest = item - g * (NB * NPIX);
+    const int g = item % G;               // neighbouring lanes share a pixel (one broadcast read) and split its channels
+    const int rest = item / G;
     const int b = rest / NPIX, pix = rest - b * NPIX;
     const int py = pix / WO, x = pix - py * WO;
     // the two pixels of this thread
@@ -80,7 +80,7 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
     float acc0[Q], acc1[Q];
 #pragma unroll
     for (int q = 0; q < Q; q++) acc0[q] = acc1[q] = __ldg(bias + g * Q + q);
-    const float *wg = wgt + g * Q;
+    const float *wg = wgt + g * 4;        // weights are laid out [k][c][q4][g][4]: a warp's read is one contiguous line
 #pragma unroll 1
     for (int ky = 0; ky < KH; ky++) {
 #pragma unroll 1
@@ -91,7 +91,7 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
           const float a0 = q0[0], a1 = q1[0];
 #pragma unroll
           for (int q4 = 0; q4 < Q / 4; q4++) {
-            const float4 w = __ldg(reinterpret_cast<const float4 *>(wk) + q4);
+            const float4 w = __ldg(reinterpret_cast<const float4 *>(wk + q4 * G * 4));
             acc0[4 * q4 + 0] = fmaf(a0, w.x, acc0[4 * q4 + 0]); acc1[4 * q4 + 0] = fmaf(a1, w.x, acc1[4 * q4 + 0]);
             acc0[4 * q4 + 1] = fmaf(a0, w.y, acc0[4 * q4 + 1]); acc1[4 * q4 + 1] = fmaf(a1, w.y, acc1[4 * q4 + 1]);
             acc0[4 * q4 + 2] = fmaf(a0, w.z, acc0[4 * q4 + 2]); acc1[4 * q4 + 2] = fmaf(a1, w.z, acc1[4 * q4 + 2]);
@@ -105,10 +105,10 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
             const float a0[4] = {v0.x, v0.y, v0.z, v0.w}, a1[4] = {v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
             for (int cc = 0; cc < 4; cc++) {
-              const float4 *wr = reinterpret_cast<const float4 *>(wk + (4 * c4 + cc) * O);
+              const float *wr = wk + (4 * c4 + cc) * O;
 #pragma unroll
               for (int q4 = 0; q4 < Q / 4; q4++) {
-                const float4 w = __ldg(wr + q4);
+                const float4 w = __ldg(reinterpret_cast<const float4 *>(wr + q4 * G * 4));
                 acc0[4 * q4 + 0] = fmaf(a0[cc], w.x, acc0[4 * q4 + 0]); acc1[4 * q4 + 0] = fmaf(a1[cc], w.x, acc1[4 * q4 + 0]);
                 acc0[4 * q4 + 1] = fmaf(a0[cc], w.y, acc0[4 * q4 + 1]); acc1[4 * q4 + 1] = fmaf(a1[cc], w.y, acc1[4 * q4 + 1]);
                 acc0[4 * q4 + 2] = fmaf(a0[cc], w.z, acc0[4 * q4 + 2]); acc1[4 * q4 + 2] = fmaf(a1[cc], w.z, acc1[4 * q4 + 2]);
@@ -158,13 +158,13 @@ cube_f32_kernel(const CubeModel *__restrict__ M, const float *__restrict__ net_i
       S.a[b][j] = b < nc ? __ldg(net_in + (c0 + b) * EDISON_NET_IN + j) : 0.f;
     }
     __syncthreads();
-    conv_layer<31, 13, 1, 5, 5, 16, true, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], M->w1, M->b1);
+    conv_layer<31, 13, 1, 5, 5, 16, 8, true, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], M->w1, M->b1);
     __syncthreads();
-    conv_layer<13, 9, 16, 3, 3, 32, true, kBufB, kBufA, kPad>(&S.b[0][0], &S.a[0][0], M->w2, M->b2);
+    conv_layer<13, 9, 16, 3, 3, 32, 8, true, kBufB, kBufA, kPad>(&S.b[0][0], &S.a[0][0], M->w2, M->b2);
     __syncthreads();
-    conv_layer<5, 7, 32, 3, 3, 64, false, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], M->w3, M->b3);
+    conv_layer<5, 7, 32, 3, 3, 64, 8, false, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], M->w3, M->b3);
     __syncthreads();
-    conv_layer<3, 5, 64, 3, 3, 32, false, kBufB, kBufA, 0>(&S.b[0][0], &S.a[0][0], M->w4, M->b4);
+    conv_layer<3, 5, 64, 3, 3, 32, 4, false, kBufB, kBufA, 0>(&S.b[0][0], &S.a[0][0], M->w4, M->b4);
     __syncthreads();
     // dense (forward_dense): one thread per (clip, class)
     if (threadIdx.x < kCubeClips * EDISON_N_CLASSES) {
@@ -227,9 +227,12 @@ static int cube_load(const char *path) {
     if (off + 4 * (nw + co) > raw.size()) { delete h; return ctx_fail(EDISON_E_DATA, "%s: truncated", path); }
     const float *w = reinterpret_cast<const float *>(&raw[off]);
     if (hd[0] == 1) {
-      for (size_t o = 0; o < co; o++)          // O,H,W,I (kws.c strides) -> [ky][kx][c][o]
+      const size_t Q = l == 3 ? 4 : 8, G = co / Q;     // per-thread channel tile of each layer (conv_layer<..., Q, ...>)
+      for (size_t o = 0; o < co; o++) {                // O,H,W,I (kws.c strides) -> [ky][kx][c][q4][g][4], o = g*Q + 4*q4 + j
+        const size_t g = o / Q, q4 = (o % Q) / 4, j = o % 4;
         for (size_t k = 0; k < kh * kw; k++)
-          for (size_t c = 0; c < ci; c++) wdst[l][(k * ci + c) * co + o] = w[(o * kh * kw + k) * ci + c];
+          for (size_t c = 0; c < ci; c++) wdst[l][(k * ci + c) * co + (q4 * G + g) * 4 + j] = w[(o * kh * kw + k) * ci + c];
+      }
     } else {
       memcpy(wdst[l], w, 4 * nw);
     }
