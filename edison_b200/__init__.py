@@ -13,6 +13,7 @@ from .capi import (  # noqa: F401
     N_FRAMES,
     MFCC_F32_HOST,
     MfccC,
+    Model,
     MFCC_F32_MCU,
     MFCC_F32_MCU_LOG,
     N_MEL,

@@ -61,6 +61,11 @@ def lib():
         L.mfcc_compute.restype = None
         L.mfcc_delete.argtypes = [vp]
         L.mfcc_delete.restype = None
+        L.edison_model_load.argtypes = [ctypes.c_char_p, ctypes.POINTER(vp)]
+        L.edison_model_free.argtypes = [vp]
+        L.edison_model_free.restype = None
+        L.edison_model_shape.argtypes = [vp] + [ctypes.POINTER(ci)] * 4
+        L.edison_model_infer.argtypes = [vp, vp, sz, vp, vp]
         L.edison_infer_f32_batch.argtypes = [vp, sz, vp, vp]
         L.edison_infer_f32_batch_dev.argtypes = [vp, sz, vp, vp, vp]
         for t in ("f32", "f64"):
@@ -190,6 +195,37 @@ def mfcc_float_batch(pcm, mode=MFCC_F32_HOST, dtype=np.float64):
     mfcc_utils.mfcc does (frame_count = 1 + (n - 1024) // 1024)."""
     pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
     return mfcc_float_clips(pcm, pcm.size // FRAME_LEN, 1, FRAME_LEN, mode, dtype)
+
+
+class Model:
+    """Any NNoM int8 model of the sequential conv/dense family, from a blob made by tools/convert_nnom_weights.py."""
+
+    def __init__(self, blob_path):
+        self._h = ctypes.c_void_p()
+        check(lib().edison_model_load(os.fsencode(blob_path), ctypes.byref(self._h)), "edison_model_load")
+        d = [ctypes.c_int() for _ in range(4)]
+        check(lib().edison_model_shape(self._h, *[ctypes.byref(v) for v in d]), "edison_model_shape")
+        self.in_shape = (d[0].value, d[1].value, d[2].value)
+        self.in_size = d[0].value * d[1].value * d[2].value
+        self.n_out = d[3].value
+
+    def infer(self, x):
+        x = np.ascontiguousarray(x, dtype=np.int8).reshape(-1, self.in_size)
+        lg = np.empty((x.shape[0], self.n_out), dtype=np.int8)
+        sm = np.empty((x.shape[0], self.n_out), dtype=np.int8)
+        check(lib().edison_model_infer(self._h, _p(x), x.shape[0], _p(lg), _p(sm)), "edison_model_infer")
+        return lg, sm
+
+    def close(self):
+        if self._h:
+            lib().edison_model_free(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
 
 
 class MfccC:

@@ -156,6 +156,17 @@ void mfcc_compute(mfcc_t *mfcc, const int16_t *audio_data, int8_t *mfcc_out);
 int edison_infer_f32_batch(const float *net_in, size_t n, float *logits, float *softmax);
 int edison_infer_f32_batch_dev(const float *d_net_in, size_t n, float *d_logits, float *d_softmax, void *stream);
 
+/* ---- section 2d: any NNoM int8 model of the sequential conv/dense family (nnom_model_create() of a generated weights.h,
+ * e.g. firmware/src/ai/nnom/kws_nnom/weights.h:138-161 or the upstream keyword_spotting example), converted by
+ * tools/convert_nnom_weights.py.  Layer vocabulary: Input, Conv2D valid/stride 1, ReLU, MaxPool (p,1), Dense, Softmax.
+ * in[n][in_h*in_w*in_c] int8 -> logits[n][n_out] (last Dense output), softmax[n][n_out] (mode of edison_set_softmax_mode);
+ * host or device pointers (device pointers 4-byte aligned).  Bit-exact with the NNoM runtime; generic kernels, not K2. */
+typedef struct edison_model edison_model;
+int edison_model_load(const char *blob_path, edison_model **out);
+void edison_model_free(edison_model *m);
+int edison_model_shape(const edison_model *m, int *in_h, int *in_w, int *in_c, int *n_out);
+int edison_model_infer(edison_model *m, const int8_t *in, size_t n, int8_t *logits, int8_t *softmax);
+
 /* ---- section 3: device-resident variants (all pointers are device pointers; stream is a
  *      cudaStream_t passed as void*, NULL = the library's stream; asynchronous) --------------- */
 int edison_mfcc_q15_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip,

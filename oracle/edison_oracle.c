@@ -441,7 +441,7 @@ void eo_softmax_q7(const int8_t *in, int n, int8_t *out, int mode)
 static int forward(const int8_t *in403, int8_t *logits, int8_t *softmax, int mode, int8_t *taps)
 {
   if (!n_layers) return -1;
-  static __thread int8_t bufA[8192], bufB[8192];
+  static __thread int8_t bufA[65536], bufB[65536];
   int H = (int)net_h, W = (int)net_w, C = (int)net_c, tap = 0;
   memcpy(bufA, in403, (size_t)(H * W * C));
   int8_t *cur = bufA, *nxt = bufB, *t;
@@ -466,19 +466,23 @@ static int forward(const int8_t *in403, int8_t *logits, int8_t *softmax, int mod
       for (uint32_t r = 0; r < L->cout; r++) {
         int32_t acc = (int32_t)((uint32_t)(int32_t)L->b[r] << L->lshift) + (1 << (L->rshift - 1));
         for (int j = 0; j < n_in; j++) acc += cur[j] * L->w[r * (uint32_t)n_in + (uint32_t)j];
-        nxt[r] = (int8_t)ssat8(acc >> L->rshift);
+        int32_t v = ssat8(acc >> L->rshift);
+        if (L->relu && v < 0) v = 0;
+        nxt[r] = (int8_t)v;
       }
       H = 1; W = 1; C = (int)L->cout;
       t = cur; cur = nxt; nxt = t;
       if (taps) memcpy(taps + 4096 * tap++, cur, (size_t)C);
     }
   }
-  if (logits) memcpy(logits, cur, EO_N_CLASSES);
+  const int n_out = H * W * C;      /* 10 for the reference model */
+  if (n_out > 256) return -3;
+  if (logits) memcpy(logits, cur, (size_t)n_out);
   if (softmax || taps) {
-    int8_t sm[EO_N_CLASSES];
-    eo_softmax_q7(cur, EO_N_CLASSES, sm, mode);
-    if (softmax) memcpy(softmax, sm, EO_N_CLASSES);
-    if (taps) memcpy(taps + 4096 * tap++, sm, EO_N_CLASSES);
+    int8_t sm[256];
+    eo_softmax_q7(cur, n_out, sm, mode);
+    if (softmax) memcpy(softmax, sm, (size_t)n_out);
+    if (taps) memcpy(taps + 4096 * tap++, sm, (size_t)n_out);
   }
   return tap;
 }
@@ -497,6 +501,23 @@ int eo_nnom_forward_batch(const int8_t *in, size_t n, int8_t *logits, int8_t *so
   }
   return 0;
 }
+
+/* any model of the blob's layer family (tools/convert_nnom_weights.py): in [n][in_h*in_w*in_c], outputs [n][n_out] */
+int eo_nnom_forward_generic(const int8_t *in, size_t n, int8_t *logits, int8_t *softmax, int mode)
+{
+  if (!n_layers) return -1;
+  const size_t in_size = (size_t)net_h * net_w * net_c;
+  const eo_layer *last = &layers[n_layers - 1];
+  if (last->kind != 2) return -4;
+  const size_t n_out = last->cout;
+  for (size_t i = 0; i < n; i++) {
+    int r = forward(in + i * in_size, logits ? logits + i * n_out : 0, softmax ? softmax + i * n_out : 0, mode, 0);
+    if (r < 0) return r;
+  }
+  return 0;
+}
+int eo_nnom_in_size(void) { return (int)(net_h * net_w * net_c); }
+int eo_nnom_out_size(void) { return n_layers ? (int)layers[n_layers - 1].cout : 0; }
 
 int eo_nnom_forward_layers(const int8_t *in403, int8_t *buf8x4096)
 {

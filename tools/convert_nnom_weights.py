@@ -113,7 +113,9 @@ def main():
         out += struct.pack("<9I", L["kind"], L["cout"], L["kh"], L["kw"], L["cin"], L["rshift"], L["lshift"], L["relu"], L["pool"])
         out += L["w"].tobytes() + L["b"].tobytes()
         out += b"\0" * (-len(out) % 4)
-    out += struct.pack("<iiiIII", ints["NNOM_INPUT_SCALE"], ints["NNOM_INPUT_MIN"], ints["NNOM_INPUT_MAX"], *in_shape)
+    # the NNOM_INPUT_* macros are an addition of the reference's own generator; upstream NNoM headers lack them
+    out += struct.pack("<iiiIII", ints.get("NNOM_INPUT_SCALE", 1), ints.get("NNOM_INPUT_MIN", -128), ints.get("NNOM_INPUT_MAX", 127),
+                       *in_shape)
     open(dst, "wb").write(out)
     for L in layers:
         print("%-10s kind=%d cout=%d k=%dx%d cin=%d rshift=%d lshift=%d relu=%d pool=%d" %
