@@ -168,7 +168,9 @@ int edison_model_shape(const edison_model *m, int *in_h, int *in_w, int *in_c, i
 int edison_model_infer(edison_model *m, const int8_t *in, size_t n, int8_t *logits, int8_t *softmax);
 
 /* ---- section 3: device-resident variants (all pointers are device pointers; stream is a
- *      cudaStream_t passed as void*, NULL = the library's stream; asynchronous) --------------- */
+ *      cudaStream_t passed as void*, NULL = the library's own non-blocking stream; asynchronous.
+ *      Work queued on other streams is NOT ordered against the library's stream: pass the stream the
+ *      inputs were produced on, or synchronise first) ------------------------------------------ */
 int edison_mfcc_q15_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip,
                               size_t clip_stride_samples, int16_t *d_mfcc, int8_t *d_net_in,
                               void *stream);
