@@ -89,6 +89,10 @@ def lib():
         L.aiGetKeywordFromIndex.argtypes = [ctypes.c_uint32]
         L.aiGetKeywordCount.restype = ctypes.c_uint32
         L.edison_net_input_window.restype = ctypes.POINTER(ctypes.c_int8)
+        L.aiGetInputShape.argtypes = [ctypes.POINTER(ctypes.c_uint16)] * 2
+        L.aiGetInputShape.restype = None
+        L.mfccToNetInput.argtypes = [ctypes.POINTER(ctypes.c_int16), ctypes.c_uint16, ctypes.c_uint16, ctypes.c_uint32]
+        L.mfccToNetInput.restype = None
         _lib = L
     return _lib
 
