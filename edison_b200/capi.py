@@ -77,6 +77,7 @@ def lib():
         L.edison_streams_close.restype = None
         L.edison_streams_push_hop.argtypes = [vp, vp, vp, vp, vp]
         L.edison_streams_push_hop_dev.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.edison_streams_set_incremental.argtypes = [vp, ci]
         L.edison_streams_hops.argtypes = [vp]
         L.edison_streams_hops.restype = ctypes.c_ulonglong
         L.edison_streams_window.argtypes = [vp, sz, vp]
@@ -270,10 +271,11 @@ class Streams:
     push_hop(pcm[n,1024]) -> (softmax int8 [n,10], filt float32 [n,10], detect int32 [n]); detect is the class index when
     the filtered maximum exceeds 0.5, -1 when it does not, -2 while the 31-row window is still filling."""
 
-    def __init__(self, n):
+    def __init__(self, n, incremental=True):
         self.n = int(n)
         self._h = ctypes.c_void_p()
         check(lib().edison_streams_open(self.n, ctypes.byref(self._h)), "edison_streams_open")
+        check(lib().edison_streams_set_incremental(self._h, int(bool(incremental))), "edison_streams_set_incremental")
 
     def close(self):
         if self._h:

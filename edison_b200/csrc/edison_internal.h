@@ -33,6 +33,14 @@ cudaError_t nnom_configure(void);
 cudaError_t launch_nnom_q7(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits,
                            int8_t *softmax, int softmax_mode, int sm_count, cudaStream_t stream);
 
+// incremental sliding-window inference (one new row per layer and hop); state rings live in one device allocation
+struct NnomIncrState { int8_t *c1, *p1, *c2, *p2, *c3; };
+size_t nnom_incr_state_bytes(long long n_streams);
+void nnom_incr_state_bind(NnomIncrState *st, int8_t *base, long long n_streams);
+cudaError_t launch_nnom_q7_incremental(const NnomModel *model, const int8_t *window, const NnomIncrState &st, long long n,
+                                       long long newest_row, int8_t *logits, int8_t *softmax, int softmax_mode, int sm_count,
+                                       cudaStream_t stream);
+
 // ---- debug kernels --------------------------------------------------------------------------------
 cudaError_t launch_debug_sqrt(const int32_t *d_in, size_t n, int32_t *d_out, cudaStream_t stream);
 cudaError_t launch_debug_mag_sweep(uint32_t lo, uint32_t hi, const uint32_t *d_exc, unsigned long long *d_out2,

@@ -20,6 +20,7 @@
 // activation buffers (implicit im2col; C = 32 / 64 buffers are XOR-swizzled per pixel so those loads
 // are bank-conflict free), B fragments are pre-packed in fragment order at model load.
 // Epilogue, fused: >> out_rshift, SSAT8, ReLU, (2x1 max pool), int8 store in the next layer's layout.
+#include <stddef.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -299,7 +300,252 @@ __global__ void __launch_bounds__(kNetThreads, 2) nnom_q7_kernel(const NnomModel
   }
 }
 
+// ---- incremental sliding-window inference (app.c:706-719 advances the window one row per hop) ----------
+// A window that starts at global row s is  conv1 rows s..s+26 -> pool pairs (s+2i, s+2i+1) -> conv2 rows on pooled rows
+// (a, a+2, a+4), a = s+2i -> pool pairs (a, a+2), a = s+4j -> conv3 on (a, a+4, a+8) -> conv4 on c3[s], c3[s+4], c3[s+8].
+// All of these are functions of GLOBAL row indices, so one hop (newest input row r, window start s = r-30) adds exactly one new
+// row per layer:  c1[r-4],  p1[r-5] = max(c1[r-5], c1[r-4]),  c2[r-9] = f(p1[r-9], p1[r-7], p1[r-5]),
+// p2[r-11] = max(c2[r-11], c2[r-9]),  c3[r-19] = f(p2[r-19], p2[r-15], p2[r-11]),  and the output needs
+// c3[r-30], c3[r-26], c3[r-22] from earlier hops.  Rows live in HBM rings [slot][stream][row bytes] (slot = index mod depth;
+// depths 1, 5, 3, 9, 12 -> 7,392 B per stream); a hop moves ~3 KB per stream and does 184 k MAC instead of 785 k.
+// Integer convolutions are position-local and every pooling pair is anchored at the window start, so the result is
+// bit-identical to running K2 on the assembled window (tests/test_gpu_streams.py runs both).
+constexpr int kIn5Stride = 80;                     // 5 rows x 13 bytes per stream, padded
+constexpr int kRowC1 = 9 * kC1, kRowC2 = 7 * kC2, kRowC3 = 5 * kC3;      // 144, 224, 320 bytes
+constexpr int kDepthP1 = 5, kDepthC2 = 3, kDepthP2 = 9, kDepthC3 = 12;
+
+struct IncrSmem {
+  NnomModel M;
+  alignas(16) int8_t in5[kNC * kIn5Stride + 128];   // conv1 reads zero-weight taps past the 5th row
+  alignas(16) int8_t c1n[kNC * kRowC1];             // new conv1 row, plain [stream][9][16]
+  alignas(16) int8_t c1p[kNC * kRowC1];             // c1[r-5], stored by the previous hop
+  alignas(16) int8_t c2o[kNC * kRowC2];             // c2[r-11], stored two hops ago
+  alignas(16) int8_t img2[kNC * 3 * kRowC1];        // p1[r-9], p1[r-7], p1[r-5]: [stream][3][9][16]
+  alignas(16) int8_t c2n[kNC * kRowC2];             // new conv2 row, plain [stream][7][32]
+  alignas(16) int8_t img3[kNC * 3 * kRowC2];        // p2 rows, act_word<32> layout over P = stream*21 + row*7 + x
+  alignas(16) int8_t c3n[kNC * kRowC3];             // new conv3 row, plain [stream][5][64]
+  alignas(16) int8_t img4[kNC * 3 * kRowC3];        // c3 rows, act_word<64> layout over P = stream*15 + row*5 + x
+  alignas(16) int8_t act4[kNC * kDenseIn];
+  alignas(16) int8_t lg[kNC * 16];
+};
+
+// conv1 on a 5-row image per stream: one output row (9 pixels x 16 channels, ReLU), no pooling; rows g / g+8 of a tile are
+// two different pixels.  Same K indexing as conv1_mma (ky * 8 + kx, zero weights beyond 5x5).
+__device__ __forceinline__ void conv1_row_mma(const int8_t *in, int8_t *out, const uint2 *frag, const int *seed, int rs, int ns) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+  const int rows_total = ns * 9, n_tiles = (rows_total + 15) / 16;
+  const uint32_t *inw = reinterpret_cast<const uint32_t *>(in);
+  for (int tile = warp; tile < n_tiles; tile += kNetWarps) {
+    const int q0 = tile * 16 + g, q1 = q0 + 8;
+    const bool v0 = q0 < rows_total, v1 = q1 < rows_total;
+    const int qa = v0 ? q0 : 0, qb = v1 ? q1 : 0;
+    const int base_a = (qa / 9) * kIn5Stride + qa % 9, base_b = (qb / 9) * kIn5Stride + qb % 9;
+    int acc[2][4];
+#pragma unroll
+    for (int n = 0; n < 2; n++) {
+      acc[n][0] = acc[n][2] = seed[8 * n + 2 * t];
+      acc[n][1] = acc[n][3] = seed[8 * n + 2 * t + 1];
+    }
+#pragma unroll
+    for (int ks = 0; ks < 2; ks++) {
+      uint32_t a[4];
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const int ky = 4 * ks + 2 * h + (t >> 1), kx0 = 4 * (t & 1);
+        a[2 * h] = ld_unaligned32(inw, base_a + ky * kInW + kx0);
+        a[2 * h + 1] = ld_unaligned32(inw, base_b + ky * kInW + kx0);
+      }
+      mma_s8(acc[0], a, frag[(ks * 2 + 0) * 32 + lane]);
+      mma_s8(acc[1], a, frag[(ks * 2 + 1) * 32 + lane]);
+    }
+#pragma unroll
+    for (int n = 0; n < 2; n++) {
+      if (v0) reinterpret_cast<uint16_t *>(out)[(q0 * kC1 + 8 * n + 2 * t) >> 1] = (uint16_t)(q7_relu(acc[n][0], rs) | (q7_relu(acc[n][1], rs) << 8));
+      if (v1) reinterpret_cast<uint16_t *>(out)[(q1 * kC1 + 8 * n + 2 * t) >> 1] = (uint16_t)(q7_relu(acc[n][2], rs) | (q7_relu(acc[n][3], rs) << 8));
+    }
+  }
+}
+
+__device__ __forceinline__ int ring_slot(long long index, int depth) { return (int)(((index % depth) + depth) % depth); }
+__device__ __forceinline__ uint32_t max_s8x4(uint32_t a, uint32_t b) { return __vmaxs4(a, b); }
+
+// window: [n][403] after this hop's push (rows r-30..r).  r = index of the newest row (hop count - 1).
+__global__ void __launch_bounds__(kNetThreads, 2)
+nnom_q7_incr_kernel(const NnomModel *model, const int8_t *window, NnomIncrState st, long long n, long long r, int8_t *logits,
+                    int8_t *softmax, int softmax_mode) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  IncrSmem &S = *reinterpret_cast<IncrSmem *>(smem_raw);
+  {
+    const int4 *src = reinterpret_cast<const int4 *>(model);
+    int4 *dst = reinterpret_cast<int4 *>(&S.M);
+    for (int i = threadIdx.x; i < (int)(sizeof(NnomModel) / 16); i += kNetThreads) dst[i] = src[i];
+    for (int i = threadIdx.x; i < (int)sizeof(S.in5) / 4; i += kNetThreads) reinterpret_cast<uint32_t *>(S.in5)[i] = 0;
+  }
+  const NnomModel &M = S.M;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+  const int tid = threadIdx.x;
+  // ring slots of this hop
+  const int sp1_new = ring_slot(r - 5, kDepthP1), sp1_a = ring_slot(r - 9, kDepthP1), sp1_b = ring_slot(r - 7, kDepthP1);
+  const int sc2_new = ring_slot(r - 9, kDepthC2), sc2_old = ring_slot(r - 11, kDepthC2);
+  const int sp2_new = ring_slot(r - 11, kDepthP2), sp2_a = ring_slot(r - 19, kDepthP2), sp2_b = ring_slot(r - 15, kDepthP2);
+  const int sc3_new = ring_slot(r - 19, kDepthC3);
+  const int sc3_0 = ring_slot(r - 30, kDepthC3), sc3_1 = ring_slot(r - 26, kDepthC3), sc3_2 = ring_slot(r - 22, kDepthC3);
+  const long long n_tiles = (n + kNC - 1) / kNC;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long c0 = tile * kNC;
+    const int ns = (int)min((long long)kNC, n - c0);
+    __syncthreads();
+    // (1) everything this hop reads from HBM, issued up front as independent 128-bit loads (the kernel is latency bound):
+    //     per stream 60 + 28 + 18 + 9 + 14 = 129 chunks: img4 rows 0..2, img3 rows 0..1, img2 rows 0..1, c1[r-5], c2[r-11]
+    {
+      constexpr int kJobs = 129, kIter = (kNC * kJobs + kNetThreads - 1) / kNetThreads;
+      int4 v[kIter];
+      int dst[kIter];        // int4 index into the shared struct, -1 = nothing
+#pragma unroll
+      for (int it = 0; it < kIter; it++) {
+        const int j = tid + it * kNetThreads;
+        const int s = j / kJobs, k = j - s * kJobs;
+        dst[it] = -1;
+        if (s < ns) {
+          const long long cs = c0 + s;
+          const int4 *src;
+          if (k < 60) {
+            const int row = k / 20, c = k - row * 20, P = s * 15 + row * 5 + (c >> 2);
+            const int slot = row == 0 ? sc3_0 : (row == 1 ? sc3_1 : sc3_2);
+            src = reinterpret_cast<const int4 *>(st.c3) + ((long long)slot * n + cs) * 20 + c;
+            dst[it] = (int)(offsetof(IncrSmem, img4) / 16) + P * 4 + ((c & 3) ^ ((P >> 1) & 3));
+          } else if (k < 88) {
+            const int kk = k - 60, row = kk / 14, c = kk - row * 14, P = s * 21 + row * 7 + (c >> 1);
+            src = reinterpret_cast<const int4 *>(st.p2) + ((long long)(row ? sp2_b : sp2_a) * n + cs) * 14 + c;
+            dst[it] = (int)(offsetof(IncrSmem, img3) / 16) + P * 2 + ((c & 1) ^ ((P >> 2) & 1));
+          } else if (k < 106) {
+            const int kk = k - 88, row = kk / 9, c = kk - row * 9;
+            src = reinterpret_cast<const int4 *>(st.p1) + ((long long)(row ? sp1_b : sp1_a) * n + cs) * 9 + c;
+            dst[it] = (int)(offsetof(IncrSmem, img2) / 16) + (s * 27 + row * 9) + c;
+          } else if (k < 115) {
+            src = reinterpret_cast<const int4 *>(st.c1) + cs * 9 + (k - 106);
+            dst[it] = (int)(offsetof(IncrSmem, c1p) / 16) + s * 9 + (k - 106);
+          } else {
+            src = reinterpret_cast<const int4 *>(st.c2) + ((long long)sc2_old * n + cs) * 14 + (k - 115);
+            dst[it] = (int)(offsetof(IncrSmem, c2o) / 16) + s * 14 + (k - 115);
+          }
+          v[it] = __ldg(src);
+        }
+      }
+      // newest five input rows of each stream: window rows 26..30 (65 bytes at an odd offset: byte loads)
+      constexpr int kInIter = (kNC * 65 + kNetThreads - 1) / kNetThreads;
+      int8_t b[kInIter];
+#pragma unroll
+      for (int it = 0; it < kInIter; it++) {
+        const int i = tid + it * kNetThreads, s = i / 65, j = i - s * 65;
+        b[it] = s < ns ? window[(c0 + s) * EDISON_NET_IN + 26 * 13 + j] : (int8_t)0;
+      }
+#pragma unroll
+      for (int it = 0; it < kInIter; it++) {
+        const int i = tid + it * kNetThreads, s = i / 65, j = i - s * 65;
+        if (s < kNC) S.in5[s * kIn5Stride + j] = b[it];
+      }
+#pragma unroll
+      for (int it = 0; it < kIter; it++)
+        if (dst[it] >= 0) reinterpret_cast<int4 *>(&S)[dst[it]] = v[it];
+    }
+    __syncthreads();
+    // (2) conv1 row r-4
+    conv1_row_mma(S.in5, S.c1n, &M.f1[0][0][0], M.seed1, M.rs[0], ns);
+    __syncthreads();
+    // (3) p1[r-5] = max(c1[r-5], c1[r-4]) -> img2 row 2 and the ring; c1[r-4] becomes the stored previous row
+    for (int i = tid; i < ns * 9; i += kNetThreads) {
+      const int s = i / 9, c = i - s * 9;
+      const int4 cur = reinterpret_cast<const int4 *>(S.c1n)[i], prv = reinterpret_cast<const int4 *>(S.c1p)[i];
+      const int4 m = make_int4((int)max_s8x4(prv.x, cur.x), (int)max_s8x4(prv.y, cur.y), (int)max_s8x4(prv.z, cur.z), (int)max_s8x4(prv.w, cur.w));
+      reinterpret_cast<int4 *>(st.c1)[(c0 + s) * 9 + c] = cur;
+      reinterpret_cast<int4 *>(st.p1)[((long long)sp1_new * n + c0 + s) * 9 + c] = m;
+      reinterpret_cast<int4 *>(S.img2)[s * 27 + 18 + c] = m;
+    }
+    __syncthreads();
+    // (4) conv2 row r-9 on (p1[r-9], p1[r-7], p1[r-5])
+    conv3x3_mma<9, 27, kC1, kC2, 1, 7, false, false, 1>(S.img2, S.c2n, &M.f2[0][0][0], M.seed2, M.rs[1], ns);
+    __syncthreads();
+    // (5) p2[r-11] = max(c2[r-11], c2[r-9]); store c2[r-9]
+    for (int i = tid; i < ns * 14; i += kNetThreads) {
+      const int s = i / 14, c = i - s * 14, P = s * 21 + 14 + (c >> 1);
+      const int4 cur = reinterpret_cast<const int4 *>(S.c2n)[i], old = reinterpret_cast<const int4 *>(S.c2o)[i];
+      const int4 m = make_int4((int)max_s8x4(old.x, cur.x), (int)max_s8x4(old.y, cur.y), (int)max_s8x4(old.z, cur.z), (int)max_s8x4(old.w, cur.w));
+      reinterpret_cast<int4 *>(st.c2)[((long long)sc2_new * n + c0 + s) * 14 + c] = cur;
+      reinterpret_cast<int4 *>(st.p2)[((long long)sp2_new * n + c0 + s) * 14 + c] = m;
+      reinterpret_cast<int4 *>(S.img3)[P * 2 + ((c & 1) ^ ((P >> 2) & 1))] = m;
+    }
+    __syncthreads();
+    // (6) conv3 row r-19 on (p2[r-19], p2[r-15], p2[r-11]); conv4 on the three stored c3 rows (independent of (6))
+    conv3x3_mma<7, 21, kC2, kC3, 1, 5, false, false, 2>(S.img3, S.c3n, &M.f3[0][0][0], M.seed3, M.rs[2], ns);
+    conv3x3_mma<5, 15, kC3, kC4, 1, 3, false, false, 4>(S.img4, S.act4, &M.f4[0][0][0], M.seed4, M.rs[3], ns);
+    __syncthreads();
+    for (int i = tid; i < ns * 20; i += kNetThreads) {
+      const int s = i / 20, c = i - s * 20;
+      reinterpret_cast<int4 *>(st.c3)[((long long)sc3_new * n + c0 + s) * 20 + c] = reinterpret_cast<const int4 *>(S.c3n)[i];
+    }
+    // (7) dense + softmax, as in nnom_q7_kernel
+    if (warp < 2) {
+      const uint32_t *aw = reinterpret_cast<const uint32_t *>(S.act4);
+      const int r0 = g < ns ? g : 0, r1 = g + 8 < ns ? g + 8 : 0;
+      int acc[4];
+      acc[0] = acc[2] = M.seedd[8 * warp + 2 * t];
+      acc[1] = acc[3] = M.seedd[8 * warp + 2 * t + 1];
+#pragma unroll
+      for (int ks = 0; ks < 3; ks++) {
+        uint32_t a[4];
+        a[0] = aw[r0 * 24 + 8 * ks + t];     a[1] = aw[r1 * 24 + 8 * ks + t];
+        a[2] = aw[r0 * 24 + 8 * ks + 4 + t]; a[3] = aw[r1 * 24 + 8 * ks + 4 + t];
+        mma_s8(acc, a, M.fd[ks][warp][lane]);
+      }
+      const int rs = M.rs[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int clip = g + 8 * (j >> 1), col = 8 * warp + 2 * t + (j & 1);
+        if (clip < ns && col < kDenseOut) {
+          const int8_t v = (int8_t)ssat8(acc[j] >> rs);
+          S.lg[clip * 16 + col] = v;
+          if (logits) logits[(c0 + clip) * kDenseOut + col] = v;
+        }
+      }
+    }
+    __syncthreads();
+    if (softmax && tid < ns) {
+      int8_t sm[kDenseOut];
+      softmax_q7(&S.lg[tid * 16], sm, softmax_mode);
+      for (int i = 0; i < kDenseOut; i++) softmax[(c0 + tid) * kDenseOut + i] = sm[i];
+    }
+  }
+}
+
+size_t nnom_incr_state_bytes(long long n) {
+  return (size_t)n * (kRowC1 * (1 + kDepthP1) + kRowC2 * (kDepthC2 + kDepthP2) + kRowC3 * kDepthC3);
+}
+
+void nnom_incr_state_bind(NnomIncrState *st, int8_t *base, long long n) {
+  st->c1 = base;
+  st->p1 = st->c1 + (size_t)n * kRowC1;
+  st->c2 = st->p1 + (size_t)n * kRowC1 * kDepthP1;
+  st->p2 = st->c2 + (size_t)n * kRowC2 * kDepthC2;
+  st->c3 = st->p2 + (size_t)n * kRowC2 * kDepthP2;
+}
+
+cudaError_t launch_nnom_q7_incremental(const NnomModel *model, const int8_t *window, const NnomIncrState &st, long long n,
+                                       long long newest_row, int8_t *logits, int8_t *softmax, int softmax_mode, int sm_count,
+                                       cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  const long long n_tiles = (n + kNC - 1) / kNC;
+  long long ctas = n_tiles < (long long)sm_count * 2 ? n_tiles : (long long)sm_count * 2;
+  nnom_q7_incr_kernel<<<(unsigned)ctas, kNetThreads, sizeof(IncrSmem), stream>>>(model, window, st, n, newest_row, logits, softmax,
+                                                                                softmax_mode);
+  count_launch();
+  return cudaGetLastError();
+}
+
 cudaError_t nnom_configure(void) {
+  cudaError_t e = cudaFuncSetAttribute(nnom_q7_incr_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IncrSmem));
+  if (e != cudaSuccess) return e;
+
   return cudaFuncSetAttribute(nnom_q7_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NetSmem));
 }
 

@@ -19,6 +19,9 @@ struct edison_streams {
   float *d_filt;       // [n][10]
   int32_t *d_detect;   // [n]
   int16_t *d_pcm;      // [n][1024] staging for host callers
+  int8_t *d_incr;      // ring state of the incremental net (nnom_q7_kernel.cu), 7,392 B per stream
+  edison::NnomIncrState incr;
+  int incremental;     // 1: one new row per layer and hop (default); 0: the whole window through K2 every hop
 };
 
 namespace edison {
@@ -90,8 +93,13 @@ static int push_dev(edison_streams *s, const CtxView &c, const int16_t *d_pcm, i
   count_launch();
   s->hops++;
   // the firmware fills the window (31 frames), waits for one more frame, then starts inferring (app.c:311-318)
-  if (s->hops > EDISON_N_FRAMES) {
-    CUS(launch_nnom_q7(c.model, s->d_window, (long long)n, nullptr, s->d_softmax, c.softmax_mode, c.sm_count, st));
+  const bool infer = s->hops > EDISON_N_FRAMES;
+  if (s->incremental)   // runs from the first hop on: it is what fills the rings
+    CUS(launch_nnom_q7_incremental(c.model, s->d_window, s->incr, (long long)n, (long long)s->hops - 1, nullptr,
+                                   infer ? s->d_softmax : nullptr, c.softmax_mode, c.sm_count, st));
+  if (infer) {
+    if (!s->incremental)
+      CUS(launch_nnom_q7(c.model, s->d_window, (long long)n, nullptr, s->d_softmax, c.softmax_mode, c.sm_count, st));
     stream_post_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s->d_softmax, s->d_filt, s->d_detect, n);
     count_launch();
   } else {
@@ -128,6 +136,10 @@ int edison_streams_open(size_t n_streams, edison_streams **out) {
   if (e == cudaSuccess) e = cudaMalloc(&s->d_filt, n_streams * EDISON_N_CLASSES * sizeof(float));
   if (e == cudaSuccess) e = cudaMalloc(&s->d_detect, n_streams * sizeof(int32_t));
   if (e == cudaSuccess) e = cudaMalloc(&s->d_pcm, n_streams * EDISON_FRAME_LEN * sizeof(int16_t));
+  s->incremental = 1;
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_incr, nnom_incr_state_bytes((long long)n_streams));
+  if (e == cudaSuccess) e = cudaMemset(s->d_incr, 0, nnom_incr_state_bytes((long long)n_streams));
+  if (e == cudaSuccess) nnom_incr_state_bind(&s->incr, s->d_incr, (long long)n_streams);
   if (e == cudaSuccess) e = cudaMemset(s->d_window, 0, n_streams * EDISON_NET_IN);   // netInput is zero-initialised static storage
   if (e == cudaSuccess) e = cudaMemset(s->d_filt, 0, n_streams * EDISON_N_CLASSES * sizeof(float));  // app.c:300
   if (e == cudaSuccess) e = cudaMemset(s->d_softmax, 0, n_streams * EDISON_N_CLASSES);
@@ -142,13 +154,20 @@ int edison_streams_open(size_t n_streams, edison_streams **out) {
 void edison_streams_close(edison_streams *s) {
   if (!s) return;
   cudaDeviceSynchronize();
-  void *bufs[] = {s->d_window, s->d_rows, s->d_softmax, s->d_filt, s->d_detect, s->d_pcm};
+  void *bufs[] = {s->d_window, s->d_rows, s->d_softmax, s->d_filt, s->d_detect, s->d_pcm, s->d_incr};
   for (void *b : bufs)
     if (b) cudaFree(b);
   delete s;
 }
 
 unsigned long long edison_streams_hops(const edison_streams *s) { return s ? s->hops : 0; }
+
+int edison_streams_set_incremental(edison_streams *s, int on) {
+  if (!s) return ctx_fail(EDISON_E_ARG, "edison_streams_set_incremental: null handle");
+  if (s->hops) return ctx_fail(EDISON_E_ARG, "edison_streams_set_incremental: only before the first hop (the rings fill from hop 1)");
+  s->incremental = on ? 1 : 0;
+  return EDISON_OK;
+}
 
 int edison_streams_push_hop_dev(edison_streams *s, const int16_t *d_hop_pcm, int8_t *d_softmax, float *d_filt,
                                 int32_t *d_detect, void *stream) {

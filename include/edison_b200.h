@@ -197,6 +197,9 @@ int edison_streams_push_hop(edison_streams *s, const int16_t *hop_pcm, int8_t *s
 int edison_streams_push_hop_dev(edison_streams *s, const int16_t *d_hop_pcm, int8_t *d_softmax, float *d_filt,
                                 int32_t *d_detect, void *stream);
 unsigned long long edison_streams_hops(const edison_streams *s);
+/* 1 (default): the net advances one new row per layer and hop from cached rows (bit-identical, ~4x less work);
+ * 0: the whole 31-row window goes through the net every hop, as the firmware does.  Only before the first hop. */
+int edison_streams_set_incremental(edison_streams *s, int on);
 /* copy one stream's 31x13 window (netInput, app.c:71-93) to the host, for inspection */
 int edison_streams_window(edison_streams *s, size_t stream_index, int8_t *window403);
 

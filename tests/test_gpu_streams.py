@@ -31,12 +31,13 @@ def simulate(oracle, pcm_hops, mode=0):
     return out
 
 
+@pytest.mark.parametrize("incremental", [True, False])
 @pytest.mark.parametrize("n", [1, 37])
-def test_streams_vs_firmware_loop(edison, oracle, n):
-    hops = 40
+def test_streams_vs_firmware_loop(edison, oracle, n, incremental):
+    hops = 58          # > 31 + 12 + 12: every ring of the incremental net wraps at least twice after inference starts
     pcm = synth_frames(hops * n, seed=77).reshape(hops, n, 1024)
     want = simulate(oracle, pcm)
-    with edison.Streams(n) as st:
+    with edison.Streams(n, incremental) as st:
         for h in range(hops):
             sm, fl, dt = st.push_hop(pcm[h])
             w_sm, w_fl, w_dt, w_win = want[h]
@@ -44,7 +45,7 @@ def test_streams_vs_firmware_loop(edison, oracle, n):
             if h + 1 > 31:
                 assert np.array_equal(sm, w_sm), "softmax, hop %d" % h
             assert np.array_equal(fl.view(np.uint32), w_fl.view(np.uint32)), "filter bits, hop %d" % h
-            if h in (0, 12, 30, 31, 39):
+            if h in (0, 12, 30, 31, 39, 57):
                 for i in (0, n - 1):
                     assert np.array_equal(st.window(i), w_win[i]), "window, hop %d stream %d" % (h, i)
         assert st.hops == hops
