@@ -205,8 +205,11 @@ class HifDevice(_Endpoint):
         return cmd
 
     def serve(self):
-        while self.run_once() is not None:
-            pass
+        try:
+            while self.run_once() is not None:
+                pass
+        except (EOFError, OSError):       # the host hung up in the middle of a transaction
+            return
 
 
 # ---- ingest formats -----------------------------------------------------------------------------------------------------
