@@ -49,7 +49,7 @@ static_assert(sizeof(NnomModel) % 16 == 0, "NnomModel is copied with 16-byte vec
 constexpr int kNC = 16;            // clips per CTA tile
 constexpr int kNetThreads = 256;
 constexpr int kNetWarps = kNetThreads / 32;
-constexpr int kInStride = 416;     // 403 input bytes per clip, padded
+constexpr int kInStride = EDISON_NET_IN;   // 403: a tile's 16 inputs stay contiguous, exactly as they lie in HBM (conv1 fetches unaligned)
 constexpr int kPix1 = 13 * 9, kPix2 = 5 * 7, kPix3 = 3 * 5, kPix4 = 3;   // pixels per clip after each conv(+pool)
 constexpr int kRegionX = kNC * kPix2 * kC2;   // holds: input [16][416] | act2 [16][35][32] | act4 [16][3][32]
 constexpr int kRegionY = kNC * kPix1 * kC1;   // holds: act1 [16][117][16] | act3 [16][15][64] | logits [16][16]
@@ -252,10 +252,28 @@ __global__ void __launch_bounds__(kNetThreads, 2) nnom_q7_kernel(const NnomModel
     const long long c0 = tile * kNC;
     const int nclips = (int)min((long long)kNC, n - c0);
     __syncthreads();   // previous tile's readers are done (and, first time, the model copy is visible)
-    // input: 403 bytes per clip -> X[clip * 416 ..]; the pad bytes only ever meet zero weights
-    for (int i = threadIdx.x; i < nclips * EDISON_NET_IN; i += kNetThreads) {
-      const int clip = i / EDISON_NET_IN, j = i - clip * EDISON_NET_IN;
-      S.X[clip * kInStride + j] = net_in[(c0 + clip) * EDISON_NET_IN + j];
+    // input: the tile's nclips x 403 bytes are contiguous in HBM and 16-byte aligned when the tile is full (16 x 403 = 403
+    // int4): two independent 128-bit loads per thread.  Bytes past a clip's end only ever meet zero weights.
+    {
+      const int8_t *src = net_in + c0 * EDISON_NET_IN;
+      const int bytes = nclips * EDISON_NET_IN;
+      if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        const int n16 = bytes >> 4;
+        int4 v[2];
+#pragma unroll
+        for (int it = 0; it < 2; it++) {
+          const int i = threadIdx.x + it * kNetThreads;
+          if (i < n16) v[it] = __ldg(reinterpret_cast<const int4 *>(src) + i);
+        }
+#pragma unroll
+        for (int it = 0; it < 2; it++) {
+          const int i = threadIdx.x + it * kNetThreads;
+          if (i < n16) reinterpret_cast<int4 *>(S.X)[i] = v[it];
+        }
+        for (int i = (n16 << 4) + threadIdx.x; i < bytes; i += kNetThreads) S.X[i] = src[i];
+      } else {
+        for (int i = threadIdx.x; i < bytes; i += kNetThreads) S.X[i] = src[i];
+      }
     }
     __syncthreads();
     conv1_mma(S.X, S.Y, &M.f1[0][0][0], M.seed1, M.rs[0], nclips);                                          // -> act1 [13][9][16]
