@@ -32,6 +32,8 @@ N_STREAMS = 100000              # config #5
 # dram__bytes_read.sum + dram__bytes_write.sum of one mfcc_q15_kernel launch over 131,072 x 31 frames, from the ncu
 # --set full capture summarised in profiles/ (8.32 GB read + 10 MB written): no re-reads.
 K1_NCU_DRAM_BYTES = 8.33e9
+# smsp__inst_executed.sum / frames of the same capture: what actually bounds K1 (integer issue, SURVEY F9 / DESIGN.md section 3)
+K1_WARP_INST_PER_FRAME = 2549
 
 
 def peaks():
@@ -326,6 +328,7 @@ def run_ours(args, rank, world, local_rank):
 
     if rank == 0:
         peak, peak_kind = peaks()
+        sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
         k1_bytes = n * 31 * K1_BYTES_PER_FRAME
         achieved = k1_bytes / (k1_ms / 1e3) / 1e9
         line = {"metric": "kws_clips_per_s", "value": value, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
@@ -339,7 +342,13 @@ def run_ours(args, rank, world, local_rank):
                 "cfg2_mfcc": {"workload": "config#2: 65,536 x 1 s clips (15 frames each), q15 MFCC only, 1 GPU",
                               "frames_per_s": cfg2_fps, "clips_per_s": CFG2_CLIPS / (cfg2_ms / 1e3), "ms": cfg2_ms},
                 "roofline": {"kernel": "mfcc_q15_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": K1_NCU_DRAM_BYTES * (k1_bytes / (131072 * 31 * K1_BYTES_PER_FRAME)), "bytes_per_launch": k1_bytes},
+                             "frac": achieved / peak, "traffic": K1_NCU_DRAM_BYTES * (k1_bytes / (131072 * 31 * K1_BYTES_PER_FRAME)), "bytes_per_launch": k1_bytes,
+                             # the bound that actually binds: 4 warp-instructions per clock per SM (measured pipe rates, profiles/)
+                             "secondary": {"bound": "int-issue", "unit": "G warp-inst/s", "warp_inst_per_frame": K1_WARP_INST_PER_FRAME,
+                                           "achieved": n * 31 / (k1_ms / 1e3) * K1_WARP_INST_PER_FRAME / 1e9,
+                                           "peak": sm_count * 4 * (clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965) * 1e6 / 1e9,
+                                           "frac": (n * 31 / (k1_ms / 1e3) * K1_WARP_INST_PER_FRAME) /
+                                                   (sm_count * 4 * (clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965) * 1e6)}},
                 "e2e": {"value": e2e_val, "unit": "clips/s", "h2d_bytes_per_step": ne * CLIP * 2, "d2h_bytes_per_step": ne * 20,
                         "clips_per_step": ne, "matches_device_path": same},
                 "gpu_launches": int(launches), "clocks": clocks}
@@ -353,6 +362,11 @@ def run_ours(args, rank, world, local_rank):
             res = cpu_baseline.run(clips_per_proc=64, procs=os.cpu_count() or 1, reps=1)
             line["cpu_baseline"] = {"value": res["clips_per_s"], "unit": "clips/s", "cores": res["cores"], "kind": res["kind"],
                                     "sample": res["sample"]}
+            # the "fair CPU" figure of BASELINE.md (B2): the oracle's plain-C restatement at -O2 (bit-identical results, no
+            # host emulation of M4 intrinsics, audioprocessing.c's -O0 not needed), same sample, all cores
+            res2 = cpu_baseline.run(clips_per_proc=64, procs=os.cpu_count() or 1, reps=1, which="port")
+            line["cpu_baseline_port"] = {"value": res2["clips_per_s"], "unit": "clips/s", "cores": res2["cores"], "kind": "port",
+                                         "sample": res2["sample"]}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -36,14 +36,14 @@ def _synth(n_clips, seed):
 
 
 def _worker(args):
-    n_clips, seed, mfcc_only, reps = args
+    n_clips, seed, mfcc_only, reps, which = args
     pcm = _synth(n_clips, seed)
     p = lambda a: a.ctypes.data_as(ctypes.c_void_p)
     nf = n_clips * 31
     mf = np.zeros((nf, 32), np.int16)
     lg = np.zeros((n_clips, 10), np.int8)
     sm = np.zeros((n_clips, 10), np.int8)
-    if kind() == "reference":
+    if which == "reference":
         A, N = ctypes.CDLL(REF_MFCC), ctypes.CDLL(REF_NNOM)
         N.ref_nnom_init()
 
@@ -70,16 +70,17 @@ def _worker(args):
     return times, int(lg.astype(np.int64).sum())
 
 
-def run(clips_per_proc=128, procs=None, mfcc_only=False, reps=1, seed=20):
+def run(clips_per_proc=128, procs=None, mfcc_only=False, reps=1, seed=20, which=None):
     """returns dict(clips_per_s, frames_per_s, cores, kind, sample, step_s=[...]) ; step time = max over processes"""
     procs = procs or os.cpu_count() or 1
+    which = which or kind()      # "reference" = oracle/_ref (firmware-true build), "port" = the C restatement at -O2
     ctx = mp.get_context("spawn")
     with ctx.Pool(procs) as pool:
-        res = pool.map(_worker, [(clips_per_proc, seed + i, mfcc_only, reps) for i in range(procs)])
+        res = pool.map(_worker, [(clips_per_proc, seed + i, mfcc_only, reps, which) for i in range(procs)])
     step_s = [max(r[0][k] for r in res) for k in range(reps)]
     total = clips_per_proc * procs
     best = min(step_s)
-    return {"clips_per_s": total / best, "frames_per_s": total * 31 / best, "cores": procs, "kind": kind(),
+    return {"clips_per_s": total / best, "frames_per_s": total * 31 / best, "cores": procs, "kind": which,
             "sample": "%d clips x 31 frames (%d per process, %d processes), %s" %
                       (total, clips_per_proc, procs, "q15 MFCC only" if mfcc_only else "q15 MFCC + int8 NNoM net"),
             "step_s": step_s, "clips": total}
