@@ -320,11 +320,24 @@ def run_ours(args, rank, world, local_rank):
                 chk(L.edison_streams_push_hop(ss.handle, P(h_hop), P(h_sm), P(h_fl), P(h_dt)))
                 lat_e2e.append((time.perf_counter() - t0) * 1e3)
             lat_e2e = sorted(lat_e2e[8:])
+            small = {}
+            with ed.Streams(1024) as s2:
+                for h in range(34):
+                    chk(L.edison_streams_push_hop_dev(s2.handle, P(pcm[(h % 36) * 1024 * 1024:]), P(d_sm), P(d_fl), P(d_dt), sp))
+                torch.cuda.synchronize()
+                lat2 = []
+                for h in range(100):
+                    t0 = time.perf_counter()
+                    chk(L.edison_streams_push_hop_dev(s2.handle, P(pcm[(h % 36) * 1024 * 1024:]), P(d_sm), P(d_fl), P(d_dt), sp))
+                    torch.cuda.synchronize()
+                    lat2.append((time.perf_counter() - t0) * 1e3)
+                lat2.sort()
+                small = {"streams": 1024, "hop_ms_p50": lat2[50], "hop_ms_p99": lat2[98], "note": "host wall clock, launch to completion"}
             stream_stats = {"workload": "config#5: %d concurrent streams, hop 1024 samples (64 ms), window 31 rows, device resident" % ns,
                             "hop_ms_p50": p50, "hop_ms_p99": p99, "hops_timed": n_hops,
                             "stream_hops_per_s": ns / (p50 / 1e3), "realtime_streams_per_gpu": int(ns * 64.0 / p99),
                             "ingest_hop_ms_p50": lat_e2e[len(lat_e2e) // 2], "ingest_hop_ms_p99": lat_e2e[-1],
-                            "ingest_bytes_per_hop": ns * 2048, "ingest_realtime_streams_per_gpu": int(ns * 64.0 / lat_e2e[-1])}
+                            "ingest_bytes_per_hop": ns * 2048, "small_batch": small, "ingest_realtime_streams_per_gpu": int(ns * 64.0 / lat_e2e[-1])}
 
     if rank == 0:
         peak, peak_kind = peaks()
@@ -338,6 +351,8 @@ def run_ours(args, rank, world, local_rank):
                            "clip_samples": CLIP, "global_clips": world * n, "l2": "inputs (8.3 GB/GPU) larger than L2",
                            "parallelism": "clip shards, dp%d" % world, "peak": peak_kind},
                 "mfcc_frames_per_s": world * n * 31 / (k1_ms / 1e3), "audio_seconds_per_s": value * 31 * 0.064,
+                # BASELINE.json words the metric in "1 s 16 kHz" clips; the net's own window is 31 frames = 1.984 s
+                "one_second_equiv_clips_per_s": value * 31 / 15.625,
                 "k1_ms": k1_ms, "k2_ms": k2_ms,
                 "cfg2_mfcc": {"workload": "config#2: 65,536 x 1 s clips (15 frames each), q15 MFCC only, 1 GPU",
                               "frames_per_s": cfg2_fps, "clips_per_s": CFG2_CLIPS / (cfg2_ms / 1e3), "ms": cfg2_ms},
