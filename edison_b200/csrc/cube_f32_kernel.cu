@@ -6,13 +6,19 @@
 // The arithmetic of ST's closed runtime is unknown beyond "float32 MACs": parity is tolerance-based against the fp64
 // restatement in the test tree (cube_float.py) and UNPINNED at the keras boundary.
 //
-// A CTA keeps a tile of 12 clips in shared memory through all layers (1,612 B in, 40 + 40 B out per clip).  Each thread owns
-// a register tile of 2 pixels x 8 output channels (4 in the last, tiny conv): for the two pooled layers the 2 pixels are the two conv rows under one
-// pooled pixel (max pool = max of the thread's own accumulators), for the others the same pixel of two clips.  Activations are
-// H,W,C with every pixel's channel vector padded by 4 floats, so the 128-bit reads of a warp (one pixel per lane) spread
-// over all banks; weights are re-laid [ky][kx][c][q4][g][4] at load so a warp's weight read is one contiguous 128-byte line served by
-// L1/L2 (the 172 KB model is shared by every CTA).  Why FFMA and not tensor cores: at fp32 accuracy the alternatives are
-// 3xTF32 / 3xBF16 splits on mma.sync; 0.78 MMAC per clip puts this kernel at ~1/3 of K1's time per clip already.
+// A persistent CTA per SM keeps a tile of 8 clips in shared memory through all layers (1,612 B in, 40 + 40 B out per clip) and
+// ALL conv weights beside it: w1/w2 (20 KB) stay for the CTA's life, w3 and w4 (73.7 KB each) take turns in one buffer, refilled
+// by cp.async -- w3 while conv1/conv2 of the same tile run, w4 between conv3 and conv4 (~2 % of a tile, not overlapped) -- and
+// the next tile's input is prefetched into its staging buffer as soon as conv1 has consumed the current one.  (Weights read
+// through L1 instead missed 7 % of the time -- 172 KB of weights against the ~80 KB of L1 left beside the tile -- and those
+// L2 round trips were the top stall; profiles/r01i_k4.txt.)  Each thread owns a register tile of 2 pixels x 8 output
+// channels (4 in the last, tiny conv): for the two pooled layers the 2 pixels are the two conv rows under one pooled pixel
+// (max pool = max of the thread's own accumulators), for the others the same pixel of two clips.  conv4 has only 96 such
+// tiles per 8 clips, so its 3 kernel rows go to different threads and the dense layer adds the three partial sums.
+// Activations are H,W,C with every pixel's channel vector padded by 4 floats, so the 128-bit reads of a warp spread over all
+// banks; weights are re-laid [ky][kx][c][q4][g][4] at load so a warp's weight read is one contiguous 128-byte line.
+// Why FFMA and not tensor cores: at fp32 accuracy the alternatives are 3xTF32 / 3xBF16 splits on mma.sync; 0.78 MMAC per
+// clip puts this kernel at ~1/3 of K1's time per clip already.
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
@@ -24,7 +30,7 @@
 
 namespace edison {
 
-constexpr int kCubeClips = 12;       // clips per CTA tile (even: the unpooled layers pair clip b with b + 6)
+constexpr int kCubeClips = 8;        // clips per CTA tile (even: the unpooled layers pair clip b with b + 4)
 constexpr int kCubeThreads = 512;
 constexpr int kPad = 4;              // floats appended to every pixel's channel vector
 
@@ -32,27 +38,49 @@ constexpr int kPad = 4;              // floats appended to every pixel's channel
 constexpr int kA1 = 13 * 9 * (16 + kPad);     // conv1 + pool
 constexpr int kA2 = 5 * 7 * (32 + kPad);      // conv2 + pool
 constexpr int kA3 = 3 * 5 * (64 + kPad);      // conv3
-constexpr int kA4 = 1 * 3 * 32;               // conv4 (flattened H,W,C = dense input, unpadded)
-constexpr int kBufA = kA2 > EDISON_NET_IN ? kA2 : EDISON_NET_IN;   // input / conv2 out / conv4 out
-constexpr int kBufB = kA1;                                         // conv1 out / conv3 out
+constexpr int kA4 = 1 * 3 * 32;               // conv4 (flattened H,W,C = dense input, unpadded), x3 partial sums
+constexpr int kBufA = kA2;                    // conv2 out / conv4 partial sums
+constexpr int kBufB = kA1;                    // conv1 out / conv3 out
+constexpr int kW1 = 5 * 5 * 1 * 16, kW2 = 3 * 3 * 16 * 32, kW3 = 3 * 3 * 32 * 64, kW4 = 3 * 3 * 64 * 32;
+static_assert(kW3 == kW4 && 3 * kA4 <= kBufA && kA3 <= kBufB, "buffer sharing");
 
 struct CubeModel {
-  float w1[5 * 5 * 1 * 16], b1[16];
-  float w2[3 * 3 * 16 * 32], b2[32];
-  float w3[3 * 3 * 32 * 64], b3[64];
-  float w4[3 * 3 * 64 * 32], b4[32];
+  float w1[kW1], b1[16];
+  float w2[kW2], b2[32];
+  float w3[kW3], b3[64];
+  float w4[kW4], b4[32];
   float wd[10 * 96], bd[10];         // dense stays [out][in]
   float pad_[2];
 };
 
 struct CubeSmem {
+  float wbig[kW3];                            // w3 during conv3, w4 during conv4
+  float w1[kW1], w2[kW2];
+  float stage[kCubeClips * EDISON_NET_IN];    // the tile's input, contiguous as in HBM
   float a[kCubeClips][kBufA];
   float b[kCubeClips][kBufB];
   float logits[kCubeClips][12];
 };
+static_assert(sizeof(CubeSmem) <= 227 * 1024, "tile + weights exceed the shared memory of an SM");
 
-// One conv layer over the tile.  in: [clip][HIN][WIN][C + pad] (C == 1: unpadded scalars), out: [clip][HP][WO][O + opad].
-template <int HIN, int WIN, int C, int KH, int KW, int O, int Q, bool POOL, int IN_STRIDE, int OUT_STRIDE, int OPAD>
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+}
+// n floats (a multiple of 4, both sides 16-byte aligned) by the whole CTA
+__device__ __forceinline__ void stage_floats(float *dst, const float *src, int n) {
+  for (int i = threadIdx.x * 4; i < n; i += kCubeThreads * 4) cp_async16(dst + i, src + i);
+}
+
+// One conv layer over the tile.  in: [clip][HIN][WIN][C + pad] (C == 1: unpadded scalars), out: [clip][HP][WO][O + opad];
+// wgt in shared memory.  KSPLIT > 1: the kernel rows are dealt to KSPLIT threads, each writing a raw partial sum (no bias,
+// no ReLU) to out[clip][split][pixel][O] for the consumer to add up.
+template <int HIN, int WIN, int C, int KH, int KW, int O, int Q, bool POOL, int KSPLIT, int IN_STRIDE, int OUT_STRIDE, int OPAD>
 __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *__restrict__ out, const float *__restrict__ wgt,
                                            const float *__restrict__ bias) {
   constexpr int HO = HIN - KH + 1, WO = WIN - KW + 1;
@@ -62,10 +90,14 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
   constexpr int OP = O + OPAD;
   constexpr int NPIX = HP * WO;
   constexpr int NB = POOL ? kCubeClips : kCubeClips / 2;
-  constexpr int NITEMS = G * NB * NPIX;
+  constexpr int NITEMS = G * NB * NPIX * KSPLIT;
+  constexpr int KROWS = KH / KSPLIT;
+  static_assert(KH % KSPLIT == 0 && (KSPLIT == 1 || !POOL), "row split");
   for (int item = threadIdx.x; item < NITEMS; item += kCubeThreads) {
     const int g = item % G;               // neighbouring lanes share a pixel (one broadcast read) and split its channels
-    const int rest = item / G;
+    int rest = item / G;
+    const int ks = KSPLIT > 1 ? rest % KSPLIT : 0;
+    if (KSPLIT > 1) rest /= KSPLIT;
     const int b = rest / NPIX, pix = rest - b * NPIX;
     const int py = pix / WO, x = pix - py * WO;
     // the two pixels of this thread
@@ -79,25 +111,29 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
     }
     float acc0[Q], acc1[Q];
 #pragma unroll
-    for (int q = 0; q < Q; q++) acc0[q] = acc1[q] = __ldg(bias + g * Q + q);
+    for (int q = 0; q < Q; q++) acc0[q] = acc1[q] = KSPLIT > 1 ? 0.f : __ldg(bias + g * Q + q);
     const float *wg = wgt + g * 4;        // weights are laid out [k][c][q4][g][4]: a warp's read is one contiguous line
 #pragma unroll 1
-    for (int ky = 0; ky < KH; ky++) {
-#pragma unroll 1
-      for (int kx = 0; kx < KW; kx++) {
-        const float *q0 = p0 + (ky * WIN + kx) * CP, *q1 = p1 + (ky * WIN + kx) * CP;
-        const float *wk = wg + (ky * KW + kx) * C * O;
-        if (C == 1) {
-          const float a0 = q0[0], a1 = q1[0];
+    for (int ky = ks * KROWS; ky < (ks + 1) * KROWS; ky++) {
+      if (C == 1) {
+#pragma unroll
+        for (int kx = 0; kx < KW; kx++) {
+          const float a0 = p0[ky * WIN + kx], a1 = p1[ky * WIN + kx];
+          const float *wk = wg + (ky * KW + kx) * O;
 #pragma unroll
           for (int q4 = 0; q4 < Q / 4; q4++) {
-            const float4 w = __ldg(reinterpret_cast<const float4 *>(wk + q4 * G * 4));
+            const float4 w = *reinterpret_cast<const float4 *>(wk + q4 * G * 4);
             acc0[4 * q4 + 0] = fmaf(a0, w.x, acc0[4 * q4 + 0]); acc1[4 * q4 + 0] = fmaf(a1, w.x, acc1[4 * q4 + 0]);
             acc0[4 * q4 + 1] = fmaf(a0, w.y, acc0[4 * q4 + 1]); acc1[4 * q4 + 1] = fmaf(a1, w.y, acc1[4 * q4 + 1]);
             acc0[4 * q4 + 2] = fmaf(a0, w.z, acc0[4 * q4 + 2]); acc1[4 * q4 + 2] = fmaf(a1, w.z, acc1[4 * q4 + 2]);
             acc0[4 * q4 + 3] = fmaf(a0, w.w, acc0[4 * q4 + 3]); acc1[4 * q4 + 3] = fmaf(a1, w.w, acc1[4 * q4 + 3]);
           }
-        } else {
+        }
+      } else {
+#pragma unroll 1
+        for (int kx = 0; kx < KW; kx++) {
+          const float *q0 = p0 + (ky * WIN + kx) * CP, *q1 = p1 + (ky * WIN + kx) * CP;
+          const float *wk = wg + (ky * KW + kx) * C * O;
 #pragma unroll 2
           for (int c4 = 0; c4 < C / 4; c4++) {
             const float4 v0 = *reinterpret_cast<const float4 *>(q0 + 4 * c4);
@@ -108,7 +144,7 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
               const float *wr = wk + (4 * c4 + cc) * O;
 #pragma unroll
               for (int q4 = 0; q4 < Q / 4; q4++) {
-                const float4 w = __ldg(reinterpret_cast<const float4 *>(wr + q4 * G * 4));
+                const float4 w = *reinterpret_cast<const float4 *>(wr + q4 * G * 4);
                 acc0[4 * q4 + 0] = fmaf(a0[cc], w.x, acc0[4 * q4 + 0]); acc1[4 * q4 + 0] = fmaf(a1[cc], w.x, acc1[4 * q4 + 0]);
                 acc0[4 * q4 + 1] = fmaf(a0[cc], w.y, acc0[4 * q4 + 1]); acc1[4 * q4 + 1] = fmaf(a1[cc], w.y, acc1[4 * q4 + 1]);
                 acc0[4 * q4 + 2] = fmaf(a0[cc], w.z, acc0[4 * q4 + 2]); acc1[4 * q4 + 2] = fmaf(a1[cc], w.z, acc1[4 * q4 + 2]);
@@ -120,8 +156,8 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
       }
     }
     // ReLU (nl_func_relu_array_f32) then max pool (pool_func_mp_array_f32), or two separate pixels
-    float *o0 = out + b * OUT_STRIDE + (py * WO + x) * OP + g * Q;
     if (POOL) {
+      float *o0 = out + b * OUT_STRIDE + (py * WO + x) * OP + g * Q;
 #pragma unroll
       for (int q4 = 0; q4 < Q / 4; q4++) {
         float4 r;
@@ -132,14 +168,31 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
         *reinterpret_cast<float4 *>(o0 + 4 * q4) = r;
       }
     } else {
+      float *o0 = out + b * OUT_STRIDE + ((ks * HP + py) * WO + x) * OP + g * Q;
       float *o1 = o0 + (kCubeClips / 2) * OUT_STRIDE;
 #pragma unroll
-      for (int q4 = 0; q4 < Q / 4; q4++) {
-        *reinterpret_cast<float4 *>(o0 + 4 * q4) = make_float4(fmaxf(acc0[4 * q4 + 0], 0.f), fmaxf(acc0[4 * q4 + 1], 0.f),
-                                                               fmaxf(acc0[4 * q4 + 2], 0.f), fmaxf(acc0[4 * q4 + 3], 0.f));
-        *reinterpret_cast<float4 *>(o1 + 4 * q4) = make_float4(fmaxf(acc1[4 * q4 + 0], 0.f), fmaxf(acc1[4 * q4 + 1], 0.f),
-                                                               fmaxf(acc1[4 * q4 + 2], 0.f), fmaxf(acc1[4 * q4 + 3], 0.f));
+      for (int q = 0; q < Q; q++) {
+        if (KSPLIT == 1) { acc0[q] = fmaxf(acc0[q], 0.f); acc1[q] = fmaxf(acc1[q], 0.f); }
       }
+#pragma unroll
+      for (int q4 = 0; q4 < Q / 4; q4++) {
+        *reinterpret_cast<float4 *>(o0 + 4 * q4) = make_float4(acc0[4 * q4 + 0], acc0[4 * q4 + 1], acc0[4 * q4 + 2], acc0[4 * q4 + 3]);
+        *reinterpret_cast<float4 *>(o1 + 4 * q4) = make_float4(acc1[4 * q4 + 0], acc1[4 * q4 + 1], acc1[4 * q4 + 2], acc1[4 * q4 + 3]);
+      }
+    }
+  }
+}
+
+// the tile's input: 16-byte copies when the tile is whole and aligned, else word copies + zero fill
+__device__ __forceinline__ void stage_input(float *stage, const float *net_in, long long c0, long long n, bool aligned) {
+  const int nc = (int)((n - c0) < kCubeClips ? (n - c0) : kCubeClips);
+  const float *src = net_in + c0 * EDISON_NET_IN;
+  if (nc == kCubeClips && aligned) {
+    stage_floats(stage, src, kCubeClips * EDISON_NET_IN);
+  } else {
+    for (int i = threadIdx.x; i < kCubeClips * EDISON_NET_IN; i += kCubeThreads) {
+      if (i < nc * EDISON_NET_IN) cp_async4(stage + i, src + i);
+      else stage[i] = 0.f;
     }
   }
 }
@@ -150,30 +203,45 @@ cube_f32_kernel(const CubeModel *__restrict__ M, const float *__restrict__ net_i
   extern __shared__ __align__(16) unsigned char smem_raw[];
   CubeSmem &S = *reinterpret_cast<CubeSmem *>(smem_raw);
   const long long n_tiles = (n + kCubeClips - 1) / kCubeClips;
+  const bool aligned = (reinterpret_cast<unsigned long long>(net_in) & 15) == 0;   // a tile is 12,896 B: alignment is the base's
+  if ((long long)blockIdx.x >= n_tiles) return;
+  stage_floats(S.w1, M->w1, kW1);
+  stage_floats(S.w2, M->w2, kW2);
+  stage_floats(S.wbig, M->w3, kW3);
+  stage_input(S.stage, net_in, (long long)blockIdx.x * kCubeClips, n, aligned);
+  cp_async_wait_all();
+  __syncthreads();
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long c0 = tile * kCubeClips;
     const int nc = (int)((n - c0) < kCubeClips ? (n - c0) : kCubeClips);
-    for (int i = threadIdx.x; i < kCubeClips * EDISON_NET_IN; i += kCubeThreads) {
-      const int b = i / EDISON_NET_IN, j = i - b * EDISON_NET_IN;
-      S.a[b][j] = b < nc ? __ldg(net_in + (c0 + b) * EDISON_NET_IN + j) : 0.f;
-    }
+    conv_layer<31, 13, 1, 5, 5, 16, 8, true, 1, EDISON_NET_IN, kBufB, kPad>(S.stage, &S.b[0][0], S.w1, M->b1);
     __syncthreads();
-    conv_layer<31, 13, 1, 5, 5, 16, 8, true, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], M->w1, M->b1);
+    if (tile + gridDim.x < n_tiles) stage_input(S.stage, net_in, (tile + gridDim.x) * kCubeClips, n, aligned);   // lands during conv2..4
+    conv_layer<13, 9, 16, 3, 3, 32, 8, true, 1, kBufB, kBufA, kPad>(&S.b[0][0], &S.a[0][0], S.w2, M->b2);
+    cp_async_wait_all();                  // w3 (issued after the previous tile's conv4) and the next input
     __syncthreads();
-    conv_layer<13, 9, 16, 3, 3, 32, 8, true, kBufB, kBufA, kPad>(&S.b[0][0], &S.a[0][0], M->w2, M->b2);
+    conv_layer<5, 7, 32, 3, 3, 64, 8, false, 1, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], S.wbig, M->b3);
     __syncthreads();
-    conv_layer<5, 7, 32, 3, 3, 64, 8, false, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], M->w3, M->b3);
+    stage_floats(S.wbig, M->w4, kW4);
+    cp_async_wait_all();
     __syncthreads();
-    conv_layer<3, 5, 64, 3, 3, 32, 4, false, kBufB, kBufA, 0>(&S.b[0][0], &S.a[0][0], M->w4, M->b4);
+    conv_layer<3, 5, 64, 3, 3, 32, 4, false, 3, kBufB, kBufA, 0>(&S.b[0][0], &S.a[0][0], S.wbig, M->b4);
     __syncthreads();
-    // dense (forward_dense): one thread per (clip, class)
-    if (threadIdx.x < kCubeClips * EDISON_N_CLASSES) {
-      const int b = threadIdx.x / EDISON_N_CLASSES, o = threadIdx.x - b * EDISON_N_CLASSES;
-      float acc = __ldg(M->bd + o);
+    if (tile + gridDim.x < n_tiles) stage_floats(S.wbig, M->w3, kW3);     // lands during the next tile's conv1/conv2
+    // conv4 bias + ReLU on the sum of its three partial sums, then dense (forward_dense): 4 lanes per (clip, class)
+    if (threadIdx.x < kCubeClips * EDISON_N_CLASSES * 4) {
+      const int part = threadIdx.x & 3, bo = threadIdx.x >> 2;
+      const int b = bo / EDISON_N_CLASSES, o = bo - b * EDISON_N_CLASSES;
       const float *x = &S.a[b][0], *w = M->wd + o * 96;
+      float acc = part == 0 ? __ldg(M->bd + o) : 0.f;
 #pragma unroll 8
-      for (int j = 0; j < 96; j++) acc = fmaf(x[j], __ldg(w + j), acc);
-      S.logits[b][o] = acc;
+      for (int j = part * 24; j < part * 24 + 24; j++) {
+        const float v = fmaxf(__ldg(M->b4 + (j & 31)) + x[j] + x[kA4 + j] + x[2 * kA4 + j], 0.f);
+        acc = fmaf(v, __ldg(w + j), acc);
+      }
+      acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+      acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+      if (part == 0) S.logits[b][o] = acc;
     }
     __syncthreads();
     // softmax, natural e (forward_sm)
@@ -192,7 +260,6 @@ cube_f32_kernel(const CubeModel *__restrict__ M, const float *__restrict__ net_i
         if (softmax) softmax[(c0 + b) * EDISON_N_CLASSES + o] = e[o] * inv;
       }
     }
-    __syncthreads();
   }
 }
 
