@@ -11,10 +11,8 @@
 // by cp.async -- w3 while conv1/conv2 of the same tile run, w4 between conv3 and conv4 (~2 % of a tile, not overlapped) -- and
 // the next tile's input is prefetched into its staging buffer as soon as conv1 has consumed the current one.  (Weights read
 // through L1 instead missed 7 % of the time -- 172 KB of weights against the ~80 KB of L1 left beside the tile -- and those
-// L2 round trips were the top stall; profiles/r01i_k4.txt.)  Each thread owns a register tile of 2 pixels x 8 output
-// channels (4 in the last, tiny conv): for the two pooled layers the 2 pixels are the two conv rows under one pooled pixel
-// (max pool = max of the thread's own accumulators), for the others the same pixel of two clips.  conv4 has only 96 such
-// tiles per 8 clips, so its 3 kernel rows go to different threads and the dense layer adds the three partial sums.
+// L2 round trips were the top stall; profiles/r01i_k4.txt.)  Each thread owns a register tile of P pixels x Q output
+// channels (conv_layer below); 576 threads because the layers then have 936 / 560 / 480 / 288 tiles per 8 clips.
 // Activations are H,W,C with every pixel's channel vector padded by 4 floats, so the 128-bit reads of a warp spread over all
 // banks; weights are re-laid [ky][kx][c][q4][g][4] at load so a warp's weight read is one contiguous 128-byte line.
 // Why FFMA and not tensor cores: at fp32 accuracy the alternatives are 3xTF32 / 3xBF16 splits on mma.sync; 0.78 MMAC per
@@ -31,15 +29,15 @@
 namespace edison {
 
 constexpr int kCubeClips = 8;        // clips per CTA tile (even: the unpooled layers pair clip b with b + 4)
-constexpr int kCubeThreads = 512;
+constexpr int kCubeThreads = 576;         // 18 warps: conv2 has 560 register tiles, conv3 480, conv1 936
 constexpr int kPad = 4;              // floats appended to every pixel's channel vector
 
 // activation geometry (H, W, C) after each layer
 constexpr int kA1 = 13 * 9 * (16 + kPad);     // conv1 + pool
 constexpr int kA2 = 5 * 7 * (32 + kPad);      // conv2 + pool
 constexpr int kA3 = 3 * 5 * (64 + kPad);      // conv3
-constexpr int kA4 = 1 * 3 * 32;               // conv4 (flattened H,W,C = dense input, unpadded), x3 partial sums
-constexpr int kBufA = kA2;                    // conv2 out / conv4 partial sums
+constexpr int kA4 = 1 * 3 * 32;               // conv4 (flattened H,W,C = dense input, unpadded)
+constexpr int kBufA = kA2;                    // conv2 out / conv4 out
 constexpr int kBufB = kA1;                    // conv1 out / conv3 out
 constexpr int kW1 = 5 * 5 * 1 * 16, kW2 = 3 * 3 * 16 * 32, kW3 = 3 * 3 * 32 * 64, kW4 = 3 * 3 * 64 * 32;
 static_assert(kW3 == kW4 && 3 * kA4 <= kBufA && kA3 <= kBufB, "buffer sharing");
@@ -78,9 +76,12 @@ __device__ __forceinline__ void stage_floats(float *dst, const float *src, int n
 }
 
 // One conv layer over the tile.  in: [clip][HIN][WIN][C + pad] (C == 1: unpadded scalars), out: [clip][HP][WO][O + opad];
-// wgt in shared memory.  KSPLIT > 1: the kernel rows are dealt to KSPLIT threads, each writing a raw partial sum (no bias,
-// no ReLU) to out[clip][split][pixel][O] for the consumer to add up.
-template <int HIN, int WIN, int C, int KH, int KW, int O, int Q, bool POOL, int KSPLIT, int IN_STRIDE, int OUT_STRIDE, int OPAD>
+// wgt in shared memory.  A thread's register tile is P pixels x Q output channels, P = PB clips (b, b + 8/PB, ...) times the
+// two conv rows under a pooled pixel (POOL) or one pixel; S neighbouring lanes split the input channels of the same tile
+// and add their sums by shuffle; KS > 1 deals the kernel rows to KS threads, each writing a raw partial sum (no bias, no
+// ReLU) to out[clip][split][pixel][O] for the consumer to add up.  Shared memory hands a lane 4 B per clock whatever the broadcast, so the tile shape sets
+// the ceiling: P*Q FFMAs per P+Q loaded floats (2x8 = 1.6 held the FMA pipe at 41 %; 4x8 = 2.7, 8x8 = 4.0).
+template <int HIN, int WIN, int C, int KH, int KW, int O, int Q, bool POOL, int PB, int S, int KS, int IN_STRIDE, int OUT_STRIDE, int OPAD>
 __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *__restrict__ out, const float *__restrict__ wgt,
                                            const float *__restrict__ bias) {
   constexpr int HO = HIN - KH + 1, WO = WIN - KW + 1;
@@ -89,95 +90,113 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
   constexpr int CP = C == 1 ? 1 : C + kPad;
   constexpr int OP = O + OPAD;
   constexpr int NPIX = HP * WO;
-  constexpr int NB = POOL ? kCubeClips : kCubeClips / 2;
-  constexpr int NITEMS = G * NB * NPIX * KSPLIT;
-  constexpr int KROWS = KH / KSPLIT;
-  static_assert(KH % KSPLIT == 0 && (KSPLIT == 1 || !POOL), "row split");
-  for (int item = threadIdx.x; item < NITEMS; item += kCubeThreads) {
-    const int g = item % G;               // neighbouring lanes share a pixel (one broadcast read) and split its channels
-    int rest = item / G;
-    const int ks = KSPLIT > 1 ? rest % KSPLIT : 0;
-    if (KSPLIT > 1) rest /= KSPLIT;
+  constexpr int NB = kCubeClips / PB;            // clip groups; a thread's clips are b, b + NB, ...
+  constexpr int R = POOL ? 2 : 1;                // conv rows per clip in the tile
+  constexpr int P = PB * R;
+  constexpr int NITEMS = S * G * KS * NB * NPIX;
+  constexpr int KROWS = KH / KS;
+  constexpr int C4 = C == 1 ? 1 : C / 4;
+  static_assert(kCubeClips % PB == 0 && (S & (S - 1)) == 0 && S * G <= 32 && 32 % (S * G) == 0 && (C == 1 ? S == 1 : C4 % S == 0), "tile shape");
+  static_assert(KH % KS == 0 && (KS == 1 || !POOL), "row split");
+  constexpr int NROUNDS = (NITEMS + kCubeThreads - 1) / kCubeThreads;
+#pragma unroll 1
+  for (int round = 0; round < NROUNDS; round++) {
+    const int item_raw = round * kCubeThreads + threadIdx.x;
+    if (S > 1 ? (item_raw & ~31) >= NITEMS : item_raw >= NITEMS) break;      // whole warps stay for the shuffles
+    const bool valid = item_raw < NITEMS;
+    const int item = valid ? item_raw : 0;
+    const int g = item % G;                      // a quarter warp reads one line of weights and one pixel
+    const int s = (item / G) % S;
+    int rest = item / (S * G);
+    const int ks = KS > 1 ? rest % KS : 0;
+    if (KS > 1) rest /= KS;
     const int b = rest / NPIX, pix = rest - b * NPIX;
     const int py = pix / WO, x = pix - py * WO;
-    // the two pixels of this thread
-    const float *p0, *p1;
-    if (POOL) {
-      p0 = in + b * IN_STRIDE + ((2 * py) * WIN + x) * CP;
-      p1 = p0 + WIN * CP;
-    } else {
-      p0 = in + b * IN_STRIDE + (py * WIN + x) * CP;
-      p1 = p0 + (kCubeClips / 2) * IN_STRIDE;
-    }
-    float acc0[Q], acc1[Q];
+    const float *p0 = in + b * IN_STRIDE + ((R * py) * WIN + x) * CP + (C == 1 ? 0 : 4 * s);
+    float acc[P][Q];
 #pragma unroll
-    for (int q = 0; q < Q; q++) acc0[q] = acc1[q] = KSPLIT > 1 ? 0.f : __ldg(bias + g * Q + q);
-    const float *wg = wgt + g * 4;        // weights are laid out [k][c][q4][g][4]: a warp's read is one contiguous line
+    for (int p = 0; p < P; p++)
+#pragma unroll
+      for (int q = 0; q < Q; q++) acc[p][q] = 0.f;
+    const float *wg = wgt + g * 4 + (C == 1 ? 0 : 4 * s * O);   // weights [k][c][q4][g][4]: a warp's read is contiguous lines
 #pragma unroll 1
     for (int ky = ks * KROWS; ky < (ks + 1) * KROWS; ky++) {
       if (C == 1) {
 #pragma unroll
         for (int kx = 0; kx < KW; kx++) {
-          const float a0 = p0[ky * WIN + kx], a1 = p1[ky * WIN + kx];
+          float av[P];
+#pragma unroll
+          for (int p = 0; p < P; p++) av[p] = p0[(p / R) * NB * IN_STRIDE + (p % R) * WIN + ky * WIN + kx];
           const float *wk = wg + (ky * KW + kx) * O;
 #pragma unroll
           for (int q4 = 0; q4 < Q / 4; q4++) {
             const float4 w = *reinterpret_cast<const float4 *>(wk + q4 * G * 4);
-            acc0[4 * q4 + 0] = fmaf(a0, w.x, acc0[4 * q4 + 0]); acc1[4 * q4 + 0] = fmaf(a1, w.x, acc1[4 * q4 + 0]);
-            acc0[4 * q4 + 1] = fmaf(a0, w.y, acc0[4 * q4 + 1]); acc1[4 * q4 + 1] = fmaf(a1, w.y, acc1[4 * q4 + 1]);
-            acc0[4 * q4 + 2] = fmaf(a0, w.z, acc0[4 * q4 + 2]); acc1[4 * q4 + 2] = fmaf(a1, w.z, acc1[4 * q4 + 2]);
-            acc0[4 * q4 + 3] = fmaf(a0, w.w, acc0[4 * q4 + 3]); acc1[4 * q4 + 3] = fmaf(a1, w.w, acc1[4 * q4 + 3]);
+#pragma unroll
+            for (int p = 0; p < P; p++) {
+              acc[p][4 * q4 + 0] = fmaf(av[p], w.x, acc[p][4 * q4 + 0]);
+              acc[p][4 * q4 + 1] = fmaf(av[p], w.y, acc[p][4 * q4 + 1]);
+              acc[p][4 * q4 + 2] = fmaf(av[p], w.z, acc[p][4 * q4 + 2]);
+              acc[p][4 * q4 + 3] = fmaf(av[p], w.w, acc[p][4 * q4 + 3]);
+            }
           }
         }
       } else {
 #pragma unroll 1
         for (int kx = 0; kx < KW; kx++) {
-          const float *q0 = p0 + (ky * WIN + kx) * CP, *q1 = p1 + (ky * WIN + kx) * CP;
+          const float *q0 = p0 + (ky * WIN + kx) * CP;
           const float *wk = wg + (ky * KW + kx) * C * O;
-#pragma unroll 2
-          for (int c4 = 0; c4 < C / 4; c4++) {
-            const float4 v0 = *reinterpret_cast<const float4 *>(q0 + 4 * c4);
-            const float4 v1 = *reinterpret_cast<const float4 *>(q1 + 4 * c4);
-            const float a0[4] = {v0.x, v0.y, v0.z, v0.w}, a1[4] = {v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+          for (int c4 = 0; c4 < C4 / S; c4++) {
+            float4 v[P];
+#pragma unroll
+            for (int p = 0; p < P; p++)
+              v[p] = *reinterpret_cast<const float4 *>(q0 + (p / R) * NB * IN_STRIDE + (p % R) * WIN * CP + 4 * S * c4);
 #pragma unroll
             for (int cc = 0; cc < 4; cc++) {
-              const float *wr = wk + (4 * c4 + cc) * O;
+              const float *wr = wk + (4 * S * c4 + cc) * O;
 #pragma unroll
               for (int q4 = 0; q4 < Q / 4; q4++) {
                 const float4 w = *reinterpret_cast<const float4 *>(wr + q4 * G * 4);
-                acc0[4 * q4 + 0] = fmaf(a0[cc], w.x, acc0[4 * q4 + 0]); acc1[4 * q4 + 0] = fmaf(a1[cc], w.x, acc1[4 * q4 + 0]);
-                acc0[4 * q4 + 1] = fmaf(a0[cc], w.y, acc0[4 * q4 + 1]); acc1[4 * q4 + 1] = fmaf(a1[cc], w.y, acc1[4 * q4 + 1]);
-                acc0[4 * q4 + 2] = fmaf(a0[cc], w.z, acc0[4 * q4 + 2]); acc1[4 * q4 + 2] = fmaf(a1[cc], w.z, acc1[4 * q4 + 2]);
-                acc0[4 * q4 + 3] = fmaf(a0[cc], w.w, acc0[4 * q4 + 3]); acc1[4 * q4 + 3] = fmaf(a1[cc], w.w, acc1[4 * q4 + 3]);
+#pragma unroll
+                for (int p = 0; p < P; p++) {
+                  const float a = cc == 0 ? v[p].x : cc == 1 ? v[p].y : cc == 2 ? v[p].z : v[p].w;
+                  acc[p][4 * q4 + 0] = fmaf(a, w.x, acc[p][4 * q4 + 0]);
+                  acc[p][4 * q4 + 1] = fmaf(a, w.y, acc[p][4 * q4 + 1]);
+                  acc[p][4 * q4 + 2] = fmaf(a, w.z, acc[p][4 * q4 + 2]);
+                  acc[p][4 * q4 + 3] = fmaf(a, w.w, acc[p][4 * q4 + 3]);
+                }
               }
             }
           }
         }
       }
     }
-    // ReLU (nl_func_relu_array_f32) then max pool (pool_func_mp_array_f32), or two separate pixels
-    if (POOL) {
-      float *o0 = out + b * OUT_STRIDE + (py * WO + x) * OP + g * Q;
+    if (S > 1) {
+#pragma unroll
+      for (int p = 0; p < P; p++)
+#pragma unroll
+        for (int q = 0; q < Q; q++)
+#pragma unroll
+          for (int m = 1; m < S; m <<= 1) acc[p][q] += __shfl_xor_sync(0xffffffffu, acc[p][q], m * G);
+    }
+    // bias, ReLU (nl_func_relu_array_f32), then max pool over the two rows (pool_func_mp_array_f32); lane s of a split
+    // group stores clips s, s + S, ... of the tile
+    float bq[Q];
+#pragma unroll
+    for (int q = 0; q < Q; q++) bq[q] = KS > 1 ? 0.f : __ldg(bias + g * Q + q);
+#pragma unroll
+    for (int j = 0; j < PB; j++) {
+      if (!valid || (S > 1 && (j % S) != s)) continue;
+      float *o = out + (b + j * NB) * OUT_STRIDE + ((ks * HP + py) * WO + x) * OP + g * Q;
 #pragma unroll
       for (int q4 = 0; q4 < Q / 4; q4++) {
-        float4 r;
-        r.x = fmaxf(fmaxf(acc0[4 * q4 + 0], acc1[4 * q4 + 0]), 0.f);
-        r.y = fmaxf(fmaxf(acc0[4 * q4 + 1], acc1[4 * q4 + 1]), 0.f);
-        r.z = fmaxf(fmaxf(acc0[4 * q4 + 2], acc1[4 * q4 + 2]), 0.f);
-        r.w = fmaxf(fmaxf(acc0[4 * q4 + 3], acc1[4 * q4 + 3]), 0.f);
-        *reinterpret_cast<float4 *>(o0 + 4 * q4) = r;
-      }
-    } else {
-      float *o0 = out + b * OUT_STRIDE + ((ks * HP + py) * WO + x) * OP + g * Q;
-      float *o1 = o0 + (kCubeClips / 2) * OUT_STRIDE;
+        float r[4];
 #pragma unroll
-      for (int q = 0; q < Q; q++) {
-        if (KSPLIT == 1) { acc0[q] = fmaxf(acc0[q], 0.f); acc1[q] = fmaxf(acc1[q], 0.f); }
-      }
-#pragma unroll
-      for (int q4 = 0; q4 < Q / 4; q4++) {
-        *reinterpret_cast<float4 *>(o0 + 4 * q4) = make_float4(acc0[4 * q4 + 0], acc0[4 * q4 + 1], acc0[4 * q4 + 2], acc0[4 * q4 + 3]);
-        *reinterpret_cast<float4 *>(o1 + 4 * q4) = make_float4(acc1[4 * q4 + 0], acc1[4 * q4 + 1], acc1[4 * q4 + 2], acc1[4 * q4 + 3]);
+        for (int i = 0; i < 4; i++) {
+          const float t = POOL ? fmaxf(acc[j * R][4 * q4 + i], acc[j * R + R - 1][4 * q4 + i]) : acc[j][4 * q4 + i];
+          r[i] = KS > 1 ? t : fmaxf(t + bq[4 * q4 + i], 0.f);
+        }
+        *reinterpret_cast<float4 *>(o + 4 * q4) = make_float4(r[0], r[1], r[2], r[3]);
       }
     }
   }
@@ -214,18 +233,18 @@ cube_f32_kernel(const CubeModel *__restrict__ M, const float *__restrict__ net_i
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long c0 = tile * kCubeClips;
     const int nc = (int)((n - c0) < kCubeClips ? (n - c0) : kCubeClips);
-    conv_layer<31, 13, 1, 5, 5, 16, 8, true, 1, EDISON_NET_IN, kBufB, kPad>(S.stage, &S.b[0][0], S.w1, M->b1);
+    conv_layer<31, 13, 1, 5, 5, 16, 8, true, 2, 1, 1, EDISON_NET_IN, kBufB, kPad>(S.stage, &S.b[0][0], S.w1, M->b1);
     __syncthreads();
     if (tile + gridDim.x < n_tiles) stage_input(S.stage, net_in, (tile + gridDim.x) * kCubeClips, n, aligned);   // lands during conv2..4
-    conv_layer<13, 9, 16, 3, 3, 32, 8, true, 1, kBufB, kBufA, kPad>(&S.b[0][0], &S.a[0][0], S.w2, M->b2);
+    conv_layer<13, 9, 16, 3, 3, 32, 8, true, 2, 1, 1, kBufB, kBufA, kPad>(&S.b[0][0], &S.a[0][0], S.w2, M->b2);
     cp_async_wait_all();                  // w3 (issued after the previous tile's conv4) and the next input
     __syncthreads();
-    conv_layer<5, 7, 32, 3, 3, 64, 8, false, 1, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], S.wbig, M->b3);
+    conv_layer<5, 7, 32, 3, 3, 64, 8, false, 4, 2, 1, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], S.wbig, M->b3);
     __syncthreads();
     stage_floats(S.wbig, M->w4, kW4);
     cp_async_wait_all();
     __syncthreads();
-    conv_layer<3, 5, 64, 3, 3, 32, 4, false, 3, kBufB, kBufA, 0>(&S.b[0][0], &S.a[0][0], S.wbig, M->b4);
+    conv_layer<3, 5, 64, 3, 3, 32, 4, false, 8, 4, 3, kBufB, kBufA, 0>(&S.b[0][0], &S.a[0][0], S.wbig, M->b4);
     __syncthreads();
     if (tile + gridDim.x < n_tiles) stage_floats(S.wbig, M->w3, kW3);     // lands during the next tile's conv1/conv2
     // conv4 bias + ReLU on the sum of its three partial sums, then dense (forward_dense): 4 lanes per (clip, class)
