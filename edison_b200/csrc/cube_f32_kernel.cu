@@ -81,7 +81,7 @@ __device__ __forceinline__ void stage_floats(float *dst, const float *src, int n
 // and add their sums by shuffle; KS > 1 deals the kernel rows to KS threads, each writing a raw partial sum (no bias, no
 // ReLU) to out[clip][split][pixel][O] for the consumer to add up.  Shared memory hands a lane 4 B per clock whatever the broadcast, so the tile shape sets
 // the ceiling: P*Q FFMAs per P+Q loaded floats (2x8 = 1.6 held the FMA pipe at 41 %; 4x8 = 2.7, 8x8 = 4.0).
-template <int HIN, int WIN, int C, int KH, int KW, int O, int Q, bool POOL, int PB, int S, int KS, int IN_STRIDE, int OUT_STRIDE, int OPAD>
+template <int HIN, int WIN, int C, int KH, int KW, int O, int Q, bool POOL, int PB, int S, int KS, bool PIXBIT, int IN_STRIDE, int OUT_STRIDE, int OPAD>
 __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *__restrict__ out, const float *__restrict__ wgt,
                                            const float *__restrict__ bias) {
   constexpr int HO = HIN - KH + 1, WO = WIN - KW + 1;
@@ -93,23 +93,30 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
   constexpr int NB = kCubeClips / PB;            // clip groups; a thread's clips are b, b + NB, ...
   constexpr int R = POOL ? 2 : 1;                // conv rows per clip in the tile
   constexpr int P = PB * R;
-  constexpr int NITEMS = S * G * KS * NB * NPIX;
+  constexpr int NREST = KS * NB * NPIX;                            // (row split, clip group, pixel) triples
+  static_assert(!PIXBIT || KS == 1 || (NB * NPIX) % 2 == 0, "a lane pair must not straddle two kernel rows");
+  constexpr int NITEMS = S * G * (PIXBIT ? (NREST + 1) / 2 * 2 : NREST);
   constexpr int KROWS = KH / KS;
   constexpr int C4 = C == 1 ? 1 : C / 4;
-  static_assert(kCubeClips % PB == 0 && (S & (S - 1)) == 0 && S * G <= 32 && 32 % (S * G) == 0 && (C == 1 ? S == 1 : C4 % S == 0), "tile shape");
+  constexpr int LB = PIXBIT ? 2 : 1;              // lanes of one (g, s) before the next
+  static_assert(kCubeClips % PB == 0 && (S & (S - 1)) == 0 && LB * S * G <= 32 && 32 % (LB * S * G) == 0 && (C == 1 ? S == 1 : C4 % S == 0), "tile shape");
   static_assert(KH % KS == 0 && (KS == 1 || !POOL), "row split");
   constexpr int NROUNDS = (NITEMS + kCubeThreads - 1) / kCubeThreads;
 #pragma unroll 1
   for (int round = 0; round < NROUNDS; round++) {
     const int item_raw = round * kCubeThreads + threadIdx.x;
     if (S > 1 ? (item_raw & ~31) >= NITEMS : item_raw >= NITEMS) break;      // whole warps stay for the shuffles
-    const bool valid = item_raw < NITEMS;
-    const int item = valid ? item_raw : 0;
-    const int g = item % G;                      // a quarter warp reads one line of weights and one pixel
-    const int s = (item / G) % S;
-    int rest = item / (S * G);
-    const int ks = KS > 1 ? rest % KS : 0;
-    if (KS > 1) rest /= KS;
+    // lane order: [pixel bit] g s rest.  A 128-bit shared load costs the data pipe 4 clocks when neighbouring lanes read
+    // different addresses and 2.1 when each even/odd pair shares one or the pairs alternate between two (tools/ubench/lds.cu):
+    // with the pixel bit lowest, weight reads are of the first kind of cheap and pixel reads of the second.
+    const int item = item_raw < NITEMS ? item_raw : 0;
+    const int g = (item / LB) % G;
+    const int s = (item / (LB * G)) % S;
+    int rest = PIXBIT ? 2 * (item / (2 * S * G)) + (item & 1) : item / (S * G);
+    const bool valid = item_raw < NITEMS && rest < NREST;
+    if (rest >= NREST) rest = 0;
+    const int ks = KS > 1 ? rest / (NB * NPIX) : 0;       // slowest, so that a lane pair reads the same kernel row's weights
+    if (KS > 1) rest -= ks * (NB * NPIX);
     const int b = rest / NPIX, pix = rest - b * NPIX;
     const int py = pix / WO, x = pix - py * WO;
     const float *p0 = in + b * IN_STRIDE + ((R * py) * WIN + x) * CP + (C == 1 ? 0 : 4 * s);
@@ -118,7 +125,7 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
     for (int p = 0; p < P; p++)
 #pragma unroll
       for (int q = 0; q < Q; q++) acc[p][q] = 0.f;
-    const float *wg = wgt + g * 4 + (C == 1 ? 0 : 4 * s * O);   // weights [k][c][q4][g][4]: a warp's read is contiguous lines
+    const float *wg = wgt + (s * G + g) * 4;     // weights [k][c4 / S][cc][q4][s][g][4]: a warp's read is contiguous lines
 #pragma unroll 1
     for (int ky = ks * KROWS; ky < (ks + 1) * KROWS; ky++) {
       if (C == 1) {
@@ -153,10 +160,10 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
               v[p] = *reinterpret_cast<const float4 *>(q0 + (p / R) * NB * IN_STRIDE + (p % R) * WIN * CP + 4 * S * c4);
 #pragma unroll
             for (int cc = 0; cc < 4; cc++) {
-              const float *wr = wk + (4 * S * c4 + cc) * O;
+              const float *wr = wk + (4 * c4 + cc) * S * O;
 #pragma unroll
               for (int q4 = 0; q4 < Q / 4; q4++) {
-                const float4 w = *reinterpret_cast<const float4 *>(wr + q4 * G * 4);
+                const float4 w = *reinterpret_cast<const float4 *>(wr + q4 * S * G * 4);
 #pragma unroll
                 for (int p = 0; p < P; p++) {
                   const float a = cc == 0 ? v[p].x : cc == 1 ? v[p].y : cc == 2 ? v[p].z : v[p].w;
@@ -177,7 +184,7 @@ __device__ __forceinline__ void conv_layer(const float *__restrict__ in, float *
 #pragma unroll
         for (int q = 0; q < Q; q++)
 #pragma unroll
-          for (int m = 1; m < S; m <<= 1) acc[p][q] += __shfl_xor_sync(0xffffffffu, acc[p][q], m * G);
+          for (int m = 1; m < S; m <<= 1) acc[p][q] += __shfl_xor_sync(0xffffffffu, acc[p][q], m * G * LB);
     }
     // bias, ReLU (nl_func_relu_array_f32), then max pool over the two rows (pool_func_mp_array_f32); lane s of a split
     // group stores clips s, s + S, ... of the tile
@@ -233,18 +240,18 @@ cube_f32_kernel(const CubeModel *__restrict__ M, const float *__restrict__ net_i
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long c0 = tile * kCubeClips;
     const int nc = (int)((n - c0) < kCubeClips ? (n - c0) : kCubeClips);
-    conv_layer<31, 13, 1, 5, 5, 16, 8, true, 2, 1, 1, EDISON_NET_IN, kBufB, kPad>(S.stage, &S.b[0][0], S.w1, M->b1);
+    conv_layer<31, 13, 1, 5, 5, 16, 8, true, 2, 1, 1, false, EDISON_NET_IN, kBufB, kPad>(S.stage, &S.b[0][0], S.w1, M->b1);
     __syncthreads();
     if (tile + gridDim.x < n_tiles) stage_input(S.stage, net_in, (tile + gridDim.x) * kCubeClips, n, aligned);   // lands during conv2..4
-    conv_layer<13, 9, 16, 3, 3, 32, 8, true, 2, 1, 1, kBufB, kBufA, kPad>(&S.b[0][0], &S.a[0][0], S.w2, M->b2);
+    conv_layer<13, 9, 16, 3, 3, 32, 8, true, 2, 1, 1, true, kBufB, kBufA, kPad>(&S.b[0][0], &S.a[0][0], S.w2, M->b2);
     cp_async_wait_all();                  // w3 (issued after the previous tile's conv4) and the next input
     __syncthreads();
-    conv_layer<5, 7, 32, 3, 3, 64, 8, false, 4, 2, 1, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], S.wbig, M->b3);
+    conv_layer<5, 7, 32, 3, 3, 64, 8, false, 4, 2, 1, true, kBufA, kBufB, kPad>(&S.a[0][0], &S.b[0][0], S.wbig, M->b3);
     __syncthreads();
     stage_floats(S.wbig, M->w4, kW4);
     cp_async_wait_all();
     __syncthreads();
-    conv_layer<3, 5, 64, 3, 3, 32, 4, false, 8, 4, 3, kBufB, kBufA, 0>(&S.b[0][0], &S.a[0][0], S.wbig, M->b4);
+    conv_layer<3, 5, 64, 3, 3, 32, 4, false, 4, 2, 3, true, kBufB, kBufA, 0>(&S.b[0][0], &S.a[0][0], S.wbig, M->b4);
     __syncthreads();
     if (tile + gridDim.x < n_tiles) stage_floats(S.wbig, M->w3, kW3);     // lands during the next tile's conv1/conv2
     // conv4 bias + ReLU on the sum of its three partial sums, then dense (forward_dense): 4 lanes per (clip, class)
@@ -313,11 +320,16 @@ static int cube_load(const char *path) {
     if (off + 4 * (nw + co) > raw.size()) { delete h; return ctx_fail(EDISON_E_DATA, "%s: truncated", path); }
     const float *w = reinterpret_cast<const float *>(&raw[off]);
     if (hd[0] == 1) {
-      const size_t Q = l == 3 ? 4 : 8, G = co / Q;     // per-thread channel tile of each layer (conv_layer<..., Q, ...>)
-      for (size_t o = 0; o < co; o++) {                // O,H,W,I (kws.c strides) -> [ky][kx][c][q4][g][4], o = g*Q + 4*q4 + j
+      // per-thread channel tile Q and lane split S of each layer (conv_layer<..., Q, ..., S, ...>)
+      const size_t Q = l == 3 ? 4 : 8, S = l == 2 ? 2 : l == 3 ? 2 : 1, G = co / Q;
+      for (size_t o = 0; o < co; o++) {                // O,H,W,I (kws.c strides) -> [k][c4 / S][cc][q4][s][g][4], o = g*Q + 4*q4 + j
         const size_t g = o / Q, q4 = (o % Q) / 4, j = o % 4;
         for (size_t k = 0; k < kh * kw; k++)
-          for (size_t c = 0; c < ci; c++) wdst[l][(k * ci + c) * co + (q4 * G + g) * 4 + j] = w[(o * kh * kw + k) * ci + c];
+          for (size_t c = 0; c < ci; c++) {
+            const size_t c4 = c / 4, cc = c % 4, sp = ci == 1 ? 0 : c4 % S, jj = ci == 1 ? 0 : c4 / S;
+            const size_t row = ci == 1 ? k : (k * (ci / 4 / S) + jj) * 4 + cc;        // (tap, channel-block group, cc)
+            wdst[l][((row * (Q / 4) + q4) * S + sp) * G * 4 + g * 4 + j] = w[(o * kh * kw + k) * ci + c];
+          }
       }
     } else {
       memcpy(wdst[l], w, 4 * nw);
