@@ -5,6 +5,7 @@ libedison_b200.so through ctypes here.  Nothing in this package computes: every 
 to the CUDA library and raises if it is missing or no GPU is usable.
 """
 from . import capi  # noqa: F401
+from . import kws  # noqa: F401
 from .capi import (  # noqa: F401
     EdisonError,
     FRAME_LEN,
