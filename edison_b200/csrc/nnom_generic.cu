@@ -1,13 +1,20 @@
-// nnom_generic.cu -- generic executor for NNoM int8 models of the sequential conv/dense family.
+// nnom_generic.cu -- generic executor for NNoM int8 models.
 //
-// K2 (nnom_q7_kernel.cu) is specialised for the reference's kws model.  Any other model that nnom_utils.py generates from the
-// same layer vocabulary -- Input, Conv2D (valid, stride 1), ReLU, MaxPool (p,1)/(p,1), Dense, Softmax -- is converted by
-// tools/convert_nnom_weights.py into the same blob format and runs here layer by layer with activations in HBM: one thread
-// per output element, dp4a over the channel axis when it is a multiple of 4.  Same arithmetic as K2 and as the reference
-// (local_convolve_HWC_q7_nonsquare nnom_local.c:425-484, local_maxpool_q7_HWC :117-160, local_fully_connected_q7 :733-802,
-// softmax variants as in nnom_q7_kernel.cu), so results are bit-exact; it is a correctness-first fallback, not a tuned kernel.
-// Pinned against the upstream NNoM keyword_spotting example model (audio/edison/deploy/nnom/examples/keyword_spotting/mcu/
-// weights.h: 63x12 input, 35 classes) run through the reference's own NNoM runtime built for the host.
+// K2 (nnom_q7_kernel.cu) is specialised for the reference's kws model.  Any other model that nnom_utils.py generates from
+// the vocabulary below is converted to a blob -- tools/convert_nnom_weights.py (version 1: the conv/dense chain of the
+// reference model family) or tools/convert_nnom_graph.py (version 2: a graph) -- and runs here node by node with activations
+// in HBM: one thread per output element, dp4a over the channel axis when it is a multiple of 4.
+//   Input | Conv2D any kernel / stride, PADDING_VALID or PADDING_SAME (+ ReLU tail) | MaxPool any kernel / stride / padding |
+//   GlobalMaxPool | Concat on the channel axis | Add with output shift (+ ReLU tail) | Dense (+ ReLU tail) | Softmax
+// Same arithmetic as the reference's NNoM runtime, local backend (firmware/src/ai/nnom/src):
+//   conv nnom_conv2d.c:77-82, :101-112 + nnom_local.c:425-483; max pool nnom_maxpool.c:66-104 + nnom_local.c:117-159;
+//   global max pool nnom_global_pool.c:93-96; concat nnom_concat.c:186-213; add nnom_local.c:1109-1126;
+//   dense nnom_local.c:804-921; softmax variants as in nnom_q7_kernel.cu
+// so results are bit-exact; it is a correctness-first path, not a tuned kernel.  Pinned against three upstream NNoM example
+// models inside the reference tree (keyword_spotting, mnist-simple, uci-inception) run through the reference's own runtime
+// built for the host (tests/golden/nnom_example.npz, nnom_graphs.npz).  Not supported, because this NNoM version does not
+// compute them reproducibly: Concat of unequal inputs (nnom_concat.c:104, :208 size every input like the first) and
+// UpSample (nnom_local.c:383 never writes the odd rows).
 #include <stdio.h>
 #include <string.h>
 
@@ -18,68 +25,117 @@
 
 namespace edison {
 
-struct GenLayer {
-  int kind, cout, kh, kw, cin, rshift, lshift, relu, pool;
-  int in_h, in_w, out_h, out_w;       // conv: out_h is after pooling
+enum { G_INPUT, G_CONV, G_DENSE, G_MAXPOOL, G_CONCAT, G_SOFTMAX, G_GMAXPOOL, G_ADD };
+constexpr int kMaxNodes = 64;
+
+struct GenNode {
+  int op, n_in, in[8];
+  int cout, kh, kw, sh, sw, ph, pw, same, rshift, lshift, relu;
+  int H, W, C;                        // output shape
+  int aH, aW, aC;                     // shape of the first input
   long long w_off, b_off;             // into the device weight buffer
+  long long act_off, act_size;        // per input: offset and size of this node's output in the arena
 };
 
 __device__ __forceinline__ int g_ssat8(int v) { return min(max(v, -128), 127); }
 __device__ __forceinline__ int g_usat(int v, int bits) { return min(max(v, 0), (1 << bits) - 1); }
 
-// conv (valid, stride 1) + optional ReLU + optional (pool x 1) max pool.  in: [n][H][W][C], out: [n][HP][WO][O]
+// conv + optional ReLU.  in: [n][aH][aW][aC], out: [n][H][W][C]; taps outside the image are skipped
 __global__ void gen_conv_kernel(const int8_t *__restrict__ in, int8_t *__restrict__ out, const int8_t *__restrict__ w,
-                                const int8_t *__restrict__ b, GenLayer L, long long n) {
-  const int O = L.cout, C = L.cin, W = L.in_w, WO = L.out_w, HP = L.out_h, P = L.pool ? L.pool : 1;
-  const long long total = n * HP * WO * O;
+                                const int8_t *__restrict__ b, GenNode L, long long n) {
+  const int O = L.C, C = L.aC;
+  const long long total = n * L.H * L.W * O;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
     const int o = (int)(idx % O);
     long long r = idx / O;
-    const int x = (int)(r % WO); r /= WO;
-    const int yp = (int)(r % HP);
-    const long long clip = r / HP;
-    const int8_t *src = in + clip * ((long long)L.in_h * W * C);
+    const int x = (int)(r % L.W); r /= L.W;
+    const int y = (int)(r % L.H);
+    const long long clip = r / L.H;
+    const int8_t *src = in + clip * ((long long)L.aH * L.aW * C);
     const int8_t *wo = w + (long long)o * L.kh * L.kw * C;
-    const int seed = (int)((unsigned)(int)b[o] << L.lshift) + (1 << (L.rshift - 1));
-    int best = -129;
-    for (int p = 0; p < P; p++) {
-      const int y = yp * P + p;
-      int acc = seed;
-      for (int ky = 0; ky < L.kh; ky++) {
-        const int8_t *row = src + ((long long)(y + ky) * W + x) * C;
-        const int8_t *wr = wo + ky * L.kw * C;
-        const int len = L.kw * C;            // contiguous in both operands (HWC activations, O,H,W,I weights)
-        int i = 0;
-        if ((C & 3) == 0) {
-          for (; i < len; i += 4)
-            acc = __dp4a(*reinterpret_cast<const int *>(row + i), *reinterpret_cast<const int *>(wr + i), acc);
-        } else {
-          for (; i < len; i++) acc += (int)row[i] * (int)wr[i];
-        }
+    int acc = (int)((unsigned)(int)b[o] << L.lshift) + (1 << (L.rshift - 1));
+    const int c0 = x * L.sw - L.pw;
+    const int kx0 = c0 < 0 ? -c0 : 0, kx1 = min(L.kw, L.aW - c0);   // the valid taps of a row are contiguous in both operands
+    for (int ky = 0; ky < L.kh; ky++) {
+      const int row = y * L.sh - L.ph + ky;
+      if (row < 0 || row >= L.aH || kx1 <= kx0) continue;
+      const int8_t *a = src + ((long long)row * L.aW + c0 + kx0) * C;
+      const int8_t *wr = wo + (ky * L.kw + kx0) * C;
+      const int len = (kx1 - kx0) * C;
+      int i = 0;
+      if ((C & 3) == 0) {
+        for (; i < len; i += 4)
+          acc = __dp4a(*reinterpret_cast<const int *>(a + i), *reinterpret_cast<const int *>(wr + i), acc);
+      } else {
+        for (; i < len; i++) acc += (int)a[i] * (int)wr[i];
       }
-      int v = g_ssat8(acc >> L.rshift);
-      if (L.relu && v < 0) v = 0;
-      best = max(best, v);
     }
-    out[idx] = (int8_t)best;
+    int v = g_ssat8(acc >> L.rshift);
+    if (L.relu && v < 0) v = 0;
+    out[idx] = (int8_t)v;
   }
 }
 
-// dense: in [n][cin] (the flattened H,W,C output of the previous layer), w [cout][cin]
+// dense: in [n][cin] (the flattened H,W,C output of the previous node), w [cout][cin]
 __global__ void gen_dense_kernel(const int8_t *__restrict__ in, int8_t *__restrict__ out, const int8_t *__restrict__ w,
-                                 const int8_t *__restrict__ b, GenLayer L, long long n) {
-  const long long total = n * L.cout;
+                                 const int8_t *__restrict__ b, GenNode L, long long n) {
+  const int cin = L.aH * L.aW * L.aC;
+  const long long total = n * L.C;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
-    const int o = (int)(idx % L.cout);
-    const long long clip = idx / L.cout;
-    const int8_t *x = in + clip * L.cin, *wr = w + (long long)o * L.cin;
+    const int o = (int)(idx % L.C);
+    const long long clip = idx / L.C;
+    const int8_t *x = in + clip * cin, *wr = w + (long long)o * cin;
     int acc = (int)((unsigned)(int)b[o] << L.lshift) + (1 << (L.rshift - 1));
     int i = 0;
-    if ((L.cin & 3) == 0)
-      for (; i < L.cin; i += 4) acc = __dp4a(*reinterpret_cast<const int *>(x + i), *reinterpret_cast<const int *>(wr + i), acc);
+    if ((cin & 3) == 0)
+      for (; i < cin; i += 4) acc = __dp4a(*reinterpret_cast<const int *>(x + i), *reinterpret_cast<const int *>(wr + i), acc);
     else
-      for (; i < L.cin; i++) acc += (int)x[i] * (int)wr[i];
+      for (; i < cin; i++) acc += (int)x[i] * (int)wr[i];
     int v = g_ssat8(acc >> L.rshift);
+    if (L.relu && v < 0) v = 0;
+    out[idx] = (int8_t)v;
+  }
+}
+
+// max pool (also the global one: kernel = the whole map).  Starts from -129 and stores the int as q7, as the reference does
+__global__ void gen_maxpool_kernel(const int8_t *__restrict__ in, int8_t *__restrict__ out, GenNode L, long long n) {
+  const int C = L.C;
+  const long long total = n * L.H * L.W * C;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % C);
+    long long r = idx / C;
+    const int x = (int)(r % L.W); r /= L.W;
+    const int y = (int)(r % L.H);
+    const long long clip = r / L.H;
+    const int8_t *src = in + clip * ((long long)L.aH * L.aW * C) + c;
+    int mx = -129;
+    for (int ky = y * L.sh - L.ph; ky < y * L.sh - L.ph + L.kh; ky++)
+      for (int kx = x * L.sw - L.pw; kx < x * L.sw - L.pw + L.kw; kx++)
+        if (ky >= 0 && kx >= 0 && ky < L.aH && kx < L.aW) mx = max(mx, (int)src[((long long)ky * L.aW + kx) * C]);
+    out[idx] = (int8_t)mx;
+  }
+}
+
+struct ConcatSrc { const int8_t *p[8]; };
+
+// channel-axis concat of n_in equally shaped inputs
+__global__ void gen_concat_kernel(ConcatSrc src, int8_t *__restrict__ out, GenNode L, long long n) {
+  const int Ca = L.aC, C = L.C;
+  const long long total = n * L.H * L.W * C;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % C);
+    const long long px = idx / C;
+    const int k = c / Ca;
+    out[idx] = src.p[k][px * Ca + (c - k * Ca)];
+  }
+}
+
+// add with rounding output shift + optional ReLU
+__global__ void gen_add_kernel(const int8_t *__restrict__ a, const int8_t *__restrict__ b, int8_t *__restrict__ out, GenNode L,
+                               long long n) {
+  const long long total = n * L.H * L.W * L.C;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    int v = g_ssat8(((int)a[idx] + (int)b[idx] + (1 << (L.rshift - 1))) >> L.rshift);
     if (L.relu && v < 0) v = 0;
     out[idx] = (int8_t)v;
   }
@@ -128,22 +184,22 @@ __global__ void gen_softmax_kernel(const int8_t *__restrict__ in, int8_t *__rest
 }  // namespace edison
 
 struct edison_model {
-  int n_layers;
-  edison::GenLayer L[16];
+  int n_nodes, out_node;
+  edison::GenNode N[edison::kMaxNodes];
   int8_t *d_w;               // all weights and biases, 4-byte aligned per array
   int in_h, in_w, in_c, in_size, n_out;
-  long long max_act;         // bytes per clip of the largest activation
-  int8_t *d_act[2], *d_in, *d_lg, *d_sm;
-  size_t cap;                // clips the scratch buffers hold
+  long long arena_per_input; // bytes per input of all intermediate activations
+  int8_t *d_arena, *d_in, *d_lg, *d_sm;
+  size_t cap;                // inputs the scratch buffers hold
 };
 
 namespace edison {
 
 static int model_reserve(edison_model *m, size_t n) {
   if (n <= m->cap) return EDISON_OK;
-  int8_t **bufs[] = {&m->d_act[0], &m->d_act[1], &m->d_in, &m->d_lg, &m->d_sm};
-  const size_t per[] = {(size_t)m->max_act, (size_t)m->max_act, (size_t)m->in_size, (size_t)m->n_out, (size_t)m->n_out};
-  for (int i = 0; i < 5; i++) {
+  int8_t **bufs[] = {&m->d_arena, &m->d_in, &m->d_lg, &m->d_sm};
+  const size_t per[] = {(size_t)m->arena_per_input, (size_t)m->in_size, (size_t)m->n_out, (size_t)m->n_out};
+  for (int i = 0; i < 4; i++) {
     if (*bufs[i]) cudaFree(*bufs[i]);
     *bufs[i] = nullptr;
     cudaError_t e = cudaMalloc(bufs[i], n * per[i] + 16);
@@ -155,20 +211,35 @@ static int model_reserve(edison_model *m, size_t n) {
 
 static int model_run(edison_model *m, const CtxView &c, const int8_t *d_in, size_t n, int8_t *d_logits, int8_t *d_softmax,
                      cudaStream_t st) {
-  const int8_t *cur = d_in;
   const int threads = 256;
   auto blocks = [&](long long total) { long long b = (total + threads - 1) / threads; const long long cap = (long long)c.sm_count * 32; return (unsigned)(b < cap ? (b > 0 ? b : 1) : cap); };
-  for (int i = 0; i < m->n_layers; i++) {
-    const GenLayer &L = m->L[i];
-    int8_t *dst = (i == m->n_layers - 1) ? d_logits : m->d_act[i & 1];
-    if (L.kind == 1) {
-      const long long total = (long long)n * L.out_h * L.out_w * L.cout;
-      gen_conv_kernel<<<blocks(total), threads, 0, st>>>(cur, dst, m->d_w + L.w_off, m->d_w + L.b_off, L, (long long)n);
-    } else {
-      gen_dense_kernel<<<blocks((long long)n * L.cout), threads, 0, st>>>(cur, dst, m->d_w + L.w_off, m->d_w + L.b_off, L, (long long)n);
+  // node i's output for all n inputs: [n][H][W][C] at arena + act_off * n; the input node is the caller's buffer and the
+  // output node (the softmax layer's input) goes straight to d_logits
+  auto act = [&](int i) -> int8_t * {
+    if (i == 0) return const_cast<int8_t *>(d_in);
+    if (i == m->out_node) return d_logits;
+    return m->d_arena + m->N[i].act_off * (long long)n;
+  };
+  for (int i = 1; i < m->n_nodes; i++) {
+    const GenNode &L = m->N[i];
+    const long long total = (long long)n * L.H * L.W * L.C;
+    int8_t *dst = act(i);
+    switch (L.op) {
+      case G_CONV: gen_conv_kernel<<<blocks(total), threads, 0, st>>>(act(L.in[0]), dst, m->d_w + L.w_off, m->d_w + L.b_off, L, (long long)n); break;
+      case G_DENSE: gen_dense_kernel<<<blocks(total), threads, 0, st>>>(act(L.in[0]), dst, m->d_w + L.w_off, m->d_w + L.b_off, L, (long long)n); break;
+      case G_MAXPOOL:
+      case G_GMAXPOOL: gen_maxpool_kernel<<<blocks(total), threads, 0, st>>>(act(L.in[0]), dst, L, (long long)n); break;
+      case G_CONCAT: {
+        ConcatSrc s;
+        for (int k = 0; k < 8; k++) s.p[k] = k < L.n_in ? act(L.in[k]) : nullptr;
+        gen_concat_kernel<<<blocks(total), threads, 0, st>>>(s, dst, L, (long long)n);
+        break;
+      }
+      case G_ADD: gen_add_kernel<<<blocks(total), threads, 0, st>>>(act(L.in[0]), act(L.in[1]), dst, L, (long long)n); break;
+      case G_SOFTMAX: continue;         // below, in the context's softmax variant
+      default: return ctx_fail(EDISON_E_MODEL, "generic NNoM executor: node %d has op %d", i, L.op);
     }
     count_launch();
-    cur = dst;
   }
   if (d_softmax) {
     gen_softmax_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_logits, d_softmax, m->n_out, (long long)n, c.softmax_mode);
@@ -183,6 +254,169 @@ static bool gen_dev_ptr(const void *p) {
   cudaPointerAttributes a;
   if (!p || cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
   return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+static int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// append a node; weights (if any) are copied into wbuf.  Returns 0 or an error string
+static const char *add_node(edison_model *m, std::vector<int8_t> &wbuf, GenNode L, const int8_t *w, size_t nw, const int8_t *b, size_t nb) {
+  if (m->n_nodes >= kMaxNodes) return "too many nodes";
+  const int i = m->n_nodes;
+  for (int k = 0; k < L.n_in; k++)
+    if (L.in[k] < 0 || L.in[k] >= i) return "input index out of order";
+  const GenNode *A = L.n_in ? &m->N[L.in[0]] : nullptr;
+  if (L.op != G_INPUT && !A) return "node without input";
+  if (A) { L.aH = A->H; L.aW = A->W; L.aC = A->C; }
+  switch (L.op) {
+    case G_INPUT: break;
+    case G_CONV:
+      if (L.kh < 1 || L.kw < 1 || L.sh < 1 || L.sw < 1 || L.rshift < 1 || L.rshift > 31 || L.lshift < 0 || L.lshift > 24) return "conv parameters out of range";
+      L.H = L.same ? ceil_div(A->H, L.sh) : ceil_div(A->H - L.kh + 1, L.sh);
+      L.W = L.same ? ceil_div(A->W, L.sw) : ceil_div(A->W - L.kw + 1, L.sw);
+      L.C = L.cout;
+      if (nw != (size_t)L.cout * L.kh * L.kw * A->C || nb != (size_t)L.cout) return "conv weights do not fit the input channels";
+      break;
+    case G_DENSE:
+      if (L.rshift < 1 || L.rshift > 31 || L.lshift < 0 || L.lshift > 24) return "dense shifts out of range";
+      L.H = L.W = 1; L.C = L.cout;
+      if (nw != (size_t)L.cout * A->H * A->W * A->C || nb != (size_t)L.cout) return "dense weights do not fit the input";
+      break;
+    case G_MAXPOOL:
+      if (L.kh < 1 || L.kw < 1 || L.sh < 1 || L.sw < 1) return "pool parameters out of range";
+      L.H = L.same ? ceil_div(A->H, L.sh) : ceil_div(A->H - L.kh + 1, L.sh);
+      L.W = L.same ? ceil_div(A->W, L.sw) : ceil_div(A->W - L.kw + 1, L.sw);
+      L.C = A->C;
+      break;
+    case G_GMAXPOOL:
+      L.kh = A->H; L.kw = A->W; L.sh = L.sw = 1; L.ph = L.pw = 0;
+      L.H = L.W = 1; L.C = A->C;
+      break;
+    case G_CONCAT:
+      if (L.n_in < 2) return "concat needs two inputs or more";
+      for (int k = 1; k < L.n_in; k++) {
+        const GenNode &B = m->N[L.in[k]];
+        if (B.H != A->H || B.W != A->W || B.C != A->C) return "concat inputs differ in shape (not reproducible in the reference runtime)";
+      }
+      L.H = A->H; L.W = A->W; L.C = A->C * L.n_in;
+      break;
+    case G_ADD: {
+      if (L.n_in != 2 || L.rshift < 1 || L.rshift > 15) return "add needs two inputs and a shift of 1..15";
+      const GenNode &B = m->N[L.in[1]];
+      if (B.H != A->H || B.W != A->W || B.C != A->C) return "add inputs differ in shape";
+      L.H = A->H; L.W = A->W; L.C = A->C;
+      break;
+    }
+    case G_SOFTMAX: L.H = A->H; L.W = A->W; L.C = A->C; break;
+    default: return "unknown op";
+  }
+  if (L.H < 1 || L.W < 1 || L.C < 1) return "empty output";
+  if (nw) {
+    L.w_off = (long long)wbuf.size();
+    wbuf.insert(wbuf.end(), w, w + nw);
+    wbuf.resize((wbuf.size() + 3) & ~(size_t)3);
+    L.b_off = (long long)wbuf.size();
+    wbuf.insert(wbuf.end(), b, b + nb);
+    wbuf.resize((wbuf.size() + 3) & ~(size_t)3);
+  }
+  L.act_size = ((long long)L.H * L.W * L.C + 3) & ~3LL;
+  L.act_off = m->arena_per_input;
+  if (L.op != G_INPUT && L.op != G_SOFTMAX) m->arena_per_input += L.act_size;
+  m->N[i] = L;
+  m->n_nodes = i + 1;
+  return nullptr;
+}
+
+static GenNode blank_node(int op, int n_in) {
+  GenNode L;
+  memset(&L, 0, sizeof L);
+  L.op = op; L.n_in = n_in;
+  for (int k = 0; k < 8; k++) L.in[k] = -1;
+  return L;
+}
+
+static const char *parse_v1(edison_model *m, std::vector<int8_t> &wbuf, const std::vector<unsigned char> &raw, uint32_t nl) {
+  // the trailer holds the input shape: walk the layers once to find it
+  size_t off = 16;
+  for (uint32_t i = 0; i < nl; i++) {
+    uint32_t h[9];
+    if (off + 36 > raw.size()) return "truncated";
+    memcpy(h, &raw[off], 36);
+    off += 36 + (size_t)h[1] * h[2] * h[3] * h[4] + h[1];
+    off = (off + 3) & ~(size_t)3;
+  }
+  if (off + 24 > raw.size()) return "trailer missing";
+  uint32_t s[3];
+  memcpy(s, &raw[off + 12], 12);
+  GenNode in = blank_node(G_INPUT, 0);
+  in.H = (int)s[0]; in.W = (int)s[1]; in.C = (int)s[2];
+  const char *err = add_node(m, wbuf, in, nullptr, 0, nullptr, 0);
+  if (err) return err;
+  off = 16;
+  for (uint32_t i = 0; i < nl; i++) {
+    uint32_t h[9];
+    memcpy(h, &raw[off], 36); off += 36;
+    const size_t nw = (size_t)h[1] * h[2] * h[3] * h[4];
+    const int8_t *w = (const int8_t *)&raw[off], *b = w + nw;
+    off = (off + nw + h[1] + 3) & ~(size_t)3;
+    if (h[0] != 1 && h[0] != 2) return "layer kind unsupported";
+    GenNode L = blank_node(h[0] == 1 ? G_CONV : G_DENSE, 1);
+    L.in[0] = m->n_nodes - 1;
+    L.cout = (int)h[1]; L.kh = (int)h[2]; L.kw = (int)h[3]; L.sh = L.sw = 1;
+    L.rshift = (int)h[5]; L.lshift = (int)h[6]; L.relu = h[7] ? 1 : 0;
+    const GenNode &A = m->N[L.in[0]];
+    if (h[0] == 1 && ((int)h[4] != A.C || L.kh > A.H || L.kw > A.W)) return "conv layer does not fit its input";
+    if ((err = add_node(m, wbuf, L, w, nw, b, h[1]))) return err;
+    if (h[0] == 1 && h[8]) {                       // (pool x 1) max pool, stride (pool, 1), valid
+      GenNode P = blank_node(G_MAXPOOL, 1);
+      P.in[0] = m->n_nodes - 1;
+      P.kh = P.sh = (int)h[8]; P.kw = P.sw = 1;
+      if (m->N[P.in[0]].H < P.kh) return "layer pools away its output";
+      if ((err = add_node(m, wbuf, P, nullptr, 0, nullptr, 0))) return err;
+    }
+  }
+  return nullptr;
+}
+
+static const char *parse_v2(edison_model *m, std::vector<int8_t> &wbuf, const std::vector<unsigned char> &raw, uint32_t nn) {
+  size_t off = 16;
+  for (uint32_t i = 0; i < nn; i++) {
+    uint32_t h[20];
+    if (off + 80 > raw.size()) return "truncated";
+    memcpy(h, &raw[off], 80); off += 80;
+    if (h[1] > 8) return "too many inputs";
+    GenNode L = blank_node((int)h[0], (int)h[1]);
+    for (uint32_t k = 0; k < h[1]; k++) L.in[k] = (int)h[2 + k];
+    const uint32_t *p = h + 10;
+    size_t nw = 0, nb = 0;
+    switch (L.op) {
+      case G_INPUT: L.H = (int)p[0]; L.W = (int)p[1]; L.C = (int)p[2]; if (i) return "input node must come first"; break;
+      case G_CONV:
+        L.cout = (int)p[0]; L.kh = (int)p[1]; L.kw = (int)p[2]; L.sh = (int)p[3]; L.sw = (int)p[4];
+        if (p[5]) { L.same = 1; L.ph = (L.kh - 1) / 2; L.pw = (L.kw - 1) / 2; }      // nnom_conv2d.c:77-82
+        L.rshift = (int)p[6]; L.lshift = (int)p[7]; L.relu = p[8] ? 1 : 0;
+        nw = (size_t)p[0] * p[1] * p[2] * p[9]; nb = p[0];
+        break;
+      case G_DENSE:
+        L.cout = (int)p[0]; L.rshift = (int)p[2]; L.lshift = (int)p[3]; L.relu = p[4] ? 1 : 0;
+        nw = (size_t)p[0] * p[1]; nb = p[0];
+        break;
+      case G_MAXPOOL:
+        L.kh = (int)p[0]; L.kw = (int)p[1]; L.sh = (int)p[2]; L.sw = (int)p[3];
+        if (p[4]) { L.same = 1; L.ph = (L.kh - 1) / 2; L.pw = (L.kw - 1) / 2; }      // nnom_maxpool.c:66-71
+        break;
+      case G_ADD: L.rshift = (int)p[0]; L.relu = p[1] ? 1 : 0; break;
+      case G_SOFTMAX: if (i != nn - 1) return "softmax must be the last node"; break;
+      default: break;
+    }
+    if (i == 0 && L.op != G_INPUT) return "input node must come first";
+    if (nw > raw.size() || off + nw + nb > raw.size()) return "truncated";
+    const int8_t *w = (const int8_t *)&raw[off];
+    const char *err = add_node(m, wbuf, L, w, nw, w + nw, nb);
+    if (err) return err;
+    if (nw) off = (off + nw + nb + 3) & ~(size_t)3;
+  }
+  if (off + 12 > raw.size()) return "trailer missing";
+  return nullptr;
 }
 
 }  // namespace edison
@@ -208,60 +442,28 @@ int edison_model_load(const char *blob_path, edison_model **out) {
   if (raw.size() < 16 || memcmp(raw.data(), "EDNNQ7\0\0", 8) != 0) return ctx_fail(EDISON_E_DATA, "%s: not an NNoM q7 blob", blob_path);
   uint32_t ver, nl;
   memcpy(&ver, &raw[8], 4); memcpy(&nl, &raw[12], 4);
-  if (ver != 1 || nl < 1 || nl > 16) return ctx_fail(EDISON_E_MODEL, "%s: version %u / %u layers unsupported", blob_path, ver, nl);
+  if ((ver != 1 && ver != 2) || nl < 1 || nl > (ver == 1 ? 16u : (uint32_t)kMaxNodes))
+    return ctx_fail(EDISON_E_MODEL, "%s: version %u / %u layers unsupported", blob_path, ver, nl);
   edison_model *m = new edison_model();
   memset(m, 0, sizeof *m);
-  m->n_layers = (int)nl;
   std::vector<int8_t> wbuf;
-  size_t off = 16;
-  for (uint32_t i = 0; i < nl; i++) {
-    uint32_t h[9];
-    if (off + 36 > raw.size()) { delete m; return ctx_fail(EDISON_E_DATA, "%s: truncated", blob_path); }
-    memcpy(h, &raw[off], 36); off += 36;
-    GenLayer &L = m->L[i];
-    L.kind = h[0]; L.cout = h[1]; L.kh = h[2]; L.kw = h[3]; L.cin = h[4]; L.rshift = h[5]; L.lshift = h[6]; L.relu = h[7]; L.pool = h[8];
-    const size_t nw = (size_t)L.cout * L.kh * L.kw * L.cin;
-    if ((L.kind != 1 && L.kind != 2) || L.rshift < 1 || L.rshift > 31 || L.lshift > 24 || off + nw + L.cout > raw.size()) {
-      delete m; return ctx_fail(EDISON_E_MODEL, "%s: layer %u unsupported or truncated", blob_path, i);
-    }
-    L.w_off = (long long)wbuf.size();
-    wbuf.insert(wbuf.end(), (int8_t *)&raw[off], (int8_t *)&raw[off] + nw);
-    wbuf.resize((wbuf.size() + 3) & ~(size_t)3);
-    off += nw;
-    L.b_off = (long long)wbuf.size();
-    wbuf.insert(wbuf.end(), (int8_t *)&raw[off], (int8_t *)&raw[off] + L.cout);
-    wbuf.resize((wbuf.size() + 3) & ~(size_t)3);
-    off += L.cout;
-    off = (off + 3) & ~(size_t)3;
+  const char *err = ver == 1 ? parse_v1(m, wbuf, raw, nl) : parse_v2(m, wbuf, raw, nl);
+  if (!err && m->n_nodes < 2) err = "no layers";
+  if (err) {
+    const int at = m->n_nodes;
+    delete m;
+    return ctx_fail(strstr(err, "truncated") || strstr(err, "trailer") ? EDISON_E_DATA : EDISON_E_MODEL, "%s: node %d: %s", blob_path, at, err);
   }
-  if (off + 24 > raw.size()) { delete m; return ctx_fail(EDISON_E_DATA, "%s: trailer missing", blob_path); }
-  uint32_t s[3];
-  memcpy(s, &raw[off + 12], 12);
-  m->in_h = s[0]; m->in_w = s[1]; m->in_c = s[2];
+  const GenNode &last = m->N[m->n_nodes - 1];
+  m->out_node = last.op == G_SOFTMAX ? last.in[0] : m->n_nodes - 1;
+  if (m->out_node < 1) { delete m; return ctx_fail(EDISON_E_MODEL, "%s: no output layer", blob_path); }
+  for (int i = 1; i < m->n_nodes; i++)
+    for (int k = 0; k < m->N[i].n_in; k++)
+      if (m->N[i].in[k] == m->out_node && m->N[i].op != G_SOFTMAX) { delete m; return ctx_fail(EDISON_E_MODEL, "%s: the output node has other readers", blob_path); }
+  m->in_h = m->N[0].H; m->in_w = m->N[0].W; m->in_c = m->N[0].C;
   m->in_size = m->in_h * m->in_w * m->in_c;
-  // shape propagation and checks
-  int H = m->in_h, W = m->in_w, C = m->in_c;
-  m->max_act = 4;
-  for (int i = 0; i < m->n_layers; i++) {
-    GenLayer &L = m->L[i];
-    if (L.kind == 1) {
-      if (L.cin != C || L.kh > H || L.kw > W) { delete m; return ctx_fail(EDISON_E_MODEL, "%s: conv layer %d does not fit its input (%dx%dx%d)", blob_path, i, H, W, C); }
-      L.in_h = H; L.in_w = W;
-      const int ho = H - L.kh + 1;
-      L.out_w = W - L.kw + 1;
-      L.out_h = L.pool ? (ho - L.pool) / L.pool + 1 : ho;
-      if (L.out_h < 1) { delete m; return ctx_fail(EDISON_E_MODEL, "%s: layer %d pools away its output", blob_path, i); }
-      H = L.out_h; W = L.out_w; C = L.cout;
-    } else {
-      if (L.cin != H * W * C) { delete m; return ctx_fail(EDISON_E_MODEL, "%s: dense layer %d expects %d inputs, gets %d", blob_path, i, L.cin, H * W * C); }
-      L.in_h = 1; L.in_w = 1; L.out_h = 1; L.out_w = 1;
-      H = 1; W = 1; C = L.cout;
-    }
-    const long long act = (long long)H * W * C;
-    if (act > m->max_act) m->max_act = act;
-  }
-  m->max_act = (m->max_act + 3) & ~3LL;
-  m->n_out = H * W * C;
+  m->n_out = m->N[m->out_node].H * m->N[m->out_node].W * m->N[m->out_node].C;
+  if (m->arena_per_input < 4) m->arena_per_input = 4;
   cudaError_t e = cudaMalloc(&m->d_w, wbuf.size() + 16);
   if (e == cudaSuccess) e = cudaMemcpy(m->d_w, wbuf.data(), wbuf.size(), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) { edison_model_free(m); return ctx_fail(EDISON_E_CUDA, "edison_model_load: %s", cudaGetErrorString(e)); }
@@ -272,7 +474,7 @@ int edison_model_load(const char *blob_path, edison_model **out) {
 void edison_model_free(edison_model *m) {
   if (!m) return;
   cudaDeviceSynchronize();
-  void *bufs[] = {m->d_w, m->d_act[0], m->d_act[1], m->d_in, m->d_lg, m->d_sm};
+  void *bufs[] = {m->d_w, m->d_arena, m->d_in, m->d_lg, m->d_sm};
   for (void *b : bufs)
     if (b) cudaFree(b);
   delete m;

@@ -156,11 +156,16 @@ void mfcc_compute(mfcc_t *mfcc, const int16_t *audio_data, int8_t *mfcc_out);
 int edison_infer_f32_batch(const float *net_in, size_t n, float *logits, float *softmax);
 int edison_infer_f32_batch_dev(const float *d_net_in, size_t n, float *d_logits, float *d_softmax, void *stream);
 
-/* ---- section 2d: any NNoM int8 model of the sequential conv/dense family (nnom_model_create() of a generated weights.h,
- * e.g. firmware/src/ai/nnom/kws_nnom/weights.h:138-161 or the upstream keyword_spotting example), converted by
- * tools/convert_nnom_weights.py.  Layer vocabulary: Input, Conv2D valid/stride 1, ReLU, MaxPool (p,1), Dense, Softmax.
- * in[n][in_h*in_w*in_c] int8 -> logits[n][n_out] (last Dense output), softmax[n][n_out] (mode of edison_set_softmax_mode);
- * host or device pointers (device pointers 4-byte aligned).  Bit-exact with the NNoM runtime; generic kernels, not K2. */
+/* ---- section 2d: any NNoM int8 model (nnom_model_create() of a generated weights.h, e.g.
+ * firmware/src/ai/nnom/kws_nnom/weights.h:138-161 or the upstream examples under audio/edison/deploy/nnom/examples), converted
+ * by tools/convert_nnom_weights.py (version-1 blob: the reference model's conv/dense chain) or tools/convert_nnom_graph.py
+ * (version-2 blob: a graph).  Node vocabulary: Input, Conv2D (any kernel and stride, PADDING_VALID / PADDING_SAME), ReLU tails,
+ * MaxPool (any kernel, stride, padding), GlobalMaxPool, Concat on the channel axis (equally shaped inputs), Add with output
+ * shift, Dense, Softmax.  Refused at load, because the reference's NNoM version does not compute them reproducibly: Concat of
+ * unequal inputs (nnom_concat.c:104, :208) and UpSample (nnom_local.c:383).
+ * in[n][in_h*in_w*in_c] int8 -> logits[n][n_out] (the softmax layer's input), softmax[n][n_out] (mode of
+ * edison_set_softmax_mode); host or device pointers (device pointers 4-byte aligned).  Bit-exact with the NNoM runtime
+ * (local backend); generic kernels, not K2. */
 typedef struct edison_model edison_model;
 int edison_model_load(const char *blob_path, edison_model **out);
 void edison_model_free(edison_model *m);

@@ -114,18 +114,23 @@ build_nnom local "$REF/audio/edison/deploy/nnom/port" "" 0
 build_nnom cmsis "$NNOM/port" "" 1
 # CMSIS-NN SIMD branches == firmware build
 build_nnom cmsis_simd "$NNOM/port" "-include arm_math.h -include $HERE/shim/dsp_shim_nn.h" 1
-# a second real model for the generic executor: upstream NNoM keyword_spotting example, local backend
-build_nnom_example () {
-  local d="$TMP/nn_example" objs="" i=0
+# more real models for the generic executor: upstream NNoM examples inside the reference tree, local backend.
+# (mnist-densenet and octave-conv are left out: this NNoM version's concat_build/concat_run size every input like the first
+#  one (nnom_concat.c:104, :208) and local_up_sampling_q7_HWC never writes the odd rows (nnom_local.c:383), so their
+#  outputs depend on stale buffer contents.)
+build_nnom_example () {  # $1 = example directory name, $2 = output library name
+  local d="$TMP/nn_example_$1" objs="" i=0
   mkdir -p "$d"
   local port="$REF/audio/edison/deploy/nnom/port"
-  local inc="-fPIC -w -O2 -ffunction-sections -fdata-sections -I$NNOM -I$port -I$NNOM/inc -I$REF/audio/edison/deploy/nnom/examples/keyword_spotting/mcu"
+  local inc="-fPIC -w -O2 -ffunction-sections -fdata-sections -I$NNOM -I$port -I$NNOM/inc -I$REF/audio/edison/deploy/nnom/examples/$1/mcu"
   for s in $NNOM_SRCS; do
     o="$d/n$i.o"; i=$((i+1))
     $CC $inc -c "$s" -o "$o"; objs="$objs $o"
   done
   $CC $inc -c "$HERE/drivers/ref_nnom_example_driver.c" -o "$d/driver.o"
-  $CC -shared -o "$OUT/libref_nnom_example_local.so" $objs "$d/driver.o" -Wl,--gc-sections -Wl,--version-script="$HERE/drivers/exports.map" -Wl,-z,defs -lm
+  $CC -shared -o "$OUT/$2" $objs "$d/driver.o" -Wl,--gc-sections -Wl,--version-script="$HERE/drivers/exports.map" -Wl,-z,defs -lm
 }
-build_nnom_example
+build_nnom_example keyword_spotting libref_nnom_example_local.so
+build_nnom_example mnist-simple libref_nnom_ex_mnist_simple.so
+build_nnom_example uci-inception libref_nnom_ex_uci_inception.so
 ls -la "$OUT"
