@@ -216,14 +216,13 @@ ED_HD void phase_c(int lane, int s, const MfccTables &T, const uint32_t *x, uint
     const int Sr = qsub16<SAT>(ar, cr), Si = qsub16<SAT>(ai, ci);
     const int Tr = qadd16<SAT>(br, dr), Ti = qadd16<SAT>(bi, di);
     const int Ur = qsub16<SAT>(br, dr), Ui = qsub16<SAT>(bi, di);
-    m0[v] = mag_q15((Rr + Tr) >> 1, (Ri + Ti) >> 1, T.sqrt_exc);
-    m2[v] = mag_q15((Sr + Ui) >> 1, (Si - Ur) >> 1, T.sqrt_exc);
+    mag_q15_x2((Rr + Tr) >> 1, (Ri + Ti) >> 1, (Sr + Ui) >> 1, (Si - Ur) >> 1, T.sqrt_exc, m0[v], m2[v]);
   }
   const int w = lane + 32 * s;
-  row[w] = (uint32_t)(m0[0] & 255) | ((uint32_t)(m0[1] & 255) << 8) | ((uint32_t)(m0[2] & 255) << 16) | ((uint32_t)m0[3] << 24);
-  row[w + 64] = (uint32_t)(m2[0] & 255) | ((uint32_t)(m2[1] & 255) << 8) | ((uint32_t)(m2[2] & 255) << 16) | ((uint32_t)m2[3] << 24);
-  row[kSpectPlaneWords + w] = (uint32_t)(m0[0] >> 8) | ((uint32_t)(m0[1] >> 8) << 8) | ((uint32_t)(m0[2] >> 8) << 16) | ((uint32_t)(m0[3] >> 8) << 24);
-  row[kSpectPlaneWords + w + 64] = (uint32_t)(m2[0] >> 8) | ((uint32_t)(m2[1] >> 8) << 8) | ((uint32_t)(m2[2] >> 8) << 16) | ((uint32_t)(m2[3] >> 8) << 24);
+  row[w] = pack4_plane<0>(m0[0], m0[1], m0[2], m0[3]);
+  row[w + 64] = pack4_plane<0>(m2[0], m2[1], m2[2], m2[3]);
+  row[kSpectPlaneWords + w] = pack4_plane<1>(m0[0], m0[1], m0[2], m0[3]);
+  row[kSpectPlaneWords + w + 64] = pack4_plane<1>(m2[0], m2[1], m2[2], m2[3]);
 }
 
 // ---- mel filterbank (audioprocessing.c:157-170) as a u8 x u8 tensor-core contraction ---------------

@@ -221,23 +221,6 @@ cudaError_t launch_debug_sqrt(const int32_t *d_in, size_t n, int32_t *d_out, cud
   return cudaGetLastError();
 }
 
-// mag_q15 takes (re, im); the sweep feeds it through a variant that takes s directly
-__device__ __forceinline__ int mag_from_sum(unsigned s, const uint32_t *exc_bits) {
-  unsigned h = s >> 1;
-  float y = ed_fmul(ed_sqrt_approx(ed_i2f((int)h)), 0.99999618530273437500f);
-  int g = ed_f2i_rz(y);
-  int d = (int)h - g * g;
-  int t = 2 * g + 1;
-  if (d >= t) { d -= t; g += 1; }
-  int dlo = 2 * d + (int)(s & 1u);
-  if (g < 8192) {
-    if (dlo == 0) g -= (int)((exc_bits[g >> 5] >> (g & 31)) & 1u);
-    return g;
-  }
-  int dhi = 4 * g + 2 - dlo;
-  if (dlo <= 13 || dhi <= 11) return (int)(int16_t)(sqrt_q31_newton((int)s) >> 16);
-  return g;
-}
 __global__ void debug_mag_sweep_kernel(uint32_t lo, uint32_t hi, const uint32_t *exc, unsigned long long *out2) {
   unsigned long long mism = 0, sum = 0;
   for (unsigned long long s = (unsigned long long)lo + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; s < hi;

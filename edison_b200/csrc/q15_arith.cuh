@@ -77,6 +77,19 @@ ED_HD uint32_t pack_hi(int X, int Y) {
 #endif
 }
 
+// byte plane k (0 = low bytes, 1 = high bytes) of four non-negative q15 values, a in the lowest byte: three PRMT
+template <int K> ED_HD uint32_t pack4_plane(int a, int b, int c, int d) {
+#if defined(__CUDA_ARCH__)
+  const uint32_t ab = __byte_perm((uint32_t)a, (uint32_t)b, K ? 0x0051 : 0x0040);
+  const uint32_t cd = __byte_perm((uint32_t)c, (uint32_t)d, K ? 0x0051 : 0x0040);
+  return __byte_perm(ab, cd, 0x5410);
+#else
+  const int sh = 8 * K;
+  return ((uint32_t)(a >> sh) & 255u) | (((uint32_t)(b >> sh) & 255u) << 8) | (((uint32_t)(c >> sh) & 255u) << 16) |
+         (((uint32_t)(d >> sh) & 255u) << 24);
+#endif
+}
+
 // One radix-4 DIF butterfly of a MIDDLE stage (arm_cfft_radix4_q15.c:333-479).
 // a, b, c, d are x[i0], x[i0+n2], x[i0+2n2], x[i0+3n2]; w1/w2/w3 = W^ic, W^2ic, W^3ic.
 template <bool SAT>
@@ -144,6 +157,7 @@ ED_HD void bfly_last(int &ar, int &ai, int &br, int &bi, int &cr, int &ci, int &
 // ------------------------------------------------------------------------------------------------
 #if defined(__CUDA_ARCH__)
 ED_HD float ed_i2f(int v) { return __int2float_rn(v); }
+ED_HD float ed_u2f(unsigned v) { return __uint2float_rn(v); }
 ED_HD float ed_fmul(float a, float b) { return __fmul_rn(a, b); }
 ED_HD int ed_f2i_rz(float v) { return __float2int_rz(v); }
 ED_HD int ed_f_as_i(float v) { return __float_as_int(v); }
@@ -156,6 +170,7 @@ ED_HD float ed_sqrt_approx(float v) { float r; asm("sqrt.approx.ftz.f32 %0, %1;"
 #include <string.h>
 namespace edison {
 ED_HD float ed_i2f(int v) { volatile float f = (float)v; return f; }
+ED_HD float ed_u2f(unsigned v) { volatile float f = (float)v; return f; }
 ED_HD float ed_fmul(float a, float b) { volatile float f = a * b; return f; }
 ED_HD int ed_f2i_rz(float v) { return (int)v; }
 ED_HD int ed_f_as_i(float v) { int i; memcpy(&i, &v, 4); return i; }
@@ -202,28 +217,55 @@ ED_HD_NOINLINE int sqrt_q31_newton(int in) {
 //     g <  8192 : only s == 2 g^2 exactly, and then the result is g - 1 for a fixed set of g
 //                 (a 8192-bit table, built at init from sqrt_q31_newton itself);
 //     g >= 8192 : only when s - 2 g^2 <= 13 or 2 (g+1)^2 - s <= 11; those take the Newton path.
-// So the common case costs one approximate square root and a one-sided integer correction.
+// So the common case costs one approximate square root and a one-sided integer correction, all on
+// dlo = s - 2 g^2 (which the exception tests need anyway):  g -> g + 1  <=>  dlo >= 4 g + 2.
 // ------------------------------------------------------------------------------------------------
 constexpr int kSqrtExcWords = 8192 / 32;
 
-ED_HD int mag_q15(int re, int im, const uint32_t *exc_bits) {
-  unsigned s = (unsigned)(re * re) + (unsigned)(im * im);
-  unsigned h = s >> 1;  // floor(sqrt(s/2)) == isqrt(s >> 1)
-  // y*(1 - 2^-18) is below sqrt(h) by more than the error of the approximation and by less
-  // than 1, so g0 is g or g - 1 and one upward correction settles it.
-  float y = ed_fmul(ed_sqrt_approx(ed_i2f((int)h)), 0.99999618530273437500f);
-  int g = ed_f2i_rz(y);
-  int d = (int)h - g * g;
-  int t = 2 * g + 1;
-  if (d >= t) { d -= t; g += 1; }
-  int dlo = 2 * d + (int)(s & 1u);  // s - 2 g^2
+// (1/sqrt 2)(1 - 2^-18) rounded to float.  y = sqrt.approx(float(s)) * kMagScale lies below sqrt(s/2) by a
+// relative 2^-18 -- more than the three roundings and the approximation's error (< 2^-22 together) and
+// less than 0.13 absolute (sqrt(s/2) <= 2^15) -- so trunc(y) is g or g - 1.
+#define ED_MAG_SCALE 0.70710408687591552734f
+
+// common case: g = floor(sqrt(s/2)), dlo = s - 2 g^2
+ED_HD void mag_fast(unsigned s, int &g, int &dlo) {
+  g = ed_f2i_rz(ed_fmul(ed_sqrt_approx(ed_u2f(s)), ED_MAG_SCALE));
+  dlo = (int)(s - (unsigned)(2 * g) * (unsigned)g);
+  const int t = 4 * g + 2;
+  if (dlo >= t) { dlo -= t; g += 1; }
+}
+// the arguments on which arm_sqrt_q31 may differ from g (rare unless the spectrum is near empty)
+ED_HD bool mag_is_rare(int g, int dlo) { return dlo == 0 || g >= 8192; }
+ED_HD int mag_fix(unsigned s, int g, int dlo, const uint32_t *exc_bits) {
   if (g < 8192) {
     if (dlo == 0) g -= (int)((exc_bits[g >> 5] >> (g & 31)) & 1u);
-    return g;
+  } else {
+    const int dhi = 4 * g + 2 - dlo;  // 2 (g+1)^2 - s
+    if (dlo <= 13 || dhi <= 11) g = (int)(int16_t)(sqrt_q31_newton((int)s) >> 16);
   }
-  int dhi = 4 * g + 2 - dlo;  // 2 (g+1)^2 - s
-  if (dlo <= 13 || dhi <= 11) return (int)(int16_t)(sqrt_q31_newton((int)s) >> 16);
   return g;
+}
+
+ED_HD int mag_from_sum(unsigned s, const uint32_t *exc_bits) {
+  int g, dlo;
+  mag_fast(s, g, dlo);
+  if (mag_is_rare(g, dlo)) g = mag_fix(s, g, dlo, exc_bits);
+  return g;
+}
+
+ED_HD int mag_q15(int re, int im, const uint32_t *exc_bits) {
+  return mag_from_sum((unsigned)(re * re) + (unsigned)(im * im), exc_bits);
+}
+// two bins at once: both common paths run side by side, one branch covers the two rare tests
+ED_HD void mag_q15_x2(int re0, int im0, int re1, int im1, const uint32_t *exc_bits, int &m0, int &m1) {
+  const unsigned s0 = (unsigned)(re0 * re0) + (unsigned)(im0 * im0), s1 = (unsigned)(re1 * re1) + (unsigned)(im1 * im1);
+  int d0, d1;
+  mag_fast(s0, m0, d0);
+  mag_fast(s1, m1, d1);
+  if (mag_is_rare(m0, d0) | mag_is_rare(m1, d1)) {
+    m0 = mag_fix(s0, m0, d0, exc_bits);
+    m1 = mag_fix(s1, m1, d1, exc_bits);
+  }
 }
 
 }  // namespace edison
