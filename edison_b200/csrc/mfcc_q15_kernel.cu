@@ -7,7 +7,7 @@
 // HBM traffic per frame: 2,048 B of PCM read once (coalesced 128 B per warp-load), 64 B of q15
 // coefficients and/or 13 B of int8 net input written.  Everything else stays in registers and
 // shared memory.  The kernel is integer-issue bound, so the grid is persistent:
-// one 16-warp CTA per SM.
+// one 20-warp CTA per SM.
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
@@ -91,6 +91,41 @@ __device__ __forceinline__ void mel_mma(int lane, int half, const MfccTables &T,
   }
 }
 
+// dct2_q15 + outputs for the 8 frames of group grp, whose mel spectra sit in W.mel
+__device__ __forceinline__ void group_tail(const MfccLaunch &P, const MfccTables &T, WarpSmem &W, int lane, long long grp,
+                                           long long n_frames) {
+  // dct2_q15 for the 8 frames of the group, 4 lanes per frame
+  I2 *z = reinterpret_cast<I2 *>(W.x);
+  int *out = reinterpret_cast<int *>(W.x) + 2 * kGroup * 16;
+  dct_stage1(lane, T, W.mel, z);
+  __syncwarp();
+  dct_stage2(lane, z);
+  __syncwarp();
+#pragma unroll
+  for (int it = 0; it < 4; it++) dct_split(32 * it + lane, T, z, out);
+  __syncwarp();
+  const long long f0 = grp * kGroup;
+  if (P.mfcc) {  // 8 frames x 64 B, one 16-byte store per lane
+    const int fr = lane >> 2, part = lane & 3;
+    if (f0 + fr < n_frames) {
+      const int *o = out + 32 * fr + 8 * part;
+      uint4 v;
+      v.x = (uint32_t)(o[0] & 0xffff) | ((uint32_t)o[1] << 16);
+      v.y = (uint32_t)(o[2] & 0xffff) | ((uint32_t)o[3] << 16);
+      v.z = (uint32_t)(o[4] & 0xffff) | ((uint32_t)o[5] << 16);
+      v.w = (uint32_t)(o[6] & 0xffff) | ((uint32_t)o[7] << 16);
+      *reinterpret_cast<uint4 *>(P.mfcc + (f0 + fr) * 32 + 8 * part) = v;
+    }
+  }
+  if (P.net_in) {  // 8 frames x 13 int8 (mfccToNetInput)
+    for (int idx = lane; idx < kGroup * kNCoeff; idx += 32) {
+      const int fr = idx / kNCoeff, c = idx - fr * kNCoeff;
+      if (f0 + fr < n_frames) P.net_in[(f0 + fr) * kNCoeff + c] = (int8_t)net_input_q7(out[32 * fr + c], T);
+    }
+  }
+  __syncwarp();
+}
+
 template <bool ALIGNED>
 __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -98,7 +133,7 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   {  // tables: global -> shared, once per CTA
     const int4 *src = reinterpret_cast<const int4 *>(P.tables);
     int4 *dst = reinterpret_cast<int4 *>(&S.T);
-    for (int i = threadIdx.x; i < (int)(sizeof(MfccTables) / 16); i += kThreads) dst[i] = src[i];
+    for (int i = threadIdx.x; i < (int)(sizeof(MfccTables) / 16); i += blockDim.x) dst[i] = src[i];
   }
   __syncthreads();
   const MfccTables &T = S.T;
@@ -106,50 +141,50 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   WarpSmem &W = S.w[warp];
   const long long n_frames = P.n_clips * P.frames_per_clip;
   const long long n_groups = (n_frames + kGroup - 1) / kGroup;
-  const long long warp_global = (long long)blockIdx.x * kWarpsPerCta + warp;
-  const long long warp_stride = (long long)gridDim.x * kWarpsPerCta;
+  const int warps_per_cta = blockDim.x >> 5;   // a multiple of 4, at most kWarpsPerCta (small launches run fewer warps)
+  const long long warp_global = (long long)blockIdx.x * warps_per_cta + warp;
+  const long long warp_stride = (long long)gridDim.x * warps_per_cta;
 
   uint32_t w[16];
+#pragma unroll
+  for (int q = 0; q < 16; q++) w[q] = 0;
   if (warp_global < n_groups) load_frame<ALIGNED>(P, warp_global * kGroup, lane, w);
-  // All warps of the CTA start every frame together (one bar.sync per frame): with the 16 warps inside the
-  // same ~20 KB of code at any time the instruction cache holds the working set (profiles/r01: +4 %).
-  // Every warp therefore runs the same trip count; trips past the end of its work only hit the barrier.
+  // Lockstep in groups of four warps, one warp per scheduler (named barrier 1 + warp/4, once per frame).  Warps that run
+  // the same code at the same time share their instruction fetches (free-running warps: 12.2 ms for bench.py's launch), but
+  // warps that share a SCHEDULER then also want the same pipe at the same time -- the FFT stages are ALU/IMAD throughput
+  // bound, the magnitude code latency bound -- and a CTA-wide barrier (11.9 ms) gives up that mixing; groups that drift
+  // against each other keep both (10.9 ms).  profiles/r01k.
+  // Every warp runs the same trip count and computes every frame of its trips, frames past the end from stale registers
+  // (no address depends on data; nothing of theirs is stored): the hot loop has no "valid" branches.
+  const int bar_id = 1 + (warp >> 2);
   const long long n_iter = (n_groups + warp_stride - 1) / warp_stride;
   for (long long it = 0, grp = warp_global; it < n_iter; it++, grp += warp_stride) {
 #pragma unroll 1
     for (int g = 0; g < kGroup; g++) {
       const long long f = grp * kGroup + g;
-      const bool valid = f < n_frames;  // ragged tail: unused rows are computed from stale data and never stored
-      bool sat = false;
       uint32_t *row = W.spect + (g & (kSub - 1)) * kSpectRowWords;
-      __syncthreads();
-      if (valid) {
-        sat = __reduce_max_sync(0xffffffffu, lane_peak(w)) > kNoSatPeak;
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id));
+      const bool sat = __reduce_max_sync(0xffffffffu, lane_peak(w)) > kNoSatPeak;
 #pragma unroll 1
-        for (int e = 0; e < 2; e++) phase_a(lane, e, w, T, W.x);
-        // prefetch the next frame this warp will process; it lands while phases B, C and mel run
-        const long long fn = g + 1 < kGroup ? f + 1 : (grp + warp_stride) * kGroup;
-        if (fn < n_frames) load_frame<ALIGNED>(P, fn, lane, w);
+      for (int e = 0; e < 2; e++) phase_a(lane, e, w, T, W.x);
+      // prefetch the next frame this warp will process; it lands while phases B, C and mel run
+      const long long fn = g + 1 < kGroup ? f + 1 : (grp + warp_stride) * kGroup;
+      if (fn < n_frames) load_frame<ALIGNED>(P, fn, lane, w);
+      __syncwarp();
+      if (sat) {
+#pragma unroll 1
+        for (int e = 0; e < 2; e++) phase_b<true>(lane, e, T, W.x);
+      } else {
+#pragma unroll 1
+        for (int e = 0; e < 2; e++) phase_b<false>(lane, e, T, W.x);
       }
       __syncwarp();
-      if (valid) {
-        if (sat) {
+      if (sat) {
 #pragma unroll 1
-          for (int e = 0; e < 2; e++) phase_b<true>(lane, e, T, W.x);
-        } else {
+        for (int s = 0; s < 2; s++) phase_c<true>(lane, s, T, W.x, row);
+      } else {
 #pragma unroll 1
-          for (int e = 0; e < 2; e++) phase_b<false>(lane, e, T, W.x);
-        }
-      }
-      __syncwarp();
-      if (valid) {
-        if (sat) {
-#pragma unroll 1
-          for (int s = 0; s < 2; s++) phase_c<true>(lane, s, T, W.x, row);
-        } else {
-#pragma unroll 1
-          for (int s = 0; s < 2; s++) phase_c<false>(lane, s, T, W.x, row);
-        }
+        for (int s = 0; s < 2; s++) phase_c<false>(lane, s, T, W.x, row);
       }
       __syncwarp();
       if ((g & (kSub - 1)) == kSub - 1) {
@@ -157,36 +192,7 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
         __syncwarp();
       }
     }
-    // dct2_q15 for the 8 frames of the group, 4 lanes per frame
-    I2 *z = reinterpret_cast<I2 *>(W.x);
-    int *out = reinterpret_cast<int *>(W.x) + 2 * kGroup * 16;
-    dct_stage1(lane, T, W.mel, z);
-    __syncwarp();
-    dct_stage2(lane, z);
-    __syncwarp();
-#pragma unroll
-    for (int it = 0; it < 4; it++) dct_split(32 * it + lane, T, z, out);
-    __syncwarp();
-    const long long f0 = grp * kGroup;
-    if (P.mfcc) {  // 8 frames x 64 B, one 16-byte store per lane
-      const int fr = lane >> 2, part = lane & 3;
-      if (f0 + fr < n_frames) {
-        const int *o = out + 32 * fr + 8 * part;
-        uint4 v;
-        v.x = (uint32_t)(o[0] & 0xffff) | ((uint32_t)o[1] << 16);
-        v.y = (uint32_t)(o[2] & 0xffff) | ((uint32_t)o[3] << 16);
-        v.z = (uint32_t)(o[4] & 0xffff) | ((uint32_t)o[5] << 16);
-        v.w = (uint32_t)(o[6] & 0xffff) | ((uint32_t)o[7] << 16);
-        *reinterpret_cast<uint4 *>(P.mfcc + (f0 + fr) * 32 + 8 * part) = v;
-      }
-    }
-    if (P.net_in) {  // 8 frames x 13 int8 (mfccToNetInput)
-      for (int idx = lane; idx < kGroup * kNCoeff; idx += 32) {
-        const int fr = idx / kNCoeff, c = idx - fr * kNCoeff;
-        if (f0 + fr < n_frames) P.net_in[(f0 + fr) * kNCoeff + c] = (int8_t)net_input_q7(out[32 * fr + c], T);
-      }
-    }
-    __syncwarp();
+    group_tail(P, T, W, lane, grp, n_frames);
   }
 }
 
@@ -202,9 +208,13 @@ cudaError_t launch_mfcc_q15(const MfccLaunch &p, int sm_count, cudaStream_t stre
   const long long n_groups = (n_frames + kGroup - 1) / kGroup;
   long long ctas = (n_groups + kWarpsPerCta - 1) / kWarpsPerCta;
   if (ctas > sm_count) ctas = sm_count;
+  // warps per CTA: whole barrier groups of four, no more than the work needs
+  long long warps = (n_groups + ctas - 1) / ctas;
+  warps = warps >= kWarpsPerCta ? kWarpsPerCta : (warps + 3) / 4 * 4;
+  const unsigned threads = (unsigned)warps * 32;
   const bool aligned = (reinterpret_cast<uintptr_t>(p.pcm) & 3u) == 0 && (p.clip_stride & 1) == 0;
-  if (aligned) mfcc_q15_kernel<true><<<(unsigned)ctas, kThreads, sizeof(CtaSmem), stream>>>(p);
-  else mfcc_q15_kernel<false><<<(unsigned)ctas, kThreads, sizeof(CtaSmem), stream>>>(p);
+  if (aligned) mfcc_q15_kernel<true><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
+  else mfcc_q15_kernel<false><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
   count_launch();
   return cudaGetLastError();
 }
