@@ -30,10 +30,10 @@ CLIP = 31 * 1024
 K1_BYTES_PER_FRAME = 2048 + 13  # algorithmic: PCM read + int8 net-input row written
 N_STREAMS = 100000              # config #5
 # dram__bytes_read.sum + dram__bytes_write.sum of one mfcc_q15_kernel launch over 131,072 x 31 frames, from the ncu
-# --set full capture summarised in profiles/ (8.32 GB read + 10 MB written): no re-reads.
-K1_NCU_DRAM_BYTES = 8.33e9
+# --set full capture summarised in profiles/r01k_k1_group_lockstep.txt (8.322 GB read + 9.7 MB written): no re-reads.
+K1_NCU_DRAM_BYTES = 8.332e9
 # smsp__inst_executed.sum / frames of the same capture: what actually bounds K1 (integer issue, SURVEY F9 / DESIGN.md section 3)
-K1_WARP_INST_PER_FRAME = 2549
+K1_WARP_INST_PER_FRAME = 2435
 
 
 def peaks():
