@@ -36,6 +36,38 @@ K1_NCU_DRAM_BYTES = 8.332e9
 K1_WARP_INST_PER_FRAME = 2435
 
 
+def bind_to_gpu_numa(index):
+    """Pin this process to the CPUs NVML reports as local to GPU `index`, so that pinned host buffers (first touch) and the
+    copy-issuing thread sit on the GPU's own NUMA node.  Returns the number of CPUs bound to, or None when unavailable."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:   # CUDA's device order need not be NVML's: go through the PCI address
+            import torch
+            pr = torch.cuda.get_device_properties(index)
+            h = pynvml.nvmlDeviceGetHandleByPciBusId(("%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)).encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (wd >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
+def peaks_bf16():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["bf16_tflops"]), "measured"
+    except Exception:
+        return 2250.0, "nominal"
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
@@ -154,6 +186,7 @@ def run_ours(args, rank, world, local_rank):
     from edison_b200 import shard
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = bind_to_gpu_numa(local_rank)   # before any pinned allocation: the e2e leg streams host memory over PCIe
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -349,7 +382,7 @@ def run_ours(args, rank, world, local_rank):
                 "vs_baseline": None, "dtype": "q15/int8", "data": "synthetic",
                 "config": {"workload": "config#3 shard: %d clips x 31 frames x 1024 int16 per GPU, q15 MFCC + int8 NNoM net" % n,
                            "clip_samples": CLIP, "global_clips": world * n, "l2": "inputs (8.3 GB/GPU) larger than L2",
-                           "parallelism": "clip shards, dp%d" % world, "peak": peak_kind},
+                           "parallelism": "clip shards, dp%d" % world, "peak": peak_kind, "numa_bound_cpus": numa},
                 "mfcc_frames_per_s": world * n * 31 / (k1_ms / 1e3), "audio_seconds_per_s": value * 31 * 0.064,
                 # BASELINE.json words the metric in "1 s 16 kHz" clips; the net's own window is 31 frames = 1.984 s
                 "one_second_equiv_clips_per_s": value * 31 / 15.625,
@@ -369,6 +402,12 @@ def run_ours(args, rank, world, local_rank):
                 "gpu_launches": int(launches), "clocks": clocks}
         if stream_stats:
             line["streaming"] = stream_stats
+        # the CNN's own roofline (BASELINE.json: "% tensor peak"): 784,752 MAC = 1,569,504 int8 ops per clip;
+        # the dense int8 tensor rate is taken as 2 x the measured bf16 rate of MEASURED_PEAKS.json (nominal 4.5 vs 2.25 PFLOP/s)
+        bf16 = peaks_bf16()
+        k2_tops = n * 1569504 / (k2_ms / 1e3) / 1e12
+        line["cnn_roofline"] = {"kernel": "nnom_q7_kernel", "bound": "tensor", "achieved": k2_tops, "peak": 2 * bf16[0], "unit": "TOP/s (int8)",
+                                "frac": k2_tops / (2 * bf16[0]), "peak_kind": "2 x bf16 " + bf16[1], "share_of_step": k2_ms / ms_per_step}
         line["cfg4_float_cnn"] = cfg4
         line["float_mfcc"] = dict(float_stats, workload="mfcc_utils.mfcc arithmetic on 65,536 x 1 s clips (15 frames each), 1 GPU")
         if world == 1 and not args.no_cpu:
@@ -382,6 +421,14 @@ def run_ours(args, rank, world, local_rank):
             res2 = cpu_baseline.run(clips_per_proc=64, procs=os.cpu_count() or 1, reps=1, which="port")
             line["cpu_baseline_port"] = {"value": res2["clips_per_s"], "unit": "clips/s", "cores": res2["cores"], "kind": "port",
                                          "sample": res2["sample"]}
+            # config #1's CPU side: the numpy restatement of mfcc_utils.mfcc (pinned to the reference module's own outputs) on one core
+            import mfcc_float as mf
+            rng = __import__("numpy").random.default_rng(20)
+            xs = rng.integers(-8000, 8000, size=20000 * 1024, dtype="int16")
+            t0 = time.perf_counter()
+            mf.mfcc_host(xs)
+            dt = time.perf_counter() - t0
+            line["float_mfcc"]["cpu_numpy"] = {"frames_per_s": 20000 / dt, "cores": 1, "kind": "port", "sample": "20,000 frames, oracle/mfcc_float.py::mfcc_host (vectorised numpy; the reference loops frame by frame)"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
