@@ -220,8 +220,12 @@ __device__ __forceinline__ void conv1_mma(const int8_t *in, int8_t *out, const u
 #pragma unroll
       for (int h = 0; h < 2; h++) {
         const int ky = 4 * ks + 2 * h + (t >> 1), kx0 = 4 * (t & 1);
-        a[2 * h] = ld_unaligned32(inw, base + ky * kInW + kx0);
-        a[2 * h + 1] = ld_unaligned32(inw, base + (ky + 1) * kInW + kx0);
+        if (4 * ks + 2 * h >= 5) {   // kernel rows 6, 7 (and 5, fetched beside row 4) have zero weights: nothing to fetch
+          a[2 * h] = a[2 * h + 1] = 0;
+        } else {
+          a[2 * h] = ld_unaligned32(inw, base + ky * kInW + kx0);
+          a[2 * h + 1] = ld_unaligned32(inw, base + (ky + 1) * kInW + kx0);
+        }
       }
       mma_s8(acc[0], a, frag[(ks * 2 + 0) * 32 + lane]);
       mma_s8(acc[1], a, frag[(ks * 2 + 1) * 32 + lane]);
@@ -370,6 +374,10 @@ __device__ __forceinline__ void conv1_row_mma(const int8_t *in, int8_t *out, con
 #pragma unroll
       for (int h = 0; h < 2; h++) {
         const int ky = 4 * ks + 2 * h + (t >> 1), kx0 = 4 * (t & 1);
+        if (4 * ks + 2 * h >= 5) {   // zero-weight kernel rows
+          a[2 * h] = a[2 * h + 1] = 0;
+          continue;
+        }
         a[2 * h] = ld_unaligned32(inw, base_a + ky * kInW + kx0);
         a[2 * h + 1] = ld_unaligned32(inw, base_b + ky * kInW + kx0);
       }
