@@ -31,6 +31,17 @@ def test_mfcc_q15_vs_oracle(edison, oracle, n):
     assert bad.size == 0, "frames %s differ, first: got %s want %s" % (bad[:8], got[bad[0]], want[bad[0]])
 
 
+def test_mfcc_q15_launch_geometries(edison, oracle):
+    """K1 starts whole 4-warp barrier groups, no more than the work needs, and warps without work compute on stale registers:
+    every warp count (groups of 8 frames: 1..21 groups in one CTA, then two CTAs) and ragged last groups must stay exact
+    and must not hang on a barrier."""
+    pcm = common.synth_frames(8 * 45 + 5, seed=77)
+    want = oracle.mfcc(pcm)
+    for n in list(range(1, 34)) + [8 * k + r for k in (4, 8, 12, 16, 19, 20, 21, 40, 44) for r in (0, 1, 7)] + [pcm.shape[0]]:
+        got = edison.mfcc_q15_batch(pcm[:n])
+        assert (got == want[:n]).all(), n
+
+
 def test_mfcc_empty(edison):
     assert edison.mfcc_q15_batch(np.zeros((0, 1024), np.int16)).shape == (0, 32)
 
