@@ -56,7 +56,8 @@ struct alignas(16) FloatTables {
   int frame_len;               // samples read per frame (<= 1024); the rest of the 1024-point transform is zero padding
   int bin_step;                // 1024 / padded frame length: bin i of the reference's FFT is bin i * bin_step here
   int q7_count;                // mfcc.c mode: number of coefficients written (num - offset)
-  int pad_[3];
+  int mel_count_max;           // host modes: largest (padded) filter length
+  int pad_[2];
 };
 
 template <typename R>
@@ -116,6 +117,17 @@ __device__ __forceinline__ void load4(const double *p, double (&o)[4]) {
 }
 __device__ __forceinline__ float log_r(float x) { return logf(x); }
 __device__ __forceinline__ double log_r(double x) { return log(x); }
+
+// W32^j = exp(-2 pi i j / 32), j = 0..7
+__device__ constexpr double kW32[8][2] = {
+    {1.0, -0.0},
+    {0.98078528040323044913, -0.19509032201612826785},
+    {0.92387953251128675613, -0.38268343236508977173},
+    {0.83146961230254523708, -0.55557023301960222474},
+    {0.70710678118654752440, -0.70710678118654752440},
+    {0.55557023301960222474, -0.83146961230254523708},
+    {0.38268343236508977173, -0.92387953251128675613},
+    {0.19509032201612826785, -0.98078528040323044913}};
 
 // 8-point DFT, decimation in frequency, natural order out: v[r] = sum_n v[n] W8^{n r}
 template <typename R>
@@ -234,8 +246,13 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
       for (int i = 0; i < 8; i++) t[i] = v[2 * i + h];
       radix8(t);
       W.xch[lane + 32 * h] = t[0];
+      // the kernel is bound by shared-memory wavefronts, not by the FMA pipe: W^1, W^2, W^4 are read, the other four
+      // twiddles are products of those (two roundings more at most)
+      C tw[8];
+      tw[1] = T.tw1[0][h][lane]; tw[2] = T.tw1[1][h][lane]; tw[4] = T.tw1[3][h][lane];
+      tw[3] = cmul(tw[1], tw[2]); tw[5] = cmul(tw[4], tw[1]); tw[6] = cmul(tw[4], tw[2]); tw[7] = cmul(tw[4], tw[3]);
 #pragma unroll
-      for (int r = 1; r < 8; r++) W.xch[kXchStride * r + lane + 32 * h] = cmul(t[r], T.tw1[r - 1][h][lane]);
+      for (int r = 1; r < 8; r++) W.xch[kXchStride * r + lane + 32 * h] = cmul(t[r], tw[r]);
     }
     __syncwarp();
     // ---- pass 2: over m1; this lane takes m0 = lane & 7 and r = (lane >> 3) + 4h
@@ -245,6 +262,9 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
 #pragma unroll
       for (int i = 0; i < 8; i++) v[8 * h + i] = W.xch[kXchStride * (hi2 + 4 * h) + 8 * i + lo3];
     __syncwarp();
+    C tw2[8];
+    tw2[1] = T.tw2[0][lo3]; tw2[2] = T.tw2[1][lo3]; tw2[4] = T.tw2[3][lo3];
+    tw2[3] = cmul(tw2[1], tw2[2]); tw2[5] = cmul(tw2[4], tw2[1]); tw2[6] = cmul(tw2[4], tw2[2]); tw2[7] = cmul(tw2[4], tw2[3]);
 #pragma unroll
     for (int h = 0; h < 2; h++) {
       C t[8];
@@ -255,7 +275,7 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
       const int col = 8 * r + (lo3 ^ r);
       W.xch[col] = t[0];
 #pragma unroll
-      for (int rp = 1; rp < 8; rp++) W.xch[kXchStride * rp + col] = cmul(t[rp], T.tw2[rp - 1][lo3]);
+      for (int rp = 1; rp < 8; rp++) W.xch[kXchStride * rp + col] = cmul(t[rp], tw2[rp]);
     }
     __syncwarp();
     // ---- pass 3: over m0; this lane takes r = lane & 7 and r' = (lane >> 3) + 4h; outputs k = 64 q + lane + 32 h
@@ -276,11 +296,13 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
     }
     __syncwarp();
     // ---- real-input split on pairs (k, 512 - k), k = lane + 32 j; magnitudes are 2|X| (the 1/2 lives in mel_w)
+    const C ws0 = T.tws[0][lane];
 #pragma unroll
     for (int j = 0; j < 8; j++) {
       const int k = lane + 32 * j;
       const C a = W.xch[k], bc = W.xch[512 - k];
-      const C w = T.tws[j][lane];
+      // W1024^{lane + 32 j} = W1024^{lane} * W32^{j}: one read per frame, the eight W32 powers are constants
+      const C w = j ? cmul(ws0, C{(R)kW32[j][0], (R)kW32[j][1]}) : ws0;
       const R er = a.x + bc.x, ei = a.y - bc.y;        // A + conj(Z[512-k])
       const R dr = a.x - bc.x, di = a.y + bc.y;        // A - conj(Z[512-k])
       const R tr = w.x * di + w.y * dr, ti = w.y * di - w.x * dr;   // W^k * (-j D)
@@ -295,30 +317,56 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
     __syncwarp();
     // ---- mel: 4 lanes per filter, 8 filters per round.  Each lane takes aligned chunks of 4 bins (128-bit reads of the
     //      magnitudes and of the zero-padded weights); the mfcc.c mode strides through the bins and stays scalar.
-    {
+    //      (8 lanes per filter would make every quarter-warp read 128 contiguous bytes -- no bank conflicts, 92 instead of 143
+    //      wavefronts per frame -- but doubles the rounds, each a dependent load-FMA-shuffle chain: measured 22 % slower.)
+    if (CMODE) {
       const int q = lane & 3;
 #pragma unroll
       for (int round = 0; round < 4; round++) {
         const int m = 8 * round + (lane >> 2);
         const int cnt = T.mel_count[m];
         const R *wt = T.mel_w + T.mel_off[m];
+        const int bs = T.bin_step;
+        const R *mg = W.mag + T.mel_start[m] * bs;
         R acc = (R)0;
-        if (CMODE) {
-          const int bs = T.bin_step;
-          const R *mg = W.mag + T.mel_start[m] * bs;
-          for (int i = q; i < cnt; i += 4) acc = fma(mg[i * bs], wt[i], acc);
-        } else {
-          const R *mg = W.mag + T.mel_start[m];
-          for (int i = 4 * q; i < cnt; i += 16) {
-            R a[4], w[4];
-            load4(mg + i, a);
-            load4(wt + i, w);
-            acc = fma(a[0], w[0], acc); acc = fma(a[1], w[1], acc); acc = fma(a[2], w[2], acc); acc = fma(a[3], w[3], acc);
-          }
-        }
+        for (int i = q; i < cnt; i += 4) acc = fma(mg[i * bs], wt[i], acc);
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
         if (q == 0) W.mel[m] = acc;
+      }
+    } else {
+      // the four rounds advance together, so that eight independent 128-bit loads are in flight per step (one round at a
+      // time is a chain of dependent load-FMA steps, and this part of the kernel waits on shared-memory latency)
+      const int q = lane & 3;
+      int cnt[4];
+      const R *wt[4], *mg[4];
+      R acc[4];
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        const int m = 8 * r + (lane >> 2);
+        cnt[r] = T.mel_count[m];
+        wt[r] = T.mel_w + T.mel_off[m];
+        mg[r] = W.mag + T.mel_start[m];
+        acc[r] = (R)0;
+      }
+      const int cmax = T.mel_count_max;
+      for (int i = 4 * q; i < cmax; i += 16) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+          if (i < cnt[r]) {
+            R a[4], w[4];
+            load4(mg[r] + i, a);
+            load4(wt[r] + i, w);
+            acc[r] = fma(a[0], w[0], acc[r]); acc[r] = fma(a[1], w[1], acc[r]);
+            acc[r] = fma(a[2], w[2], acc[r]); acc[r] = fma(a[3], w[3], acc[r]);
+          }
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        acc[r] += __shfl_xor_sync(0xffffffffu, acc[r], 1);
+        acc[r] += __shfl_xor_sync(0xffffffffu, acc[r], 2);
+        if (q == 0) W.mel[8 * r + (lane >> 2)] = acc[r];
       }
     }
     __syncwarp();
@@ -330,9 +378,15 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
     }
     __syncwarp();
     {
-      R acc = (R)0;
-#pragma unroll 8
-      for (int n = 0; n < 32; n++) acc = fma(W.lm[n], T.dct_t[n][lane], acc);
+      R a4[4] = {(R)0, (R)0, (R)0, (R)0};   // four chains instead of one of 32 dependent FMAs
+#pragma unroll
+      for (int n = 0; n < 32; n += 4) {
+        R l[4];
+        load4(W.lm + n, l);
+#pragma unroll
+        for (int u = 0; u < 4; u++) a4[u] = fma(l[u], T.dct_t[n + u][lane], a4[u]);
+      }
+      const R acc = (a4[0] + a4[1]) + (a4[2] + a4[3]);
       if (CMODE) {
         // mfcc.c:240-250: sum * 2^dec_bits, round() (half away from zero), saturate to q7
         if (lane < T.q7_count) {
@@ -403,6 +457,7 @@ static int fill_tables(FloatTables<R> &T, int mode) {
     const int a_count = ((start + count - a_start) + 3) & ~3;
     if (off + a_count > kMelWMax || a_start + a_count > kMagLen) return -1;
     T.mel_start[m] = a_start; T.mel_count[m] = a_count; T.mel_off[m] = off;
+    if (a_count > T.mel_count_max) T.mel_count_max = a_count;
     for (int i = 0; i < count; i++) T.mel_w[off + (start - a_start) + i] = (R)(w[i] * spec_scale * 0.5);
     off += a_count;
   }
