@@ -196,45 +196,63 @@ __device__ __forceinline__ uint32_t ld_unaligned32(const uint32_t *words, int by
   return __funnelshift_r(words[wa], words[wa + 1], (byte_addr & 3) * 8);
 }
 
-__device__ __forceinline__ void conv1_mma(const int8_t *in, int8_t *out, const uint2 *frag, const int *seed, int rs,
-                                          int nclips) {
+// Two tiles per trip: the twelve input fetches of both are issued before the first MMA (one tile at a time is a chain
+// fetch -> funnel shift -> MMA -> epilogue with nothing to overlap, and the CTA has only 8 warps).
+__device__ __forceinline__ void conv1_mma(const int8_t *__restrict__ in, int8_t *__restrict__ out, const uint2 *__restrict__ frag,
+                                          const int *__restrict__ seed, int rs, int nclips) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
   const int rows_total = nclips * kPix1;   // pooled pixels
   const int n_tiles = (rows_total + 7) / 8;
-  const uint32_t *inw = reinterpret_cast<const uint32_t *>(in);
-  for (int tile = warp; tile < n_tiles; tile += kNetWarps) {
-    const int q0 = tile * 8 + g;
-    const bool v0 = q0 < rows_total;
-    const int qa = v0 ? q0 : 0;
-    const int ca = qa / kPix1, ra = qa - ca * kPix1, yp = ra / 9, x = ra - yp * 9;
-    const int base = ca * kInStride + (2 * yp) * kInW + x;   // byte address of in[2 yp][x]; row g + 8 is one row down
-    int acc[2][4];
+  const uint32_t *__restrict__ inw = reinterpret_cast<const uint32_t *>(in);
+  uint2 fr[4];
 #pragma unroll
-    for (int n = 0; n < 2; n++) {
-      acc[n][0] = acc[n][2] = seed[8 * n + 2 * t];
-      acc[n][1] = acc[n][3] = seed[8 * n + 2 * t + 1];
+  for (int i = 0; i < 4; i++) fr[i] = frag[i * 32 + lane];
+  const int sd[4] = {seed[2 * t], seed[2 * t + 1], seed[8 + 2 * t], seed[8 + 2 * t + 1]};
+  for (int tile = warp; tile < n_tiles; tile += 2 * kNetWarps) {
+    int q0[2], base[2];
+    bool v0[2];
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+      q0[u] = (tile + u * kNetWarps) * 8 + g;
+      v0[u] = q0[u] < rows_total;
+      const int qa = v0[u] ? q0[u] : 0;
+      const int ca = qa / kPix1, ra = qa - ca * kPix1, yp = ra / 9, x = ra - yp * 9;
+      base[u] = ca * kInStride + (2 * yp) * kInW + x;   // byte address of in[2 yp][x]; row g + 8 is one row down
     }
+    uint32_t a[2][2][4];
 #pragma unroll
-    for (int ks = 0; ks < 2; ks++) {
-      uint32_t a[4];
+    for (int u = 0; u < 2; u++)
 #pragma unroll
-      for (int h = 0; h < 2; h++) {
-        const int ky = 4 * ks + 2 * h + (t >> 1), kx0 = 4 * (t & 1);
-        if (4 * ks + 2 * h >= 5) {   // kernel rows 6, 7 (and 5, fetched beside row 4) have zero weights: nothing to fetch
-          a[2 * h] = a[2 * h + 1] = 0;
-        } else {
-          a[2 * h] = ld_unaligned32(inw, base + ky * kInW + kx0);
-          a[2 * h + 1] = ld_unaligned32(inw, base + (ky + 1) * kInW + kx0);
+      for (int ks = 0; ks < 2; ks++)
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int ky = 4 * ks + 2 * h + (t >> 1), kx0 = 4 * (t & 1);
+          if (4 * ks + 2 * h >= 5) {   // kernel rows 6, 7 (and 5, fetched beside row 4) have zero weights: nothing to fetch
+            a[u][ks][2 * h] = a[u][ks][2 * h + 1] = 0;
+          } else {
+            a[u][ks][2 * h] = ld_unaligned32(inw, base[u] + ky * kInW + kx0);
+            a[u][ks][2 * h + 1] = ld_unaligned32(inw, base[u] + (ky + 1) * kInW + kx0);
+          }
         }
-      }
-      mma_s8(acc[0], a, frag[(ks * 2 + 0) * 32 + lane]);
-      mma_s8(acc[1], a, frag[(ks * 2 + 1) * 32 + lane]);
-    }
-    if (v0) {
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+      int acc[2][4];
 #pragma unroll
       for (int n = 0; n < 2; n++) {
-        const int lo = q7_relu(max(acc[n][0], acc[n][2]), rs), hi = q7_relu(max(acc[n][1], acc[n][3]), rs);
-        reinterpret_cast<uint16_t *>(out)[(q0 * kC1 + 8 * n + 2 * t) >> 1] = (uint16_t)(lo | (hi << 8));
+        acc[n][0] = acc[n][2] = sd[2 * n];
+        acc[n][1] = acc[n][3] = sd[2 * n + 1];
+      }
+#pragma unroll
+      for (int ks = 0; ks < 2; ks++) {
+        mma_s8(acc[0], a[u][ks], fr[ks * 2 + 0]);
+        mma_s8(acc[1], a[u][ks], fr[ks * 2 + 1]);
+      }
+      if (v0[u]) {
+#pragma unroll
+        for (int n = 0; n < 2; n++) {
+          const int lo = q7_relu(max(acc[n][0], acc[n][2]), rs), hi = q7_relu(max(acc[n][1], acc[n][3]), rs);
+          reinterpret_cast<uint16_t *>(out)[(q0[u] * kC1 + 8 * n + 2 * t) >> 1] = (uint16_t)(lo | (hi << 8));
+        }
       }
     }
   }
