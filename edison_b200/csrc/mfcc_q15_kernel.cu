@@ -142,7 +142,9 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   const long long n_frames = P.n_clips * P.frames_per_clip;
   const long long n_groups = (n_frames + kGroup - 1) / kGroup;
   const int warps_per_cta = blockDim.x >> 5;   // a multiple of 4, at most kWarpsPerCta (small launches run fewer warps)
-  const long long warp_global = (long long)blockIdx.x * warps_per_cta + warp;
+  // work is dealt to barrier groups (4 warps) CTA-minor: the last, partial trip then leaves a group or two busy on EVERY SM
+  // instead of filling the first few SMs completely (a 100,000-frame hop of the streaming path is 4.2 trips)
+  const long long warp_global = ((long long)(warp >> 2) * gridDim.x + blockIdx.x) * 4 + (warp & 3);
   const long long warp_stride = (long long)gridDim.x * warps_per_cta;
 
   uint32_t w[16];
@@ -154,11 +156,12 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   // warps that share a SCHEDULER then also want the same pipe at the same time -- the FFT stages are ALU/IMAD throughput
   // bound, the magnitude code latency bound -- and a CTA-wide barrier (11.9 ms) gives up that mixing; groups that drift
   // against each other keep both (10.9 ms).  profiles/r01k.
-  // Every warp runs the same trip count and computes every frame of its trips, frames past the end from stale registers
-  // (no address depends on data; nothing of theirs is stored): the hot loop has no "valid" branches.
+  // The four warps of a group run the same trip count and compute every frame of their trips, frames past the end from
+  // stale registers (no address depends on data; nothing of theirs is stored): the hot loop has no "valid" branches.
   const int bar_id = 1 + (warp >> 2);   // groups of 8, 10, 12 warps measured 11.0, 11.3, 11.35 ms
   const long long n_iter = (n_groups + warp_stride - 1) / warp_stride;
   for (long long it = 0, grp = warp_global; it < n_iter; it++, grp += warp_stride) {
+    if (grp - (warp & 3) >= n_groups) break;   // none of the four warps of this barrier group has work left: all four leave
 #pragma unroll 1
     for (int g = 0; g < kGroup; g++) {
       const long long f = grp * kGroup + g;
