@@ -379,12 +379,26 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
     __syncwarp();
     {
       R a4[4] = {(R)0, (R)0, (R)0, (R)0};   // four chains instead of one of 32 dependent FMAs
+      if (CMODE) {
 #pragma unroll
-      for (int n = 0; n < 32; n += 4) {
-        R l[4];
-        load4(W.lm + n, l);
+        for (int n = 0; n < 32; n += 4) {
+          R l[4];
+          load4(W.lm + n, l);
 #pragma unroll
-        for (int u = 0; u < 4; u++) a4[u] = fma(l[u], T.dct_t[n + u][lane], a4[u]);
+          for (int u = 0; u < 4; u++) a4[u] = fma(l[u], T.dct_t[n + u][lane], a4[u]);
+        }
+      } else {
+        // DCT-II over 32 points: row 31 - n of the matrix is (-1)^k times row n, so half of the table is read and the
+        // inputs are folded first, lm[n] + lm[31 - n] for even k (= lane), lm[n] - lm[31 - n] for odd k
+        const R sgn = (lane & 1) ? (R)-1 : (R)1;
+#pragma unroll
+        for (int n = 0; n < 16; n += 4) {
+          R l[4], h[4];
+          load4(W.lm + n, l);
+          load4(W.lm + 28 - n, h);
+#pragma unroll
+          for (int u = 0; u < 4; u++) a4[u] = fma(fma(sgn, h[3 - u], l[u]), T.dct_t[n + u][lane], a4[u]);
+        }
       }
       const R acc = (a4[0] + a4[1]) + (a4[2] + a4[3]);
       if (CMODE) {
