@@ -115,6 +115,13 @@ __device__ __forceinline__ void load4(const double *p, double (&o)[4]) {
   const double2 a = *reinterpret_cast<const double2 *>(p), b = *reinterpret_cast<const double2 *>(p + 2);
   o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
 }
+// the two halves of a 4-element chunk in the order (sw, 2 - sw), sw = 0 or 2; element order is the same for every array
+// loaded this way, which is all a dot product needs
+__device__ __forceinline__ void load4_swapped(const double *p, int sw, double (&o)[4]) {
+  const double2 a = *reinterpret_cast<const double2 *>(p + sw), b = *reinterpret_cast<const double2 *>(p + 2 - sw);
+  o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+}
+__device__ __forceinline__ void load4_swapped(const float *p, int, float (&o)[4]) { load4(p, o); }
 __device__ __forceinline__ float log_r(float x) { return logf(x); }
 __device__ __forceinline__ double log_r(double x) { return log(x); }
 
@@ -349,14 +356,20 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
         mg[r] = W.mag + T.mel_start[m];
         acc[r] = (R)0;
       }
+      // Bank conflicts: a quarter-warp (one wavefront of a 128-bit load) holds two filters with unrelated start bins.
+      // double: a 4-bin chunk is two 16-byte loads, and the odd filter of the pair issues them in the other order, so the
+      // eight lanes always read eight different 16-byte bank groups (fp64 +8 %).  float: a chunk is one load; taking every
+      // second chunk with opposite parities in the two filters is conflict-free too, but splits short filters over two
+      // steps and measured 8 % slower -- the float kernel keeps the contiguous order and its conflicts.
       const int cmax = T.mel_count_max;
+      const int sw = 2 * ((lane >> 2) & 1);
       for (int i = 4 * q; i < cmax; i += 16) {
 #pragma unroll
         for (int r = 0; r < 4; r++) {
           if (i < cnt[r]) {
             R a[4], w[4];
-            load4(mg[r] + i, a);
-            load4(wt[r] + i, w);
+            load4_swapped(mg[r] + i, sw, a);
+            load4_swapped(wt[r] + i, sw, w);
             acc[r] = fma(a[0], w[0], acc[r]); acc[r] = fma(a[1], w[1], acc[r]);
             acc[r] = fma(a[2], w[2], acc[r]); acc[r] = fma(a[3], w[3], acc[r]);
           }
