@@ -317,6 +317,18 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = t.item()
     e2e_val = world * ne / e2e_s
+    # what bounds this leg: the pinned host -> device copy rate of this box, measured on the same buffer right here
+    hb0, hb1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    d_tmp = torch.empty(ne * CLIP, dtype=torch.int16, device=dev)
+    d_tmp.copy_(h_pcm, non_blocking=True)
+    barrier()
+    hb0.record(st)
+    for _ in range(3):
+        d_tmp.copy_(h_pcm, non_blocking=True)
+    hb1.record(st)
+    torch.cuda.synchronize()
+    h2d_gbs = 3 * ne * CLIP * 2 / (hb0.elapsed_time(hb1) / 1e3) / 1e9
+    del d_tmp
     same = bool((h_logits.to(dev) == logits[:ne]).all().item())
 
     # ---- streaming (config #5): N_STREAMS concurrent streams, one hop = 1024 new samples per stream, device resident.
@@ -398,7 +410,9 @@ def run_ours(args, rank, world, local_rank):
                                            "frac": (n * 31 / (k1_ms / 1e3) * K1_WARP_INST_PER_FRAME) /
                                                    (sm_count * 4 * (clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965) * 1e6)}},
                 "e2e": {"value": e2e_val, "unit": "clips/s", "h2d_bytes_per_step": ne * CLIP * 2, "d2h_bytes_per_step": ne * 20,
-                        "clips_per_step": ne, "matches_device_path": same},
+                        "clips_per_step": ne, "matches_device_path": same,
+                        "bound": "pcie", "h2d_peak_gbs": h2d_gbs, "achieved_gbs": (e2e_val / world) * CLIP * 2 / 1e9,
+                        "frac_of_h2d_peak": (e2e_val / world) * CLIP * 2 / 1e9 / h2d_gbs},
                 "gpu_launches": int(launches), "clocks": clocks}
         if stream_stats:
             line["streaming"] = stream_stats
