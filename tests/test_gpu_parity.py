@@ -42,6 +42,17 @@ def test_mfcc_q15_launch_geometries(edison, oracle):
         assert (got == want[:n]).all(), n
 
 
+def test_mfcc_q15_repeatable(edison, oracle):
+    """warp groups drift against each other inside a CTA (named barriers per group): repeated launches on the same input must
+    give the same bits every time, and the oracle's"""
+    pcm = common.synth_frames(20000, seed=91)
+    first = edison.mfcc_q15_batch(pcm)
+    for _ in range(4):
+        assert (edison.mfcc_q15_batch(pcm) == first).all()
+    pick = np.arange(0, 20000, 37)
+    assert (first[pick] == oracle.mfcc(pcm[pick])).all()
+
+
 def test_mfcc_empty(edison):
     assert edison.mfcc_q15_batch(np.zeros((0, 1024), np.int16)).shape == (0, 32)
 
