@@ -11,9 +11,9 @@ CSRC      := edison_b200/csrc
 OBJDIR    := build
 LIB       := edison_b200/libedison_b200.so
 
-CU_SRCS   := $(CSRC)/mfcc_q15_kernel.cu $(CSRC)/nnom_q7_kernel.cu $(CSRC)/edison_api.cu $(CSRC)/stream.cu $(CSRC)/mfcc_float.cu $(CSRC)/cube_f32_kernel.cu $(CSRC)/nnom_generic.cu
-HDRS      := $(CSRC)/q15_arith.cuh $(CSRC)/mfcc_q15_core.cuh $(CSRC)/edison_internal.h include/edison_b200.h
-OBJS      := $(OBJDIR)/mfcc_q15_kernel.o $(OBJDIR)/nnom_q7_kernel.o $(OBJDIR)/edison_api.o $(OBJDIR)/stream.o $(OBJDIR)/mfcc_float.o $(OBJDIR)/cube_f32_kernel.o $(OBJDIR)/nnom_generic.o $(OBJDIR)/tables.o $(OBJDIR)/firmware_api.o
+CU_SRCS   := $(CSRC)/mfcc_q15_kernel.cu $(CSRC)/nnom_q7_kernel.cu $(CSRC)/nnom_q7_umma.cu $(CSRC)/edison_api.cu $(CSRC)/stream.cu $(CSRC)/mfcc_float.cu $(CSRC)/cube_f32_kernel.cu $(CSRC)/nnom_generic.cu
+HDRS      := $(CSRC)/k2_umma_plan.h $(CSRC)/nnom_blob.h $(CSRC)/q15_arith.cuh $(CSRC)/mfcc_q15_core.cuh $(CSRC)/edison_internal.h include/edison_b200.h
+OBJS      := $(OBJDIR)/mfcc_q15_kernel.o $(OBJDIR)/nnom_q7_kernel.o $(OBJDIR)/nnom_q7_umma.o $(OBJDIR)/edison_api.o $(OBJDIR)/stream.o $(OBJDIR)/mfcc_float.o $(OBJDIR)/cube_f32_kernel.o $(OBJDIR)/nnom_generic.o $(OBJDIR)/tables.o $(OBJDIR)/firmware_api.o
 
 all: $(LIB)
 
@@ -37,11 +37,13 @@ oracle:
 	$(MAKE) -C oracle all
 	$(MAKE) -C oracle ref
 
-emu: tests/host_emu/libemu_mfcc.so
+emu: tests/host_emu/libemu_mfcc.so tests/host_emu/libemu_k2.so
+tests/host_emu/libemu_k2.so: tests/host_emu/emu_k2.cpp $(CSRC)/k2_umma_plan.h $(CSRC)/nnom_blob.h
+	$(CXX) -O2 -std=c++17 -Wall -Wno-unknown-pragmas -fPIC -shared -I$(CSRC) tests/host_emu/emu_k2.cpp -o $@
 tests/host_emu/libemu_mfcc.so: tests/host_emu/emu_mfcc.cpp $(CSRC)/tables.cpp $(HDRS)
 	$(CXX) -O2 -std=c++17 -ffp-contract=off -fno-strict-aliasing -fPIC -shared -I/usr/local/cuda/include -I$(CSRC) tests/host_emu/emu_mfcc.cpp $(CSRC)/tables.cpp -o $@
 
 clean:
-	rm -rf $(OBJDIR) $(LIB) tests/host_emu/libemu_mfcc.so
+	rm -rf $(OBJDIR) $(LIB) tests/host_emu/libemu_mfcc.so tests/host_emu/libemu_k2.so
 
 .PHONY: all oracle emu clean

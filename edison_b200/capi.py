@@ -49,6 +49,9 @@ def lib():
         L.edison_infer_q7_batch_dev.argtypes = [vp, sz, vp, vp, vp]
         L.edison_kws_batch_dev.argtypes = [vp, sz, sz, vp, vp, vp, vp]
         L.edison_sync.argtypes = [vp]
+        L.edison_kws_counts_dev.argtypes = [vp, sz, sz, vp, vp, vp, vp, vp]
+        L.edison_infer_q7_counts_dev.argtypes = [vp, sz, vp, vp, vp, vp]
+        L.edison_debug_infer_q7_legacy_dev.argtypes = [vp, sz, vp, vp, vp]
         L.edison_mfccf_create.argtypes = [ci, ci, ci, ci, ctypes.c_float, ctypes.POINTER(vp)]
         L.edison_mfccf_delete.argtypes = [vp]
         L.edison_mfccf_delete.restype = None
@@ -103,7 +106,8 @@ def check(rc, what="edison"):
         raise EdisonError("%s failed (%d): %s" % (what, rc, lib().edison_last_error().decode(errors="replace")))
 
 
-def init(device=-1, data_dir=None, softmax_mode=SOFTMAX_CMSIS_REF, chunk_clips=0):
+def init(device=-1, data_dir=None, softmax_mode=SOFTMAX_CMSIS_SIMD, chunk_clips=0):
+    """softmax_mode defaults to the firmware build's variant (arm_softmax_q7 SIMD branch), like edison_init(NULL)"""
     cfg = _Cfg(device, data_dir.encode() if data_dir else None, softmax_mode, chunk_clips)
     check(lib().edison_init(ctypes.byref(cfg)), "edison_init")
 

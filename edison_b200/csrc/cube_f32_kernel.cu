@@ -387,6 +387,7 @@ using namespace edison;
 extern "C" {
 
 int edison_infer_f32_batch_dev(const float *d_net_in, size_t n, float *d_logits, float *d_softmax, void *stream) {
+  DeviceScope device_scope_;
   if (n && !d_net_in) return ctx_fail(EDISON_E_ARG, "edison_infer_f32_batch_dev: null input");
   ctx_lock();
   CtxView c;
@@ -397,6 +398,7 @@ int edison_infer_f32_batch_dev(const float *d_net_in, size_t n, float *d_logits,
 }
 
 int edison_infer_f32_batch(const float *net_in, size_t n, float *logits, float *softmax) {
+  DeviceScope device_scope_;
   if (n && !net_in) return ctx_fail(EDISON_E_ARG, "edison_infer_f32_batch: null input");
   if (cube_dev_ptr(net_in)) {
     int rc = edison_infer_f32_batch_dev(net_in, n, logits, softmax, nullptr);

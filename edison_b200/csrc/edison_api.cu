@@ -109,8 +109,26 @@ static void load_keywords(const std::string &path) {
   fclose(fh);
 }
 
-static int do_init(const edison_cfg *cfg) {
-  if (g.ready) return EDISON_OK;
+static void release_device_state(void) {
+  for (int i = 0; i < 2; i++) {
+    Slot &s = g.slot[i];
+    void *bufs[] = {s.pcm, s.mfcc, s.net_in, s.logits, s.softmax};
+    for (void *b : bufs)
+      if (b) cudaFree(b);
+    if (s.stream) cudaStreamDestroy(s.stream);
+    s = Slot();
+  }
+  if (g.d_tables) cudaFree(g.d_tables);
+  nnom_free(g.d_model);
+  g.d_tables = nullptr;
+  g.d_model = nullptr;
+}
+
+// The firmware build is -DARM_MATH_DSP (firmware/Makefile:30) with NNOM_USING_CMSIS_NN (nnom_port.h:42): arm_softmax_q7 runs its
+// SIMD branch (8-bit wrapping __SSUB8 / __SADD8), so that is what the drop-in symbols compute unless a cfg says otherwise.
+static const int kDefaultSoftmax = EDISON_SOFTMAX_CMSIS_SIMD;
+
+static int do_init_locked(const edison_cfg *cfg) {
   int n_dev = 0;
   cudaError_t e = cudaGetDeviceCount(&n_dev);
   if (e != cudaSuccess || n_dev == 0) {
@@ -125,9 +143,9 @@ static int do_init(const edison_cfg *cfg) {
   if (prop.major < 10)
     return fail(EDISON_E_NOGPU, "device %d is sm_%d%d; this library is built for sm_100a only", g.device, prop.major, prop.minor);
   g.sm_count = prop.multiProcessorCount;
-  g.softmax_mode = cfg ? cfg->softmax_mode : EDISON_SOFTMAX_CMSIS_REF;
+  g.softmax_mode = cfg ? cfg->softmax_mode : kDefaultSoftmax;
   if (g.softmax_mode < 0 || g.softmax_mode > 2) return fail(EDISON_E_ARG, "softmax_mode %d", g.softmax_mode);
-  if (cfg && cfg->chunk_clips) g.chunk_clips = cfg->chunk_clips;
+  g.chunk_clips = (cfg && cfg->chunk_clips) ? cfg->chunk_clips : 8192;
   g.data_dir = (cfg && cfg->data_dir) ? std::string(cfg->data_dir) : default_data_dir();
 
   char err[256] = "";
@@ -140,14 +158,62 @@ static int do_init(const edison_cfg *cfg) {
   r = build_mfcc_tables(ht, (g.data_dir + "/mel_q15.bin").c_str(), err, sizeof err);
   if (r) { free(ht); return fail(r, "%s", err); }
   ht->in_scale = g.in_scale; ht->in_min = g.in_min; ht->in_max = g.in_max;
-  CU(cudaMalloc(&g.d_tables, sizeof(MfccTables)));
-  CU(cudaMemcpy(g.d_tables, ht, sizeof(MfccTables), cudaMemcpyHostToDevice));
+  cudaError_t ce = cudaMalloc(&g.d_tables, sizeof(MfccTables));
+  if (ce == cudaSuccess) ce = cudaMemcpy(g.d_tables, ht, sizeof(MfccTables), cudaMemcpyHostToDevice);
   free(ht);
+  if (ce != cudaSuccess) return fail(EDISON_E_CUDA, "table upload: %s", cudaGetErrorString(ce));
   load_keywords(g.data_dir + "/keywords.txt");
   CU(mfcc_q15_configure());
   CU(nnom_configure());
   for (int i = 0; i < 2; i++) CU(cudaStreamCreateWithFlags(&g.slot[i].stream, cudaStreamNonBlocking));
-  g.ready = true;
+  return EDISON_OK;
+}
+
+static int do_init(const edison_cfg *cfg) {
+  if (g.ready) {
+    // one context per process: a second edison_init may repeat the first one's choices, not change them
+    if (cfg) {
+      if (cfg->device >= 0 && cfg->device != g.device)
+        return fail(EDISON_E_ARG, "edison_init: already bound to device %d (asked for %d); edison_shutdown() first", g.device, cfg->device);
+      if (cfg->softmax_mode != g.softmax_mode)
+        return fail(EDISON_E_ARG, "edison_init: already initialised with softmax_mode %d (asked for %d); use edison_set_softmax_mode()",
+                    g.softmax_mode, cfg->softmax_mode);
+      if (cfg->data_dir && g.data_dir != cfg->data_dir)
+        return fail(EDISON_E_ARG, "edison_init: already initialised from %s", g.data_dir.c_str());
+    }
+    return EDISON_OK;
+  }
+  int prev = -1;
+  cudaGetDevice(&prev);
+  cudaGetLastError();
+  const int r = do_init_locked(cfg);
+  if (r) {   // nothing half-built survives a failed init: a retry starts from scratch
+    release_device_state();
+    cudaGetLastError();
+  } else {
+    g.ready = true;
+  }
+  if (prev >= 0 && prev != g.device) cudaSetDevice(prev);   // the caller's current device is the caller's business
+  return r;
+}
+
+int ctx_device(void) { return g.ready ? g.device : -1; }
+
+// 0 = null, 1 = host (pageable or pinned), 2 = device / managed
+static int ptr_kind(const void *p) {
+  if (!p) return 0;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return 1; }
+  return (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) ? 2 : 1;
+}
+// every non-null pointer of a call must live on the same side as `ref`: a kernel storing to a pageable host address would be a
+// sticky illegal-address fault for the whole process
+static int same_side(const void *ref, const void *a, const void *b = nullptr, const void *c = nullptr, const void *d = nullptr) {
+  const int k = ptr_kind(ref);
+  const void *others[] = {a, b, c, d};
+  for (const void *o : others)
+    if (o && ptr_kind(o) != k)
+      return fail(EDISON_E_ARG, "mixed host and device pointers in one call (input is a %s pointer)", k == 2 ? "device" : "host");
   return EDISON_OK;
 }
 
@@ -173,10 +239,10 @@ static int mfcc_dev(const int16_t *d_pcm, size_t n_clips, size_t fpc, size_t str
   return EDISON_OK;
 }
 
-static int infer_dev(const int8_t *d_in, size_t n, int8_t *d_logits, int8_t *d_softmax, cudaStream_t st) {
+static int infer_dev(const int8_t *d_in, size_t n, int8_t *d_logits, int8_t *d_softmax, int32_t *d_counts, cudaStream_t st) {
   if (!n) return EDISON_OK;
-  if (!d_in || (!d_logits && !d_softmax)) return fail(EDISON_E_ARG, "null pointer");
-  CU(launch_nnom_q7(g.d_model, d_in, (long long)n, d_logits, d_softmax, g.softmax_mode, g.sm_count, st));
+  if (!d_in || (!d_logits && !d_softmax && !d_counts)) return fail(EDISON_E_ARG, "null pointer");
+  CU(launch_nnom_q7(g.d_model, d_in, (long long)n, d_logits, d_softmax, g.softmax_mode, g.sm_count, st, d_counts));
   return EDISON_OK;
 }
 
@@ -216,7 +282,7 @@ static int kws_host_chunks(const int16_t *pcm, size_t n_clips, size_t fpc, size_
     int8_t *d_net = (net_in || want_net) ? (int8_t *)s.net_in : nullptr;
     if ((rc = mfcc_dev((const int16_t *)s.pcm, nc, fpc, stride, mfcc ? (int16_t *)s.mfcc : nullptr, d_net, s.stream))) return rc;
     if (want_net &&
-        (rc = infer_dev(d_net, nc, logits ? (int8_t *)s.logits : nullptr, softmax ? (int8_t *)s.softmax : nullptr, s.stream)))
+        (rc = infer_dev(d_net, nc, logits ? (int8_t *)s.logits : nullptr, softmax ? (int8_t *)s.softmax : nullptr, nullptr, s.stream)))
       return rc;
     if (mfcc) CU(cudaMemcpyAsync(mfcc + c0 * fpc * 32, s.mfcc, nf * 64, cudaMemcpyDeviceToHost, s.stream));
     if (net_in) CU(cudaMemcpyAsync(net_in + c0 * fpc * EDISON_N_COEFF, s.net_in, nf * EDISON_N_COEFF, cudaMemcpyDeviceToHost, s.stream));
@@ -244,7 +310,7 @@ static int infer_host_chunks(const int8_t *net_in, size_t n, int8_t *logits, int
     if (softmax && (rc = ensure(&s.softmax, &s.softmax_cap, nc * EDISON_N_CLASSES))) return rc;
     CU(cudaMemcpyAsync(s.net_in, net_in + c0 * EDISON_NET_IN, nc * EDISON_NET_IN, cudaMemcpyHostToDevice, s.stream));
     if ((rc = infer_dev((const int8_t *)s.net_in, nc, logits ? (int8_t *)s.logits : nullptr,
-                        softmax ? (int8_t *)s.softmax : nullptr, s.stream)))
+                        softmax ? (int8_t *)s.softmax : nullptr, nullptr, s.stream)))
       return rc;
     if (logits) CU(cudaMemcpyAsync(logits + c0 * EDISON_N_CLASSES, s.logits, nc * EDISON_N_CLASSES, cudaMemcpyDeviceToHost, s.stream));
     if (softmax) CU(cudaMemcpyAsync(softmax + c0 * EDISON_N_CLASSES, s.softmax, nc * EDISON_N_CLASSES, cudaMemcpyDeviceToHost, s.stream));
@@ -272,6 +338,7 @@ int ctx_acquire(CtxView *out) {  // caller holds ctx_lock()
   out->softmax_mode = g.softmax_mode;
   out->stream = g.slot[0].stream;
   out->data_dir = g.data_dir.c_str();
+  out->device = g.device;
   return EDISON_OK;
 }
 
@@ -297,21 +364,11 @@ int edison_init(const edison_cfg *cfg) {
 void edison_shutdown(void) {
   std::lock_guard<std::mutex> lk(g_mu);
   if (!g.ready) return;
+  DeviceScope device_scope_;
   cudaDeviceSynchronize();
-  for (int i = 0; i < 2; i++) {
-    Slot &s = g.slot[i];
-    void *bufs[] = {s.pcm, s.mfcc, s.net_in, s.logits, s.softmax};
-    for (void *b : bufs)
-      if (b) cudaFree(b);
-    if (s.stream) cudaStreamDestroy(s.stream);
-    s = Slot();
-  }
-  if (g.d_tables) cudaFree(g.d_tables);
-  nnom_free(g.d_model);
+  release_device_state();
   mfcc_float_release();
   cube_release();
-  g.d_tables = nullptr;
-  g.d_model = nullptr;
   g.ready = false;
 }
 
@@ -327,6 +384,7 @@ int edison_set_softmax_mode(int mode) {
 unsigned long long edison_launch_count(void) { return g_launches.load(); }
 
 void *edison_host_alloc(size_t bytes) {
+  DeviceScope device_scope_;
   void *p = nullptr;
   if (cudaMallocHost(&p, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
   return p;
@@ -339,9 +397,11 @@ int edison_mfcc_q15_clips(const int16_t *pcm, size_t n_clips, size_t frames_per_
                           int16_t *mfcc, int8_t *net_in) {
   std::lock_guard<std::mutex> lk(g_mu);
   REQUIRE_READY();
+  DeviceScope device_scope_;
   if (!n_clips || !frames_per_clip) return EDISON_OK;
   if (!pcm || (!mfcc && !net_in)) return fail(EDISON_E_ARG, "null pointer");
   if (n_clips > 1 && clip_stride_samples == 0) return fail(EDISON_E_ARG, "zero clip stride");
+  if (int r = same_side(pcm, mfcc, net_in)) return r;
   if (is_device_ptr(pcm)) {
     int r = mfcc_dev(pcm, n_clips, frames_per_clip, clip_stride_samples, mfcc, net_in, g.slot[0].stream);
     if (r) return r;
@@ -359,9 +419,11 @@ int edison_kws_batch(const int16_t *pcm, size_t n_clips, size_t clip_stride_samp
                      int8_t *net_in) {
   std::lock_guard<std::mutex> lk(g_mu);
   REQUIRE_READY();
+  DeviceScope device_scope_;
   if (!n_clips) return EDISON_OK;
   if (!pcm || (!logits && !softmax && !net_in)) return fail(EDISON_E_ARG, "null pointer");
   if (n_clips > 1 && clip_stride_samples == 0) return fail(EDISON_E_ARG, "zero clip stride");
+  if (int r = same_side(pcm, logits, softmax, net_in)) return r;
   if (is_device_ptr(pcm)) {
     cudaStream_t st = g.slot[0].stream;
     Slot &s = g.slot[0];
@@ -374,7 +436,7 @@ int edison_kws_batch(const int16_t *pcm, size_t n_clips, size_t clip_stride_samp
     int r = mfcc_dev(pcm, n_clips, EDISON_N_FRAMES, clip_stride_samples, nullptr, d_net, st);
     if (r) return r;
     if (logits || softmax) {
-      r = infer_dev(d_net, n_clips, logits, softmax, st);
+      r = infer_dev(d_net, n_clips, logits, softmax, nullptr, st);
       if (r) return r;
     }
     CU(cudaStreamSynchronize(st));
@@ -386,10 +448,12 @@ int edison_kws_batch(const int16_t *pcm, size_t n_clips, size_t clip_stride_samp
 int edison_infer_q7_batch(const int8_t *net_in, size_t n, int8_t *logits, int8_t *softmax) {
   std::lock_guard<std::mutex> lk(g_mu);
   REQUIRE_READY();
+  DeviceScope device_scope_;
   if (!n) return EDISON_OK;
   if (!net_in || (!logits && !softmax)) return fail(EDISON_E_ARG, "null pointer");
+  if (int r = same_side(net_in, logits, softmax)) return r;
   if (is_device_ptr(net_in)) {
-    int r = infer_dev(net_in, n, logits, softmax, g.slot[0].stream);
+    int r = infer_dev(net_in, n, logits, softmax, nullptr, g.slot[0].stream);
     if (r) return r;
     CU(cudaStreamSynchronize(g.slot[0].stream));
     return EDISON_OK;
@@ -400,28 +464,44 @@ int edison_infer_q7_batch(const int8_t *net_in, size_t n, int8_t *logits, int8_t
 int edison_mfcc_q15_clips_dev(const int16_t *d_pcm, size_t n_clips, size_t frames_per_clip, size_t clip_stride_samples,
                               int16_t *d_mfcc, int8_t *d_net_in, void *stream) {
   if (!g.ready) return fail(EDISON_E_NOINIT, "edison_init() first");
+  DeviceScope device_scope_;
   return mfcc_dev(d_pcm, n_clips, frames_per_clip, clip_stride_samples, d_mfcc, d_net_in,
                   stream ? (cudaStream_t)stream : g.slot[0].stream);
 }
 
 int edison_infer_q7_batch_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, void *stream) {
   if (!g.ready) return fail(EDISON_E_NOINIT, "edison_init() first");
-  return infer_dev(d_net_in, n, d_logits, d_softmax, stream ? (cudaStream_t)stream : g.slot[0].stream);
+  DeviceScope device_scope_;
+  return infer_dev(d_net_in, n, d_logits, d_softmax, nullptr, stream ? (cudaStream_t)stream : g.slot[0].stream);
 }
 
 int edison_kws_batch_dev(const int16_t *d_pcm, size_t n_clips, size_t clip_stride_samples, int8_t *d_logits,
                          int8_t *d_softmax, int8_t *d_net_in, void *stream) {
+  return edison_kws_counts_dev(d_pcm, n_clips, clip_stride_samples, d_logits, d_softmax, d_net_in, nullptr, stream);
+}
+
+int edison_kws_counts_dev(const int16_t *d_pcm, size_t n_clips, size_t clip_stride_samples, int8_t *d_logits, int8_t *d_softmax,
+                          int8_t *d_net_in, int32_t *d_class_counts, void *stream) {
   if (!g.ready) return fail(EDISON_E_NOINIT, "edison_init() first");
   if (!d_net_in) return fail(EDISON_E_ARG, "d_net_in scratch [n_clips][403] is required by the _dev variant");
+  DeviceScope device_scope_;
   cudaStream_t st = stream ? (cudaStream_t)stream : g.slot[0].stream;
   int r = mfcc_dev(d_pcm, n_clips, EDISON_N_FRAMES, clip_stride_samples, nullptr, d_net_in, st);
   if (r) return r;
-  if (d_logits || d_softmax) return infer_dev(d_net_in, n_clips, d_logits, d_softmax, st);
+  if (d_logits || d_softmax || d_class_counts) return infer_dev(d_net_in, n_clips, d_logits, d_softmax, d_class_counts, st);
   return EDISON_OK;
+}
+
+int edison_infer_q7_counts_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, int32_t *d_class_counts,
+                               void *stream) {
+  if (!g.ready) return fail(EDISON_E_NOINIT, "edison_init() first");
+  DeviceScope device_scope_;
+  return infer_dev(d_net_in, n, d_logits, d_softmax, d_class_counts, stream ? (cudaStream_t)stream : g.slot[0].stream);
 }
 
 int edison_sync(void *stream) {
   if (!g.ready) return fail(EDISON_E_NOINIT, "edison_init() first");
+  DeviceScope device_scope_;
   CU(cudaStreamSynchronize(stream ? (cudaStream_t)stream : g.slot[0].stream));
   return EDISON_OK;
 }
@@ -429,31 +509,44 @@ int edison_sync(void *stream) {
 int edison_debug_sqrt_q31(const int32_t *in, size_t n, int32_t *out) {
   std::lock_guard<std::mutex> lk(g_mu);
   REQUIRE_READY();
+  DeviceScope device_scope_;
   if (!n) return EDISON_OK;
   int32_t *d_in = nullptr, *d_out = nullptr;
-  CU(cudaMalloc(&d_in, n * 4));
-  CU(cudaMalloc(&d_out, n * 4));
-  CU(cudaMemcpy(d_in, in, n * 4, cudaMemcpyHostToDevice));
-  CU(launch_debug_sqrt(d_in, n, d_out, g.slot[0].stream));
-  CU(cudaStreamSynchronize(g.slot[0].stream));
-  CU(cudaMemcpy(out, d_out, n * 4, cudaMemcpyDeviceToHost));
-  cudaFree(d_in);
-  cudaFree(d_out);
+  cudaError_t e = cudaMalloc(&d_in, n * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&d_out, n * 4);
+  if (e == cudaSuccess) e = cudaMemcpy(d_in, in, n * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = launch_debug_sqrt(d_in, n, d_out, g.slot[0].stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(g.slot[0].stream);
+  if (e == cudaSuccess) e = cudaMemcpy(out, d_out, n * 4, cudaMemcpyDeviceToHost);
+  if (d_in) cudaFree(d_in);
+  if (d_out) cudaFree(d_out);
+  if (e != cudaSuccess) return fail(EDISON_E_CUDA, "edison_debug_sqrt_q31: %s", cudaGetErrorString(e));
   return EDISON_OK;
 }
 
 int edison_debug_mag_sweep(uint32_t lo, uint32_t hi, unsigned long long *mismatches, unsigned long long *checksum) {
   std::lock_guard<std::mutex> lk(g_mu);
   REQUIRE_READY();
+  DeviceScope device_scope_;
   unsigned long long *d = nullptr, h[2] = {0, 0};
-  CU(cudaMalloc(&d, 16));
-  CU(cudaMemset(d, 0, 16));
-  CU(launch_debug_mag_sweep(lo, hi, g.d_tables->sqrt_exc, d, g.slot[0].stream));
-  CU(cudaStreamSynchronize(g.slot[0].stream));
-  CU(cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost));
-  cudaFree(d);
+  cudaError_t e = cudaMalloc(&d, 16);
+  if (e == cudaSuccess) e = cudaMemset(d, 0, 16);
+  if (e == cudaSuccess) e = launch_debug_mag_sweep(lo, hi, g.d_tables->sqrt_exc, d, g.slot[0].stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(g.slot[0].stream);
+  if (e == cudaSuccess) e = cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost);
+  if (d) cudaFree(d);
+  if (e != cudaSuccess) return fail(EDISON_E_CUDA, "edison_debug_mag_sweep: %s", cudaGetErrorString(e));
   if (mismatches) *mismatches = h[0];
   if (checksum) *checksum = h[1];
+  return EDISON_OK;
+}
+
+// the round-1 mma.sync kernel, for A/B timing of the two tensor paths (tools/k2_time.py); device pointers only
+int edison_debug_infer_q7_legacy_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, void *stream) {
+  if (!g.ready) return fail(EDISON_E_NOINIT, "edison_init() first");
+  DeviceScope device_scope_;
+  CU(launch_nnom_q7_legacy(g.d_model, d_net_in, (long long)n, d_logits, d_softmax, g.softmax_mode, g.sm_count,
+                           stream ? (cudaStream_t)stream : g.slot[0].stream));
   return EDISON_OK;
 }
 

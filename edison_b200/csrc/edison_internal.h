@@ -30,8 +30,15 @@ int nnom_load(const char *blob_path, NnomModel **out_dev_model, int *in_scale, i
               char *err, size_t errlen);
 void nnom_free(NnomModel *m);
 cudaError_t nnom_configure(void);
+// K2 (tcgen05 kernel, nnom_q7_umma.cu).  class_counts: optional device int32[10], += number of clips per first-maximum logit class
 cudaError_t launch_nnom_q7(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits,
-                           int8_t *softmax, int softmax_mode, int sm_count, cudaStream_t stream);
+                           int8_t *softmax, int softmax_mode, int sm_count, cudaStream_t stream, int *class_counts = nullptr);
+cudaError_t launch_nnom_q7_legacy(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax,
+                                  int softmax_mode, int sm_count, cudaStream_t stream);   // round-1 mma.sync kernel (A/B timing only)
+cudaError_t nnom_umma_configure(void);
+int nnom_umma_upload(const int8_t *const w[5], const int8_t *const b[5], const int rs[5], const int ls[5], uint8_t **out_image);
+cudaError_t launch_nnom_q7_umma(const uint8_t *image, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax, int softmax_mode,
+                                int *class_counts, int sm_count, cudaStream_t stream);
 
 // incremental sliding-window inference (one new row per layer and hop); state rings live in one device allocation
 struct NnomIncrState { int8_t *c1, *p1, *c2, *p2, *c3; };
@@ -58,6 +65,24 @@ struct CtxView {
   int softmax_mode;
   cudaStream_t stream;        // the library's default stream
   const char *data_dir;       // directory of the model / table blobs (valid until edison_shutdown)
+  int device;                 // the CUDA device the library is bound to
+};
+// One context per process, bound to one device (edison_init).  Every public entry point makes that device current for the
+// calling thread and restores the caller's on return, so calls from other threads or after the caller switched devices
+// still allocate, copy and launch on the library's GPU.
+int ctx_device(void);                              // the bound device, -1 before edison_init
+struct DeviceScope {
+  int prev = -1, want = -1;
+  DeviceScope() {
+    want = ctx_device();
+    if (want >= 0 && cudaGetDevice(&prev) == cudaSuccess && prev != want) cudaSetDevice(want);
+    else prev = want;
+  }
+  ~DeviceScope() {
+    if (prev != want && prev >= 0) cudaSetDevice(prev);
+  }
+  DeviceScope(const DeviceScope &) = delete;
+  DeviceScope &operator=(const DeviceScope &) = delete;
 };
 int ctx_acquire(CtxView *out);                     // initialises the library on first use; EDISON_OK or an error code
 int ctx_fail(int code, const char *fmt, ...);      // records the thread's last-error text, returns code

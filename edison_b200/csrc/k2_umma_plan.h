@@ -1,0 +1,376 @@
+// k2_umma_plan.h -- the static plan of K2 (int8 NNoM keyword-spotting net, firmware/src/ai/nnom/kws_nnom/weights.h:138-161)
+// on the Blackwell tensor path: which tcgen05.mma instructions run, on which shared-memory bytes, in which order, and how
+// each accumulator tile is turned into the next layer's activations.  Everything here is plain constexpr / inline C++ so
+// that the SAME plan drives the CUDA kernel (nnom_q7_umma.cu) and a host emulation of it (tests/host_emu/emu_k2.cpp, which
+// checks the index arithmetic against the oracle without a GPU).
+//
+// Layout idea ("clip-minor activations, convolution by descriptor strides"):
+//   * a CTA owns a batch of NC = 32 clips; an activation tensor [H][W][C] of the batch lives in shared memory as
+//       [C/16 planes][H*W pixels][32 clips][16 channels]            (512 B per pixel and plane)
+//     so 8 consecutive 16-byte units are 8 clips at one pixel = one core matrix of a NO-SWIZZLE K-major UMMA operand, and
+//     128 consecutive units (= the M = 128 rows of one MMA) are 4 consecutive pixels x 32 clips: the A operand of filter
+//     tap (ky, kx) is the SAME array read from a start address shifted by (ky * W + kx) pixels -- no im2col, no copies;
+//   * K = 32 int8 per instruction = two 16-byte chunks LBO bytes apart: two taps (C = 16), the two channel halves of one tap
+//     (C = 32), or two of the four channel quarters (C = 64);
+//   * outputs at the wrap-around pixels of an image row (x >= W_out) are computed and dropped;
+//   * conv1 (one input channel) is a banded (Toeplitz) product instead: an A row is (clip, image row) with the 13 input
+//     bytes of that row (padded to 16) as one chunk, N = (x_out, channel) = 9 x 16, B = the 5x5 kernel laid out along x;
+//     even and odd conv rows go to two accumulator tiles of the same lane, so the 2x1 max pool is a max in registers;
+//   * accumulators live in TMEM (lane = 32 * pixel-in-tile + clip, column = output channel), two slots of 256 columns;
+//     16 epilogue warps read them back with tcgen05.ld (lane = clip), add the bias seed, shift, saturate, ReLU, pool,
+//     pack 16 channels into one 16-byte store in the next layer's layout.
+// int32 accumulation is exact and order independent, so the result has the reference's bits
+// (arm_convolve_HWC_q7_fast_nonsquare.c:74-375, arm_fully_connected_q7_opt.c:129-475, nnom_local.c:117-160, 425-484).
+#pragma once
+#include <stdint.h>
+#include <string.h>
+
+#if defined(__CUDACC__)
+#define K2_HD __host__ __device__ __forceinline__
+#else
+#define K2_HD inline
+#endif
+
+namespace edison {
+namespace k2 {
+
+constexpr int NC = 32;                 // clips per batch
+constexpr int kEpiWarps = 16;          // warps 0..15: epilogue (lane quarter = warp & 3, work group = warp >> 2); warp 16 issues
+constexpr int kThreads = (kEpiWarps + 1) * 32;
+constexpr uint32_t PX = NC * 16;       // bytes of one pixel in one 16-channel plane
+constexpr int kNetIn = 403;
+
+// ---- shared-memory map (byte offsets from the dynamic shared memory base) --------------------------------------------
+// weight image (built once on the host, copied in with one bulk copy)
+constexpr uint32_t W1_BLK = 144 * 16;                    // one K-chunk of a conv1 B matrix: 144 rows (x * 16 + c) x 16 bytes
+constexpr uint32_t OFF_W1 = 0;                           // 11 blocks: E0c0 E0c1 E1c0 E1c1 E2c0 Z O0c1 O1c0 O1c1 O2c0 O2c1
+constexpr uint32_t OFF_W2 = OFF_W1 + 11 * W1_BLK;        // 5 x [2][32][16]
+constexpr uint32_t OFF_W3 = OFF_W2 + 5 * 1024;           // 9 x [2][64][16]
+constexpr uint32_t OFF_W4 = OFF_W3 + 9 * 2048;           // 18 x [2][32][16]
+constexpr uint32_t OFF_WD = OFF_W4 + 18 * 1024;          // 3 x [2][16][16]
+constexpr uint32_t OFF_PAR = OFF_WD + 3 * 512;           // int32: seed1[16] seed2[32] seed3[64] seed4[32] seedd[16] rs[5] hi[5]
+constexpr int PAR_SEED1 = 0, PAR_SEED2 = 16, PAR_SEED3 = 48, PAR_SEED4 = 112, PAR_SEEDD = 144, PAR_RS = 160, PAR_HI = 165;
+constexpr uint32_t PAR_BYTES = 704;
+constexpr uint32_t IMAGE_BYTES = OFF_PAR + PAR_BYTES;    // 69,568
+// activations
+constexpr uint32_t OFF_C0 = IMAGE_BYTES;                 // input rows: [parity][row / 2 (14)][clip][16]; rows 28..30 never matter
+constexpr uint32_t C0_HALF = 14 * PX;
+constexpr uint32_t OFF_RAW = OFF_C0 + 2 * C0_HALF;       // the batch's [32][403] input bytes as they lie in HBM (bulk copy target)
+constexpr uint32_t RAW_BYTES = NC * kNetIn + 16;
+constexpr uint32_t OFF_C1P = OFF_RAW + RAW_BYTES;        // pooled conv1: 12 rows x 9 px (+2 px read by zero-weight / dropped taps)
+constexpr uint32_t OFF_C2P = OFF_C1P + 110 * PX;         // pooled conv2: 2 planes x (5 x 7 px + 1)
+constexpr uint32_t PLANE2 = 36 * PX;
+constexpr uint32_t OFF_C3 = OFF_C2P + 2 * PLANE2;        // conv3: 4 planes x (3 x 5 px + 1)
+constexpr uint32_t PLANE3 = 16 * PX;
+constexpr uint32_t OFF_C4 = OFF_C3 + 4 * PLANE3;         // conv4: 2 planes x (3 px + 3 read by the dense tile's unused rows)
+constexpr uint32_t PLANE4 = 6 * PX;
+constexpr uint32_t OFF_BAR = OFF_C4 + 2 * PLANE4;        // mbarriers, TMEM base
+constexpr uint32_t SMEM_BYTES = OFF_BAR + 128;            // 6 mbarriers (48 B), TMEM base (4 B), class histogram (40 B)
+static_assert(IMAGE_BYTES % 16 == 0 && RAW_BYTES % 16 == 0 && OFF_BAR % 16 == 0, "16-byte granularity");
+static_assert(SMEM_BYTES <= 232448, "more than the 227 KB a CTA can have");
+
+// ---- the schedule --------------------------------------------------------------------------------------------------------
+// One loop iteration runs 16 units: the head of batch b (conv1, conv2) interleaved with the tail of batch b - 1 (conv3, conv4,
+// dense, lag = 1), so that the tensor pipe never waits on the short serial tail and every unit's inputs were finished at
+// least two units earlier (the issuing thread only ever waits for the epilogue that frees its TMEM slot, slot = pos & 1).
+enum Kind { C1 = 0, C2 = 1, C3 = 2, C4 = 3, DN = 4 };
+struct Unit { int kind, a, b, lag; };   // C1: a = t (conv rows 8t..8t+7), b = x half; C2: a = pooled row; C3: a = first tile, b = tiles
+constexpr int kUnits = 16;
+constexpr Unit kSched[kUnits] = {
+    {C1, 0, 0, 0}, {C1, 0, 1, 0}, {C3, 0, 2, 1}, {C1, 1, 0, 0}, {C1, 1, 1, 0}, {C3, 2, 2, 1}, {C2, 0, 0, 0}, {C3, 4, 1, 1},
+    {C1, 2, 0, 0}, {C1, 2, 1, 0}, {C4, 0, 0, 1}, {C2, 1, 0, 0}, {C2, 2, 0, 0}, {DN, 0, 0, 1}, {C2, 3, 0, 0}, {C2, 4, 0, 0}};
+constexpr int kPosTranspose = 13;   // the epilogue of this unit also lays out the NEXT batch's input (c0 is free by then)
+constexpr int kPosNextRaw = 15;     // the issuing thread starts the bulk copy of the batch after that here (raw is free by then)
+
+struct MmaOp { uint32_t a_off, a_lbo, b_off, b_lbo, n, col, acc; };   // SBO = 128 for every operand
+
+// calls f(MmaOp) for every MMA of unit `pos`, in issue order; col is relative to the unit's TMEM slot
+template <int POS, class F> K2_HD void for_each_mma(F &&f) {
+  constexpr Unit u = kSched[POS];
+  if constexpr (u.kind == C1) {
+    // lanes quarter i <-> conv rows 8t + 2i (tile E, columns 0..) and 8t + 2i + 1 (tile O, columns 128..); chunk pair j:
+    // input rows 2(4t + i + j) and 2(4t + i + j) + 1.  Same A for both tiles; B holds the kernel rows each tile needs.
+    constexpr uint32_t n = u.b ? 64 : 80, xoff = u.b ? 80 * 16 : 0;
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const uint32_t a = OFF_C0 + (uint32_t)(4 * u.a + j) * PX;
+      constexpr int blkE[3] = {0, 2, 4}, blkO[3] = {5, 7, 9};
+      f(MmaOp{a, C0_HALF, OFF_W1 + blkE[j] * W1_BLK + xoff, W1_BLK, n, 0, (uint32_t)(j > 0)});
+      f(MmaOp{a, C0_HALF, OFF_W1 + blkO[j] * W1_BLK + xoff, W1_BLK, n, 128, (uint32_t)(j > 0)});
+    }
+  } else if constexpr (u.kind == C2) {
+    // pooled row r: conv rows y = 2r + p (p = 0, 1), x halves h: tile (p, h) at columns (2p + h) * 32, pixels x = 4h..4h+3
+#pragma unroll
+    for (int p = 0; p < 2; p++)
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const uint32_t y = 2 * u.a + p, col = (2 * p + h) * 32;
+#pragma unroll
+        for (int m = 0; m < 3; m++)   // taps (m, 0) + (m, 1): next pixel
+          f(MmaOp{OFF_C1P + ((y + m) * 9 + 4 * h) * PX, PX, OFF_W2 + m * 1024, 512, 32, col, (uint32_t)(m > 0)});
+        f(MmaOp{OFF_C1P + (y * 9 + 4 * h + 2) * PX, 9 * PX, OFF_W2 + 3 * 1024, 512, 32, col, 1});        // taps (0, 2) + (1, 2): next row
+        f(MmaOp{OFF_C1P + ((y + 2) * 9 + 4 * h + 2) * PX, PX, OFF_W2 + 4 * 1024, 512, 32, col, 1});      // tap (2, 2) + zero weights
+      }
+  } else if constexpr (u.kind == C3) {
+    // tile tau: output positions q = 4 tau .. 4 tau + 3 on the 7-wide input grid (y = q / 7, x = q % 7; x >= 5 dropped)
+#pragma unroll
+    for (int tl = 0; tl < u.b; tl++)
+#pragma unroll
+      for (int tap = 0; tap < 9; tap++)
+        f(MmaOp{OFF_C2P + (uint32_t)(4 * (u.a + tl) + (tap / 3) * 7 + tap % 3) * PX, PLANE2, OFF_W3 + tap * 2048, 1024, 64,
+                (uint32_t)tl * 64, (uint32_t)(tap > 0)});
+  } else if constexpr (u.kind == C4) {
+    // one tile: output positions x = 0..3 (3 dropped) on the 5-wide grid; per tap two MMAs (channels 0..31, 32..63)
+#pragma unroll
+    for (int tap = 0; tap < 9; tap++)
+#pragma unroll
+      for (int cp = 0; cp < 2; cp++)
+        f(MmaOp{OFF_C3 + (uint32_t)((tap / 3) * 5 + tap % 3) * PX + cp * 2 * PLANE3, PLANE3, OFF_W4 + (tap * 2 + cp) * 1024, 512, 32, 0,
+                (uint32_t)(tap + cp > 0)});
+  } else {
+    // dense: rows = clips (lanes 0..31; the other 96 rows read neighbouring pixels and are ignored), K = 3 px x 32 channels
+#pragma unroll
+    for (int m = 0; m < 3; m++) f(MmaOp{OFF_C4 + (uint32_t)m * PX, PLANE4, OFF_WD + m * 512, 256, 16, 0, (uint32_t)(m > 0)});
+  }
+}
+
+// ---- quantisation epilogue -------------------------------------------------------------------------------------------
+// clamp((m + seed) >> rs, 0, 127) = (max(min(m + seed, hi), 0)) >> rs with hi = (128 << rs) - 1: SSAT8 then ReLU
+// (nnom_activation.c:118-126) of a conv output whose seed already holds (bias << lshift) + round (nnom_local.c:425-484)
+K2_HD int q7_relu(int m, int seed, int hi, int rs) {
+#if defined(__CUDA_ARCH__)
+  return __viaddmin_s32_relu(m, seed, hi) >> rs;
+#else
+  int v = m + seed;
+  v = v < hi ? v : hi;
+  v = v > 0 ? v : 0;
+  return v >> rs;
+#endif
+}
+K2_HD uint32_t pack4(int a, int b, int c, int d) { return (uint32_t)a | ((uint32_t)b << 8) | ((uint32_t)c << 16) | ((uint32_t)d << 24); }
+K2_HD int imax(int a, int b) { return a > b ? a : b; }
+
+struct Vec16 { uint32_t x, y, z, w; };
+struct Int4 { int x, y, z, w; };
+
+// 16 consecutive int32 parameters starting at index i (a multiple of 4) as four 128-bit broadcast loads
+template <class Ctx> K2_HD void load16(Ctx &c, int i, int (&s)[16]) {
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const Int4 v = c.par4(i + 4 * k);
+    s[4 * k] = v.x; s[4 * k + 1] = v.y; s[4 * k + 2] = v.z; s[4 * k + 3] = v.w;
+  }
+}
+
+// 16 accumulators (optionally the max with 16 more: the 2x1 pool) -> 16 int8 activations
+template <bool POOL> K2_HD Vec16 quant16(const uint32_t (&e)[16], const uint32_t (&o)[16], const int *seed, int hi, int rs) {
+  int v[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) v[i] = q7_relu(POOL ? imax((int)e[i], (int)o[i]) : (int)e[i], seed[i], hi, rs);
+  return Vec16{pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7]), pack4(v[8], v[9], v[10], v[11]),
+               pack4(v[12], v[13], v[14], v[15])};
+}
+
+K2_HD int ssat8(int v) { return v < -128 ? -128 : (v > 127 ? 127 : v); }
+K2_HD int usat(int v, int bits) { return v < 0 ? 0 : (v > (1 << bits) - 1 ? (1 << bits) - 1 : v); }
+
+// arm_softmax_q7 (reference branch arm_softmax_q7.c:217-254, SIMD branch :83-215) and local_softmax_q7 (nnom_local.c:948-1003)
+// mode: EDISON_SOFTMAX_* (0 CMSIS reference, 1 CMSIS SIMD with 8-bit wrapping subtractions, 2 NNoM local)
+K2_HD void softmax_q7(const int8_t *in, int8_t *out, int mode) {
+  constexpr int n = 10;
+  if (mode == 2) {
+    int base = -257;
+    for (int i = 0; i < n; i++) base = imax(base, (int)in[i]);
+    base -= 8;
+    int sum = 0;
+    for (int i = 0; i < n; i++)
+      if (in[i] > base) sum += 1 << usat(in[i] - base, 5);
+    const int ob = 0x100000 / sum;
+    for (int i = 0; i < n; i++) out[i] = in[i] > base ? (int8_t)ssat8(ob >> usat(13 + base - in[i], 5)) : (int8_t)0;
+    return;
+  }
+  int base = -128;
+  for (int i = 0; i < n; i++) base = imax(base, (int)in[i]);
+  base -= 8;
+  const int nv = mode == 1 ? (n & ~3) : 0;   // handled 4 at a time with 8-bit wrap
+  int sum = 0;
+  for (int i = 0; i < n; i++) {
+    int d = in[i] - base;
+    if (i < nv) d = (int)(int8_t)(d & 0xff);   // __SSUB8 wraps (:127)
+    sum += 1 << usat(d, 3);
+  }
+  const int ob = (1 << 20) / sum;
+  for (int i = 0; i < n; i++) {
+    int d;
+    if (i < nv) {
+      const int t = (int)(int8_t)((13 - in[i]) & 0xff);               // __SSUB8(pad, in) :177
+      d = (int)(int8_t)((t + (int)(int8_t)(base & 0xff)) & 0xff);     // __SADD8(in, baseV) :178
+    } else {
+      d = 13 + base - in[i];
+    }
+    out[i] = (int8_t)ssat8(ob >> usat(d, 5));
+  }
+}
+
+// What the epilogue of one unit needs from its executor (CUDA kernel or host emulation):
+//   c.ld16(col, v)   : this thread's lane of TMEM columns col..col+15 of the unit's slot;  c.ld_wait() before using v
+//   c.st16(off, Vec16) : 16-byte shared-memory store;  c.par(i) / c.par4(i): int32 parameter(s) i (same for all lanes)
+//   c.lane, c.q (lane quarter = pixel in tile), c.g (work group)
+//   dense only: c.clip0 (first clip of the batch), c.nclips, c.logits, c.softmax (global, may be null), c.softmax_mode,
+//               c.count(cls) (class histogram hook)
+template <int POS, class Ctx> K2_HD void epilogue(Ctx &c) {
+  constexpr Unit u = kSched[POS];
+  if constexpr (u.kind == C1) {
+    constexpr int P = u.b ? 4 : 5;
+    const int rs = c.par(PAR_RS + 0), hi = c.par(PAR_HI + 0);
+    int seed[16];
+    load16(c, PAR_SEED1, seed);
+    const int r = 4 * u.a + c.q;   // pooled row
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      const int px = c.g + 4 * k;   // group g takes pixel g (and group 0 pixel 4 of the 5-pixel half)
+      if (px < P) {
+        uint32_t e[16], o[16];
+        c.ld16(px * 16, e);
+        c.ld16(128 + px * 16, o);
+        c.ld_wait();
+        c.st16(OFF_C1P + (uint32_t)(r * 9 + 5 * u.b + px) * PX + c.lane * 16, quant16<true>(e, o, seed, hi, rs));
+      }
+    }
+  } else if constexpr (u.kind == C2) {
+    const int rs = c.par(PAR_RS + 1), hi = c.par(PAR_HI + 1);
+    const int h = c.g >> 1, half = c.g & 1, x = 4 * h + c.q;
+    if (x < 7) {
+      int seed[16];
+      load16(c, PAR_SEED2 + half * 16, seed);
+      uint32_t e[16], o[16];
+      c.ld16(h * 32 + half * 16, e);
+      c.ld16((2 + h) * 32 + half * 16, o);
+      c.ld_wait();
+      c.st16(OFF_C2P + half * PLANE2 + (uint32_t)(u.a * 7 + x) * PX + c.lane * 16, quant16<true>(e, o, seed, hi, rs));
+    }
+  } else if constexpr (u.kind == C3) {
+    const int rs = c.par(PAR_RS + 2), hi = c.par(PAR_HI + 2);
+    const int tl = c.g >> 1, half = c.g & 1;          // tile in unit, 32-channel half
+    const int idx = 4 * (u.a + tl) + c.q, y = idx / 7, x = idx - y * 7;
+    if (tl < u.b && x < 5 && y < 3) {
+#pragma unroll
+      for (int k = 0; k < 2; k++) {
+        const int plane = 2 * half + k;
+        int seed[16];
+        load16(c, PAR_SEED3 + plane * 16, seed);
+        uint32_t e[16];
+        c.ld16(tl * 64 + plane * 16, e);
+        c.ld_wait();
+        c.st16(OFF_C3 + plane * PLANE3 + (uint32_t)(y * 5 + x) * PX + c.lane * 16, quant16<false>(e, e, seed, hi, rs));
+      }
+    }
+  } else if constexpr (u.kind == C4) {
+    const int rs = c.par(PAR_RS + 3), hi = c.par(PAR_HI + 3);
+    if (c.g < 2 && c.q < 3) {
+      int seed[16];
+      load16(c, PAR_SEED4 + c.g * 16, seed);
+      uint32_t e[16];
+      c.ld16(c.g * 16, e);
+      c.ld_wait();
+      c.st16(OFF_C4 + c.g * PLANE4 + (uint32_t)c.q * PX + c.lane * 16, quant16<false>(e, e, seed, hi, rs));
+    }
+  } else {
+    // Dense 96 -> 10 (nnom_dense.c:92-119): lane = clip; logits = SSAT8((acc + seed) >> rs); then softmax
+    if (c.g == 0 && c.q == 0) {
+      const int rs = c.par(PAR_RS + 4);
+      uint32_t e[16];
+      c.ld16(0, e);
+      c.ld_wait();
+      if (c.lane < c.nclips) {
+        int8_t lg[10];
+#pragma unroll
+        for (int i = 0; i < 10; i++) lg[i] = (int8_t)ssat8(((int)e[i] + c.par(PAR_SEEDD + i)) >> rs);
+        const long long clip = c.clip0 + c.lane;
+        if (c.logits)
+#pragma unroll
+          for (int i = 0; i < 10; i++) c.logits[clip * 10 + i] = lg[i];
+        if (c.softmax) {
+          int8_t sm[10];
+          softmax_q7(lg, sm, c.softmax_mode);
+#pragma unroll
+          for (int i = 0; i < 10; i++) c.softmax[clip * 10 + i] = sm[i];
+        }
+        int best = 0;   // first maximum of the logits: the class the firmware's arm_max would report on them
+#pragma unroll
+        for (int i = 1; i < 10; i++)
+          if (lg[i] > lg[best]) best = i;
+        c.count(best);
+      }
+    }
+  }
+}
+
+// input layout step: the 13 bytes of input row `row` of clip `clip` (raw = [clip][403]) -> c0[row & 1][row >> 1][clip][16].
+// w[0..3] are the four aligned 32-bit words that hold raw bytes a..a+12, a = clip * 403 + row * 13; bytes 13..15 of the chunk
+// only ever meet zero weights.
+K2_HD Vec16 input_chunk(const uint32_t (&w)[4], uint32_t a) {
+  const uint32_t sh = (a & 3) * 8;
+  Vec16 v;
+  if (sh == 0) return Vec16{w[0], w[1], w[2], w[3]};
+  v.x = (w[0] >> sh) | (w[1] << (32 - sh));
+  v.y = (w[1] >> sh) | (w[2] << (32 - sh));
+  v.z = (w[2] >> sh) | (w[3] << (32 - sh));
+  v.w = w[3] >> sh;
+  return v;
+}
+K2_HD uint32_t c0_offset(int row, int clip) { return OFF_C0 + (uint32_t)(row & 1) * C0_HALF + (uint32_t)(row >> 1) * PX + (uint32_t)clip * 16; }
+constexpr int kInRowsUsed = 28;   // conv rows 24..26 only feed the pooled row that conv2's pooling drops (and row 26 nothing)
+
+// ---- weight image (host) ---------------------------------------------------------------------------------------------
+// w[l], b[l]: the five layers' int8 weights in the reference's O,H,W,I order and biases; rs / ls: output right shifts and bias
+// left shifts (weights.h:72-105).  dense weights already de-interleaved to [10][96].
+inline void build_image(uint8_t *img, const int8_t *const w[5], const int8_t *const b[5], const int rs[5], const int ls[5]) {
+  memset(img, 0, IMAGE_BYTES);
+  // conv1: block (tile p, pair j, chunk h) holds kernel row ky = 2j + h (E) or 2j - 1 + h (O) along x:
+  //   row n = x * 16 + c, byte kk = input x: w1[c][ky][kk - x]
+  const int blk_of[2][3][2] = {{{0, 1}, {2, 3}, {4, 5}}, {{5, 6}, {7, 8}, {9, 10}}};
+  for (int p = 0; p < 2; p++)
+    for (int j = 0; j < 3; j++)
+      for (int h = 0; h < 2; h++) {
+        const int ky = p ? 2 * j - 1 + h : 2 * j + h;
+        if (ky < 0 || ky > 4) continue;   // the shared zero block
+        uint8_t *blk = img + OFF_W1 + blk_of[p][j][h] * W1_BLK;
+        for (int x = 0; x < 9; x++)
+          for (int c = 0; c < 16; c++)
+            for (int kx = 0; kx < 5; kx++) blk[(x * 16 + c) * 16 + x + kx] = (uint8_t)w[0][(c * 5 + ky) * 5 + kx];
+      }
+  // conv2: matrix m = [chunk][n][16]; taps per chunk as in for_each_mma
+  const int tap2[5][2] = {{0, 1}, {3, 4}, {6, 7}, {2, 5}, {8, -1}};
+  for (int m = 0; m < 5; m++)
+    for (int h = 0; h < 2; h++) {
+      if (tap2[m][h] < 0) continue;
+      for (int n = 0; n < 32; n++)
+        for (int kk = 0; kk < 16; kk++) img[OFF_W2 + m * 1024 + h * 512 + n * 16 + kk] = (uint8_t)w[1][n * 144 + tap2[m][h] * 16 + kk];
+    }
+  for (int tap = 0; tap < 9; tap++)
+    for (int h = 0; h < 2; h++)
+      for (int n = 0; n < 64; n++)
+        for (int kk = 0; kk < 16; kk++) img[OFF_W3 + tap * 2048 + h * 1024 + n * 16 + kk] = (uint8_t)w[2][n * 288 + tap * 32 + 16 * h + kk];
+  for (int tap = 0; tap < 9; tap++)
+    for (int cp = 0; cp < 2; cp++)
+      for (int h = 0; h < 2; h++)
+        for (int n = 0; n < 32; n++)
+          for (int kk = 0; kk < 16; kk++)
+            img[OFF_W4 + (tap * 2 + cp) * 1024 + h * 512 + n * 16 + kk] = (uint8_t)w[3][n * 576 + tap * 64 + 32 * cp + 16 * h + kk];
+  for (int m = 0; m < 3; m++)
+    for (int h = 0; h < 2; h++)
+      for (int n = 0; n < 10; n++)
+        for (int kk = 0; kk < 16; kk++) img[OFF_WD + m * 512 + h * 256 + n * 16 + kk] = (uint8_t)w[4][n * 96 + m * 32 + 16 * h + kk];
+  int32_t par[PAR_BYTES / 4] = {0};
+  const int seed_at[5] = {PAR_SEED1, PAR_SEED2, PAR_SEED3, PAR_SEED4, PAR_SEEDD}, cout[5] = {16, 32, 64, 32, 10};
+  for (int l = 0; l < 5; l++) {
+    for (int o = 0; o < cout[l]; o++) par[seed_at[l] + o] = (int32_t)((uint32_t)(int32_t)b[l][o] << ls[l]) + (1 << (rs[l] - 1));
+    par[PAR_RS + l] = rs[l];
+    par[PAR_HI + l] = (128 << rs[l]) - 1;
+  }
+  memcpy(img + OFF_PAR, par, PAR_BYTES);
+}
+
+}  // namespace k2
+}  // namespace edison

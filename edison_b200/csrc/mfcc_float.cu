@@ -569,6 +569,7 @@ static bool float_dev_ptr(const void *p) {
 
 template <typename R>
 static int clips_dev(const int16_t *d_pcm, size_t n_clips, size_t fpc, size_t stride, R *d_mfcc, int mode, void *stream) {
+  DeviceScope device_scope_;
   if ((n_clips && fpc) && (!d_pcm || !d_mfcc)) return ctx_fail(EDISON_E_ARG, "float MFCC: null pointer");
   ctx_lock();
   CtxView c;
@@ -580,6 +581,7 @@ static int clips_dev(const int16_t *d_pcm, size_t n_clips, size_t fpc, size_t st
 
 template <typename R>
 static int clips_any(const int16_t *pcm, size_t n_clips, size_t fpc, size_t stride, R *mfcc, int mode) {
+  DeviceScope device_scope_;
   const size_t n_frames = n_clips * fpc;
   if (n_frames && (!pcm || !mfcc)) return ctx_fail(EDISON_E_ARG, "float MFCC: null pointer");
   if (float_dev_ptr(pcm)) {
@@ -699,6 +701,7 @@ extern "C" {
 
 int edison_mfccf_create(int num_mfcc_features, int feature_offset, int frame_len, int mfcc_dec_bits, float preemph,
                         edison_mfccf **out) {
+  DeviceScope device_scope_;
   if (!out) return ctx_fail(EDISON_E_ARG, "edison_mfccf_create: null out");
   ctx_lock();
   CtxView c;
@@ -722,6 +725,7 @@ int edison_mfccf_create(int num_mfcc_features, int feature_offset, int frame_len
 }
 
 void edison_mfccf_delete(edison_mfccf *h) {
+  DeviceScope device_scope_;
   if (!h) return;
   cudaDeviceSynchronize();
   if (h->d_tables) cudaFree(h->d_tables);
@@ -732,6 +736,7 @@ int edison_mfccf_n_out(const edison_mfccf *h) { return h ? h->n_out : 0; }
 
 int edison_mfccf_compute_batch_dev(edison_mfccf *h, const int16_t *d_pcm, size_t n_frames, size_t hop_samples, int8_t *d_out,
                                    void *stream) {
+  DeviceScope device_scope_;
   if (!h || (n_frames && (!d_pcm || !d_out || !hop_samples))) return ctx_fail(EDISON_E_ARG, "edison_mfccf_compute_batch_dev: bad arguments");
   ctx_lock();
   CtxView c;
@@ -742,6 +747,7 @@ int edison_mfccf_compute_batch_dev(edison_mfccf *h, const int16_t *d_pcm, size_t
 }
 
 int edison_mfccf_compute_batch(edison_mfccf *h, const int16_t *pcm, size_t n_frames, size_t hop_samples, int8_t *out) {
+  DeviceScope device_scope_;
   if (!h || (n_frames && (!pcm || !out || !hop_samples))) return ctx_fail(EDISON_E_ARG, "edison_mfccf_compute_batch: bad arguments");
   if (float_dev_ptr(pcm)) {
     int rc = edison_mfccf_compute_batch_dev(h, pcm, n_frames, hop_samples, out, nullptr);

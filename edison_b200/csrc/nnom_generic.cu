@@ -426,6 +426,7 @@ using namespace edison;
 extern "C" {
 
 int edison_model_load(const char *blob_path, edison_model **out) {
+  DeviceScope device_scope_;
   if (!blob_path || !out) return ctx_fail(EDISON_E_ARG, "edison_model_load: null argument");
   ctx_lock();
   CtxView c;
@@ -472,6 +473,7 @@ int edison_model_load(const char *blob_path, edison_model **out) {
 }
 
 void edison_model_free(edison_model *m) {
+  DeviceScope device_scope_;
   if (!m) return;
   cudaDeviceSynchronize();
   void *bufs[] = {m->d_w, m->d_arena, m->d_in, m->d_lg, m->d_sm};
@@ -490,6 +492,7 @@ int edison_model_shape(const edison_model *m, int *in_h, int *in_w, int *in_c, i
 }
 
 int edison_model_infer(edison_model *m, const int8_t *in, size_t n, int8_t *logits, int8_t *softmax) {
+  DeviceScope device_scope_;
   if (!m || (n && !in)) return ctx_fail(EDISON_E_ARG, "edison_model_infer: null argument");
   if (!n) return EDISON_OK;
   ctx_lock();

@@ -27,8 +27,13 @@
 
 #include "edison_internal.h"
 #include "../../include/edison_b200.h"
+#include "k2_umma_plan.h"
+#include "nnom_blob.h"
 
 namespace edison {
+using k2::softmax_q7;
+using k2::ssat8;
+using k2::usat;
 
 constexpr int kInH = 31, kInW = 13;
 constexpr int kC1 = 16, kC2 = 32, kC3 = 64, kC4 = 32, kDenseIn = 96, kDenseOut = 10;
@@ -61,9 +66,6 @@ struct NetSmem {
   alignas(16) int8_t Y[kRegionY];
 };
 
-__device__ __forceinline__ int ssat8(int v) { return min(max(v, -128), 127); }
-__device__ __forceinline__ int usat(int v, int bits) { return min(max(v, 0), (1 << bits) - 1); }
-
 __device__ __forceinline__ void mma_s8(int (&d)[4], const uint32_t (&a)[4], uint2 b) {
   asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
@@ -79,43 +81,6 @@ template <int C> __device__ __forceinline__ int act_word(int P, int w) {
 
 // clamp(acc >> rs) to [0, 127]: SSAT8 followed by ReLU (nnom_activation.c:118-126)
 __device__ __forceinline__ int q7_relu(int acc, int rs) { return min(max(acc >> rs, 0), 127); }
-// arm_softmax_q7 (reference :217-254, SIMD :83-215) and local_softmax_q7 (nnom_local.c:948-1003)
-__device__ void softmax_q7(const int8_t *in, int8_t *out, int mode) {
-  constexpr int n = kDenseOut;
-  if (mode == EDISON_SOFTMAX_NNOM_LOCAL) {
-    int base = -257;
-    for (int i = 0; i < n; i++) base = max(base, (int)in[i]);
-    base -= 8;
-    int sum = 0;
-    for (int i = 0; i < n; i++)
-      if (in[i] > base) sum += 1 << usat(in[i] - base, 5);
-    const int ob = 0x100000 / sum;
-    for (int i = 0; i < n; i++) out[i] = in[i] > base ? (int8_t)ssat8(ob >> usat(13 + base - in[i], 5)) : (int8_t)0;
-    return;
-  }
-  int base = -128;
-  for (int i = 0; i < n; i++) base = max(base, (int)in[i]);
-  base -= 8;
-  const int nv = mode == EDISON_SOFTMAX_CMSIS_SIMD ? (n & ~3) : 0;  // handled 4 at a time with 8-bit wrap
-  int sum = 0;
-  for (int i = 0; i < n; i++) {
-    int d = in[i] - base;
-    if (i < nv) d = (int)(int8_t)(d & 0xff);  // __SSUB8 wraps (:127)
-    sum += 1 << usat(d, 3);
-  }
-  const int ob = (1 << 20) / sum;
-  for (int i = 0; i < n; i++) {
-    int d;
-    if (i < nv) {
-      const int t = (int)(int8_t)((13 - in[i]) & 0xff);                 // __SSUB8(pad, in) :177
-      d = (int)(int8_t)((t + (int)(int8_t)(base & 0xff)) & 0xff);       // __SADD8(in, baseV) :178
-    } else {
-      d = 13 + base - in[i];
-    }
-    out[i] = (int8_t)ssat8(ob >> usat(d, 5));
-  }
-}
-
 
 // ---- 3x3 valid convolution (+ ReLU, + optional 2x1 max pool) as an implicit GEMM -----------------------
 // in : HWC int8, pixel index P = clip * PIXS_IN + y * W_IN + x, layout act_word<C>
@@ -589,12 +554,24 @@ cudaError_t launch_nnom_q7_incremental(const NnomModel *model, const int8_t *win
 cudaError_t nnom_configure(void) {
   cudaError_t e = cudaFuncSetAttribute(nnom_q7_incr_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IncrSmem));
   if (e != cudaSuccess) return e;
-
-  return cudaFuncSetAttribute(nnom_q7_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NetSmem));
+  e = cudaFuncSetAttribute(nnom_q7_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NetSmem));
+  if (e != cudaSuccess) return e;
+  return nnom_umma_configure();
 }
 
+// weight image of the tcgen05 kernel (nnom_q7_umma.cu); one model per process, like the firmware
+static uint8_t *g_umma_image = nullptr;
+
 cudaError_t launch_nnom_q7(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax,
-                           int softmax_mode, int sm_count, cudaStream_t stream) {
+                           int softmax_mode, int sm_count, cudaStream_t stream, int *class_counts) {
+  (void)model;
+  if (!g_umma_image) return cudaErrorNotReady;
+  return launch_nnom_q7_umma(g_umma_image, net_in, n, logits, softmax, softmax_mode, class_counts, sm_count, stream);
+}
+
+// the round-1 mma.sync kernel: kept for tools/k2_time.py (A/B timing of the two tensor paths), not reachable from the C ABI
+cudaError_t launch_nnom_q7_legacy(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax,
+                                  int softmax_mode, int sm_count, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   const long long n_tiles = (n + kNC - 1) / kNC;
   long long ctas = n_tiles < (long long)sm_count * 2 ? n_tiles : (long long)sm_count * 2;
@@ -603,10 +580,8 @@ cudaError_t launch_nnom_q7(const NnomModel *model, const int8_t *net_in, long lo
   return cudaGetLastError();
 }
 
-// ---- blob loader (tools/convert_nnom_weights.py) -> fragment-ordered device model ---------------------
+// ---- blob loader (tools/convert_nnom_weights.py) -> device model ----------------------------------------------------
 namespace {
-struct HostLayer { uint32_t h[9]; const int8_t *w, *b; };
-
 // B[k][n] of one layer -> mma.m16n8k32 B fragments: lane (g = lane >> 2, t = lane & 3) holds
 // b0 = B[32 ks + 4t .. +3][8 nt + g], b1 = B[32 ks + 16 + 4t .. +3][8 nt + g]
 template <class F> void pack_frags(uint2 *dst, int ksteps, int ntiles, F weight) {
@@ -624,77 +599,57 @@ template <class F> void pack_frags(uint2 *dst, int ksteps, int ntiles, F weight)
 }  // namespace
 
 int nnom_load(const char *path, NnomModel **out_dev, int *in_scale, int *in_min, int *in_max, char *err, size_t errlen) {
-  FILE *fh = fopen(path, "rb");
-  if (!fh) { snprintf(err, errlen, "cannot open %s", path); return EDISON_E_DATA; }
-  fseek(fh, 0, SEEK_END);
-  long sz = ftell(fh);
-  fseek(fh, 0, SEEK_SET);
-  unsigned char *blob = (unsigned char *)malloc((size_t)sz + 1);
-  if (!blob) { fclose(fh); return EDISON_E_NOMEM; }
-  if (fread(blob, 1, (size_t)sz, fh) != (size_t)sz) { fclose(fh); free(blob); snprintf(err, errlen, "%s: short read", path); return EDISON_E_DATA; }
-  fclose(fh);
-  int rc = EDISON_OK;
-  NnomModel *M = nullptr;
+  KwsBlob blob;
+  int rc = read_kws_blob(path, blob, err, errlen);
+  if (rc) return rc;
+  const KwsLayer *L = blob.L;
+  *in_scale = blob.in_scale; *in_min = blob.in_min; *in_max = blob.in_max;
+  NnomModel *M = (NnomModel *)calloc(1, sizeof(NnomModel));
+  if (!M) return EDISON_E_NOMEM;
+  // fragments of the incremental (sliding-window) kernel
+  // conv1: k = ky * 8 + kx (zero outside the 5x5 window); weights [o][ky][kx]
+  pack_frags(&M->f1[0][0][0], 2, 2, [&](int k, int n) -> int8_t {
+    const int ky = k >> 3, kx = k & 7;
+    return (ky < 5 && kx < 5) ? L[0].w[(n * 5 + ky) * 5 + kx] : (int8_t)0;
+  });
+  // conv2..4: k = (ky * 3 + kx) * C + c == the reference's O,H,W,I order; zero beyond 9 C
+  pack_frags(&M->f2[0][0][0], 5, 4, [&](int k, int n) -> int8_t { return k < 144 ? L[1].w[n * 144 + k] : (int8_t)0; });
+  pack_frags(&M->f3[0][0][0], 9, 8, [&](int k, int n) -> int8_t { return L[2].w[n * 288 + k]; });
+  pack_frags(&M->f4[0][0][0], 18, 4, [&](int k, int n) -> int8_t { return L[3].w[n * 576 + k]; });
+  pack_frags(&M->fd[0][0][0], 3, 2, [&](int k, int n) -> int8_t { return n < kDenseOut ? L[4].w[n * kDenseIn + k] : (int8_t)0; });
+  int *seeds[5] = {M->seed1, M->seed2, M->seed3, M->seed4, M->seedd};
+  const int8_t *w[5], *b[5];
+  int rs[5], ls[5];
+  for (int i = 0; i < 5; i++) {
+    M->rs[i] = (int)L[i].h[5];
+    for (uint32_t o = 0; o < L[i].h[1]; o++)
+      seeds[i][o] = (int)((uint32_t)(int32_t)L[i].b[o] << L[i].h[6]) + (1 << (L[i].h[5] - 1));
+    w[i] = L[i].w; b[i] = L[i].b; rs[i] = (int)L[i].h[5]; ls[i] = (int)L[i].h[6];
+  }
+  NnomModel *d = nullptr;
+  uint8_t *image = nullptr;
   do {
-    if (sz < 16 || memcmp(blob, "EDNNQ7\0\0", 8)) { snprintf(err, errlen, "%s: bad header", path); rc = EDISON_E_DATA; break; }
-    uint32_t ver, nl;
-    memcpy(&ver, blob + 8, 4); memcpy(&nl, blob + 12, 4);
-    if (ver != 1) { snprintf(err, errlen, "%s: version %u", path, ver); rc = EDISON_E_DATA; break; }
-    // the graph this build has kernels for: kind, cout, kh, kw, cin, relu, pool
-    static const uint32_t expect[5][7] = {{1, kC1, 5, 5, 1, 1, 2}, {1, kC2, 3, 3, kC1, 1, 2}, {1, kC3, 3, 3, kC2, 1, 0},
-                                          {1, kC4, 3, 3, kC3, 1, 0}, {2, kDenseOut, 1, 1, kDenseIn, 0, 0}};
-    if (nl != 5) { snprintf(err, errlen, "%s: %u layers, this build runs the 5-layer kws_conv graph", path, nl); rc = EDISON_E_MODEL; break; }
-    HostLayer L[5];
-    const unsigned char *p = blob + 16, *end = blob + sz;
-    for (int i = 0; i < 5 && rc == EDISON_OK; i++) {
-      if (p + 36 > end) { snprintf(err, errlen, "%s: truncated", path); rc = EDISON_E_DATA; break; }
-      memcpy(L[i].h, p, 36); p += 36;
-      const uint32_t *h = L[i].h;
-      const uint32_t got[7] = {h[0], h[1], h[2], h[3], h[4], h[7], h[8]};
-      if (memcmp(got, expect[i], sizeof got)) { snprintf(err, errlen, "%s: layer %d is not the kws_conv layer this build implements", path, i); rc = EDISON_E_MODEL; break; }
-      if (h[5] < 1 || h[5] > 24 || h[6] > 16) { snprintf(err, errlen, "%s: layer %d shifts out of range", path, i); rc = EDISON_E_DATA; break; }
-      const size_t nw = (size_t)h[1] * h[2] * h[3] * h[4];
-      if (p + nw + h[1] > end) { snprintf(err, errlen, "%s: truncated", path); rc = EDISON_E_DATA; break; }
-      L[i].w = (const int8_t *)p; p += nw;
-      L[i].b = (const int8_t *)p; p += h[1];
-      p += (size_t)(-(p - blob)) & 3;
-    }
-    if (rc) break;
-    if (p + 24 > end) { snprintf(err, errlen, "%s: truncated trailer", path); rc = EDISON_E_DATA; break; }
-    int32_t tq[3]; uint32_t sh[3];
-    memcpy(tq, p, 12); memcpy(sh, p + 12, 12);
-    if (sh[0] != (uint32_t)kInH || sh[1] != (uint32_t)kInW || sh[2] != 1 || tq[0] == 0) { snprintf(err, errlen, "%s: input shape/scale unsupported", path); rc = EDISON_E_MODEL; break; }
-    *in_scale = tq[0]; *in_min = tq[1]; *in_max = tq[2];
-    M = (NnomModel *)calloc(1, sizeof(NnomModel));
-    if (!M) { rc = EDISON_E_NOMEM; break; }
-    // conv1: k = ky * 8 + kx (zero outside the 5x5 window); weights [o][ky][kx]
-    pack_frags(&M->f1[0][0][0], 2, 2, [&](int k, int n) -> int8_t {
-      const int ky = k >> 3, kx = k & 7;
-      return (ky < 5 && kx < 5) ? L[0].w[(n * 5 + ky) * 5 + kx] : (int8_t)0;
-    });
-    // conv2..4: k = (ky * 3 + kx) * C + c == the reference's O,H,W,I order; zero beyond 9 C
-    pack_frags(&M->f2[0][0][0], 5, 4, [&](int k, int n) -> int8_t { return k < 144 ? L[1].w[n * 144 + k] : (int8_t)0; });
-    pack_frags(&M->f3[0][0][0], 9, 8, [&](int k, int n) -> int8_t { return L[2].w[n * 288 + k]; });
-    pack_frags(&M->f4[0][0][0], 18, 4, [&](int k, int n) -> int8_t { return L[3].w[n * 576 + k]; });
-    pack_frags(&M->fd[0][0][0], 3, 2, [&](int k, int n) -> int8_t { return n < kDenseOut ? L[4].w[n * kDenseIn + k] : (int8_t)0; });
-    int *seeds[5] = {M->seed1, M->seed2, M->seed3, M->seed4, M->seedd};
-    for (int i = 0; i < 5; i++) {
-      M->rs[i] = (int)L[i].h[5];
-      for (uint32_t o = 0; o < L[i].h[1]; o++)
-        seeds[i][o] = (int)((uint32_t)(int32_t)L[i].b[o] << L[i].h[6]) + (1 << (L[i].h[5] - 1));
-    }
-    NnomModel *d = nullptr;
     if (cudaMalloc(&d, sizeof(NnomModel)) != cudaSuccess) { snprintf(err, errlen, "cudaMalloc(model)"); rc = EDISON_E_CUDA; break; }
-    if (cudaMemcpy(d, M, sizeof(NnomModel), cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(d); snprintf(err, errlen, "cudaMemcpy(model)"); rc = EDISON_E_CUDA; break; }
-    *out_dev = d;
+    if (cudaMemcpy(d, M, sizeof(NnomModel), cudaMemcpyHostToDevice) != cudaSuccess) { snprintf(err, errlen, "cudaMemcpy(model)"); rc = EDISON_E_CUDA; break; }
+    rc = nnom_umma_upload(w, b, rs, ls, &image);
+    if (rc) { snprintf(err, errlen, "upload of the K2 weight image failed"); break; }
   } while (0);
   free(M);
-  free(blob);
-  return rc;
+  if (rc) {
+    cudaGetLastError();
+    if (d) cudaFree(d);
+    return rc;
+  }
+  if (g_umma_image) cudaFree(g_umma_image);
+  g_umma_image = image;
+  *out_dev = d;
+  return EDISON_OK;
 }
 
 void nnom_free(NnomModel *m) {
   if (m) cudaFree(m);
+  if (g_umma_image) cudaFree(g_umma_image);
+  g_umma_image = nullptr;
 }
 
 }  // namespace edison

@@ -1,0 +1,288 @@
+// nnom_q7_umma.cu -- K2 on the Blackwell tensor path: the int8 NNoM keyword-spotting net
+// (firmware/src/ai/nnom/kws_nnom/weights.h:138-161; model_run, firmware/src/ai/nnom/src/core/nnom.c:996-1041) as
+// tcgen05.mma.kind::i8 implicit GEMMs with accumulators in TMEM.  The plan -- shared-memory layout, MMA list, unit order,
+// epilogues -- is k2_umma_plan.h (also run on the host by tests/host_emu/emu_k2.cpp); this file is its executor:
+//
+//   * persistent grid, one CTA per SM, 32 clips per batch, activations of a batch never leave shared memory;
+//   * warp 16, one thread: waits for the TMEM slot of the next unit (mbarrier empty[slot]), issues the unit's MMAs from
+//     shared-memory descriptors (operands are never copied: a filter tap is a shifted start address), commits them to
+//     mbarrier full[slot]; it also starts the bulk copies (cp.async.bulk -> SASS UBLKCP) of the weight image and of each
+//     batch's 32 x 403 input bytes;
+//   * warps 0..15: wait on full[slot], read their lane quarter of the accumulators with tcgen05.ld (lane = clip), run the
+//     integer epilogue of arm_convolve_HWC_q7_fast_nonsquare.c / nnom_local.c (bias seed, >> shift, SSAT8, ReLU, 2x1 max
+//     pool), store 16 channels as one 16-byte word in the next layer's operand layout, make the stores visible to the
+//     tensor core's asynchronous proxy, and release the slot (mbarrier empty[slot]);
+//   * the unit order interleaves the head of batch b with the tail of batch b - 1 so that no unit depends on the unit
+//     right before it: the only waits are the two-deep TMEM slot ring.
+// There is no CPU path and no legacy mma.sync path behind this entry point.
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "edison_internal.h"
+#include "../../include/edison_b200.h"
+#include "k2_umma_plan.h"
+
+namespace edison {
+using namespace k2;
+
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// cute::UMMA::SmemDescriptor, no swizzle, K-major: start >> 4 [0,14), LBO >> 4 [16,30), SBO >> 4 = 8 [32,46), version 1 [46,48)
+__device__ __forceinline__ uint64_t make_desc(uint32_t addr, uint32_t lbo) {
+  return (uint64_t)(((addr >> 4) & 0x3fffu) | (((lbo >> 4) & 0x3fffu) << 16)) | ((uint64_t)(8u | (1u << 14)) << 32);
+}
+// cute::UMMA::InstrDescriptor for kind::i8: D = S32 (2 << 4), A = B = signed 8 bit (1 << 7, 1 << 10), K-major, N >> 3 at 17, M >> 4 at 24
+__host__ __device__ constexpr uint32_t make_idesc_i8(uint32_t n) { return (2u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24); }
+
+__device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n"
+               :: "r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+               "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}\n"
+               :: "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}\n" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}\n" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+struct DevCtx {
+  uint8_t *smem;
+  uint32_t taddr;   // TMEM address of this thread's lane quarter at the unit's slot
+  int lane, q, g;
+  long long clip0;
+  int nclips;
+  int8_t *logits, *softmax;
+  int softmax_mode;
+  int *hist;        // shared-memory class histogram
+  __device__ __forceinline__ void ld16(uint32_t col, uint32_t (&v)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+                   "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(taddr + col));
+  }
+  __device__ __forceinline__ void ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+  __device__ __forceinline__ void st16(uint32_t off, Vec16 v) { *reinterpret_cast<uint4 *>(smem + off) = make_uint4(v.x, v.y, v.z, v.w); }
+  __device__ __forceinline__ int par(int i) const { return reinterpret_cast<const int *>(smem + OFF_PAR)[i]; }
+  __device__ __forceinline__ Int4 par4(int i) const {
+    const int4 v = *reinterpret_cast<const int4 *>(smem + OFF_PAR + 4 * i);
+    return Int4{v.x, v.y, v.z, v.w};
+  }
+  __device__ __forceinline__ void count(int cls) { atomicAdd(&hist[cls], 1); }
+};
+
+struct Job {
+  const uint8_t *image;
+  const int8_t *net_in;
+  long long n, nb;      // clips, batches
+  int nbc;              // batches of this CTA: blockIdx.x + k * gridDim.x, k < nbc
+  bool aligned;         // net_in is 16-byte aligned: full batches come in by bulk copy
+  __device__ __forceinline__ long long batch(int k) const { return (long long)blockIdx.x + (long long)k * gridDim.x; }
+  __device__ __forceinline__ bool bulk(int k) const { return aligned && (batch(k) + 1) * NC <= n; }
+};
+
+// input layout step for this CTA's k-th batch: raw [clip][403] -> c0[row & 1][row >> 1][clip][16]; tid in 0..511
+__device__ __forceinline__ void transpose_in(uint8_t *smem, const Job &J, int k, uint32_t raw_bar, int tid) {
+  const long long clip0 = J.batch(k) * NC;
+  const int nclips = (int)min((long long)NC, J.n - clip0);
+  const bool bulk = J.bulk(k);
+  if (bulk) mbar_wait(raw_bar, (uint32_t)k & 1u);
+  const int clip = tid & 31;
+#pragma unroll
+  for (int round = 0; round < 2; round++) {
+    const int row = (tid >> 5) + 16 * round;
+    if (row < kInRowsUsed) {
+      const uint32_t a = (uint32_t)clip * kNetIn + (uint32_t)row * 13;
+      uint32_t w[4];
+      Vec16 v;
+      if (bulk) {
+        const uint32_t *wp = reinterpret_cast<const uint32_t *>(smem + OFF_RAW) + (a >> 2);
+#pragma unroll
+        for (int j = 0; j < 4; j++) w[j] = wp[j];
+        v = input_chunk(w, a);
+      } else {   // partial last batch or unaligned caller buffer: byte loads straight from HBM
+        w[0] = w[1] = w[2] = w[3] = 0;
+        if (clip < nclips) {
+          const uint8_t *src = reinterpret_cast<const uint8_t *>(J.net_in) + (clip0 + clip) * kNetIn + row * 13;
+#pragma unroll
+          for (int j = 0; j < 13; j++) w[j >> 2] |= (uint32_t)src[j] << (8 * (j & 3));
+        }
+        v = Vec16{w[0], w[1], w[2], w[3]};
+      }
+      *reinterpret_cast<uint4 *>(smem + c0_offset(row, clip)) = make_uint4(v.x, v.y, v.z, v.w);
+    }
+  }
+}
+
+struct Bars { uint32_t full[2], empty[2], raw, wts; };
+
+template <int POS> __device__ __forceinline__ void issue_unit(const Job &J, const Bars &B, uint32_t sbase, uint32_t tmem, int it) {
+  constexpr Unit u = kSched[POS];
+  const bool valid = u.lag ? it > 0 : it < J.nbc;
+  mbar_wait(B.empty[POS & 1], (uint32_t)(((POS >> 1) & 1) ^ 1));   // the epilogue of this slot's previous unit is done
+  tc_fence_after();
+  if (POS == kPosNextRaw && it + 2 < J.nbc && J.bulk(it + 2)) {    // raw was consumed by the transpose of unit kPosTranspose
+    mbar_expect_tx(B.raw, NC * kNetIn);
+    bulk_g2s(sbase + OFF_RAW, J.net_in + J.batch(it + 2) * NC * kNetIn, NC * kNetIn, B.raw);
+  }
+  if (valid)
+    for_each_mma<POS>([&](const MmaOp &op) {
+      mma_i8(tmem + (POS & 1) * 256 + op.col, make_desc(sbase + op.a_off, op.a_lbo), make_desc(sbase + op.b_off, op.b_lbo), make_idesc_i8(op.n),
+             op.acc);
+    });
+  umma_commit(B.full[POS & 1]);
+}
+
+template <int POS> __device__ __forceinline__ void drain_unit(const Job &J, const Bars &B, DevCtx &c, uint32_t tmem_q, int it, int tid) {
+  constexpr Unit u = kSched[POS];
+  const bool valid = u.lag ? it > 0 : it < J.nbc;
+  mbar_wait(B.full[POS & 1], (uint32_t)((POS >> 1) & 1));          // the unit's MMAs (and every earlier one) have completed
+  tc_fence_after();
+  if (valid) {
+    c.taddr = tmem_q + (POS & 1) * 256;
+    if (u.kind == DN) {
+      c.clip0 = J.batch(it - 1) * NC;
+      c.nclips = (int)min((long long)NC, J.n - c.clip0);
+    }
+    epilogue<POS>(c);
+  }
+  if (POS == kPosTranspose && it + 1 < J.nbc) transpose_in(c.smem, J, it + 1, B.raw, tid);
+  fence_async_smem();   // this thread's shared-memory stores -> visible to the MMAs that will read them
+  tc_fence_before();
+  mbar_arrive(B.empty[POS & 1]);
+}
+
+template <int POS> struct IssueAll {
+  static __device__ __forceinline__ void go(const Job &J, const Bars &B, uint32_t sbase, uint32_t tmem, int it) {
+    issue_unit<POS>(J, B, sbase, tmem, it);
+    if constexpr (POS + 1 < kUnits) IssueAll<POS + 1>::go(J, B, sbase, tmem, it);
+  }
+};
+template <int POS> struct DrainAll {
+  static __device__ __forceinline__ void go(const Job &J, const Bars &B, DevCtx &c, uint32_t tmem_q, int it, int tid) {
+    drain_unit<POS>(J, B, c, tmem_q, it, tid);
+    if constexpr (POS + 1 < kUnits) DrainAll<POS + 1>::go(J, B, c, tmem_q, it, tid);
+  }
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+nnom_q7_umma_kernel(const uint8_t *image, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax, int softmax_mode,
+                    int *class_counts) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t sbase = smem_u32(smem);
+  Bars B;
+  B.full[0] = sbase + OFF_BAR; B.full[1] = sbase + OFF_BAR + 8; B.empty[0] = sbase + OFF_BAR + 16; B.empty[1] = sbase + OFF_BAR + 24;
+  B.raw = sbase + OFF_BAR + 32; B.wts = sbase + OFF_BAR + 40;
+  volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(smem + OFF_BAR + 48);
+  int *hist = reinterpret_cast<int *>(smem + OFF_BAR + 64);
+  Job J;
+  J.image = image; J.net_in = net_in; J.n = n; J.nb = (n + NC - 1) / NC;
+  J.nbc = (long long)blockIdx.x < J.nb ? (int)((J.nb - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+  J.aligned = (reinterpret_cast<uintptr_t>(net_in) & 15) == 0;
+
+  if (warp == kEpiWarps) {
+    if (lane == 0) {
+      mbar_init(B.full[0], 1); mbar_init(B.full[1], 1);
+      mbar_init(B.empty[0], kEpiWarps * 32); mbar_init(B.empty[1], kEpiWarps * 32);
+      mbar_init(B.raw, 1); mbar_init(B.wts, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      mbar_expect_tx(B.wts, IMAGE_BYTES);
+      bulk_g2s(sbase, image, IMAGE_BYTES, B.wts);
+      if (J.nbc > 0 && J.bulk(0)) {
+        mbar_expect_tx(B.raw, NC * kNetIn);
+        bulk_g2s(sbase + OFF_RAW, net_in + J.batch(0) * NC * kNetIn, NC * kNetIn, B.raw);
+      }
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(sbase + OFF_BAR + 48), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (tid < 10) hist[tid] = 0;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  mbar_wait(B.wts, 0);                                       // weights and parameters are in shared memory
+  if (warp < kEpiWarps && J.nbc > 0) transpose_in(smem, J, 0, B.raw, tid);
+  fence_async_smem();
+  __syncthreads();
+
+  if (warp == kEpiWarps) {
+    if (lane == 0 && J.nbc > 0) {
+      if (J.nbc > 1 && J.bulk(1)) {
+        mbar_expect_tx(B.raw, NC * kNetIn);
+        bulk_g2s(sbase + OFF_RAW, net_in + J.batch(1) * NC * kNetIn, NC * kNetIn, B.raw);
+      }
+      for (int it = 0; it <= J.nbc; it++) IssueAll<0>::go(J, B, sbase, tmem, it);
+    }
+  } else if (J.nbc > 0) {
+    DevCtx c;
+    c.smem = smem; c.lane = lane; c.q = warp & 3; c.g = warp >> 2;
+    c.clip0 = 0; c.nclips = 0; c.logits = logits; c.softmax = softmax; c.softmax_mode = softmax_mode; c.hist = hist;
+    const uint32_t tmem_q = tmem + ((uint32_t)(c.q * 32) << 16);
+    for (int it = 0; it <= J.nbc; it++) DrainAll<0>::go(J, B, c, tmem_q, it, tid);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kEpiWarps)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(512) : "memory");
+  if (class_counts && tid < 10 && hist[tid]) atomicAdd(&class_counts[tid], hist[tid]);
+}
+
+}  // namespace
+
+// ---- host side -----------------------------------------------------------------------------------------------------------
+cudaError_t nnom_umma_configure(void) {
+  return cudaFuncSetAttribute(nnom_q7_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+}
+
+// builds the weight image of k2_umma_plan.h from the five layers and uploads it; *out_image is a device pointer
+int nnom_umma_upload(const int8_t *const w[5], const int8_t *const b[5], const int rs[5], const int ls[5], uint8_t **out_image) {
+  uint8_t *host = (uint8_t *)malloc(IMAGE_BYTES);
+  if (!host) return EDISON_E_NOMEM;
+  build_image(host, w, b, rs, ls);
+  uint8_t *d = nullptr;
+  cudaError_t e = cudaMalloc(&d, IMAGE_BYTES);
+  if (e == cudaSuccess) e = cudaMemcpy(d, host, IMAGE_BYTES, cudaMemcpyHostToDevice);
+  free(host);
+  if (e != cudaSuccess) {
+    if (d) cudaFree(d);
+    return EDISON_E_CUDA;
+  }
+  *out_image = d;
+  return EDISON_OK;
+}
+
+cudaError_t launch_nnom_q7_umma(const uint8_t *image, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax, int softmax_mode,
+                                int *class_counts, int sm_count, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  const long long nb = (n + NC - 1) / NC;
+  const unsigned ctas = (unsigned)(nb < (long long)sm_count ? nb : (long long)sm_count);
+  nnom_q7_umma_kernel<<<ctas, kThreads, SMEM_BYTES, stream>>>(image, net_in, n, logits, softmax, softmax_mode, class_counts);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace edison

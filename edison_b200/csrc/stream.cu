@@ -120,6 +120,7 @@ using namespace edison;
 extern "C" {
 
 int edison_streams_open(size_t n_streams, edison_streams **out) {
+  DeviceScope device_scope_;
   if (!out || !n_streams) return ctx_fail(EDISON_E_ARG, "edison_streams_open: bad arguments");
   ctx_lock();
   CtxView c;
@@ -152,6 +153,7 @@ int edison_streams_open(size_t n_streams, edison_streams **out) {
 }
 
 void edison_streams_close(edison_streams *s) {
+  DeviceScope device_scope_;
   if (!s) return;
   cudaDeviceSynchronize();
   void *bufs[] = {s->d_window, s->d_rows, s->d_softmax, s->d_filt, s->d_detect, s->d_pcm, s->d_incr};
@@ -171,6 +173,7 @@ int edison_streams_set_incremental(edison_streams *s, int on) {
 
 int edison_streams_push_hop_dev(edison_streams *s, const int16_t *d_hop_pcm, int8_t *d_softmax, float *d_filt,
                                 int32_t *d_detect, void *stream) {
+  DeviceScope device_scope_;
   if (!s || !d_hop_pcm) return ctx_fail(EDISON_E_ARG, "edison_streams_push_hop_dev: null pointer");
   ctx_lock();
   CtxView c;
@@ -181,6 +184,7 @@ int edison_streams_push_hop_dev(edison_streams *s, const int16_t *d_hop_pcm, int
 }
 
 int edison_streams_push_hop(edison_streams *s, const int16_t *hop_pcm, int8_t *softmax, float *filt, int32_t *detect) {
+  DeviceScope device_scope_;
   if (!s || !hop_pcm) return ctx_fail(EDISON_E_ARG, "edison_streams_push_hop: null pointer");
   ctx_lock();
   CtxView c;
@@ -204,6 +208,7 @@ int edison_streams_push_hop(edison_streams *s, const int16_t *hop_pcm, int8_t *s
 }
 
 int edison_streams_window(edison_streams *s, size_t stream_index, int8_t *window403) {
+  DeviceScope device_scope_;
   if (!s || !window403 || stream_index >= s->n) return ctx_fail(EDISON_E_ARG, "edison_streams_window: bad arguments");
   cudaError_t e = cudaDeviceSynchronize();
   if (e == cudaSuccess) e = cudaMemcpy(window403, s->d_window + stream_index * EDISON_NET_IN, EDISON_NET_IN, cudaMemcpyDeviceToHost);

@@ -47,14 +47,20 @@ extern "C" {
 typedef struct edison_cfg {
   int device;             /* CUDA device ordinal; -1 = keep the current device                   */
   const char *data_dir;   /* holds mel_q15.bin and kws_nnom_q7.bin; NULL = $EDISON_B200_DATA,
-                             else <directory of the .so>/../data                                */
-  int softmax_mode;       /* EDISON_SOFTMAX_*                                                    */
+                             else <directory of the .so>/data                                */
+  int softmax_mode;       /* EDISON_SOFTMAX_*; edison_init(NULL) selects EDISON_SOFTMAX_CMSIS_SIMD,
+                             the firmware build's variant                                        */
   size_t chunk_clips;     /* host-pointer calls are pipelined in chunks of this many clips
                              (0 = default 8192)                                                  */
 } edison_cfg;
 
 /* ---- section 0: library lifetime -------------------------------------------------------------- */
-int edison_init(const edison_cfg *cfg);          /* idempotent per process; cfg may be NULL     */
+/* One context per process, bound to one device.  cfg may be NULL (current device, default data directory, the firmware
+ * build's softmax).  A second call returns EDISON_OK when it asks for what is already there and EDISON_E_ARG when it asks
+ * for another device, softmax mode or data directory (edison_shutdown() first).  Every entry point makes the bound device
+ * current for the calling thread for the duration of the call, so calls from other threads or after cudaSetDevice are safe;
+ * a call's non-NULL data pointers must all be host pointers or all be device pointers (EDISON_E_ARG otherwise). */
+int edison_init(const edison_cfg *cfg);
 void edison_shutdown(void);
 const char *edison_last_error(void);             /* text of the last failure in this thread     */
 int edison_set_softmax_mode(int mode);
@@ -183,6 +189,13 @@ int edison_infer_q7_batch_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits
                               void *stream);
 int edison_kws_batch_dev(const int16_t *d_pcm, size_t n_clips, size_t clip_stride_samples,
                          int8_t *d_logits, int8_t *d_softmax, int8_t *d_net_in, void *stream);
+/* as the two above, plus a class histogram accumulated by K2's dense epilogue: d_class_counts[10] (int32, device) gets
+ * += the number of clips whose FIRST maximum logit is class c.  The caller zeroes it.  Any of d_logits / d_softmax may be
+ * NULL (counts only).  This is what a sharded job reduces across GPUs after its last batch. */
+int edison_kws_counts_dev(const int16_t *d_pcm, size_t n_clips, size_t clip_stride_samples, int8_t *d_logits,
+                          int8_t *d_softmax, int8_t *d_net_in, int32_t *d_class_counts, void *stream);
+int edison_infer_q7_counts_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax,
+                               int32_t *d_class_counts, void *stream);
 int edison_sync(void *stream);
 
 /* ---- section 3b: continuous streaming (appMicMfccInfereContinuous, firmware/src/app.c:288-394, and its ISR
@@ -215,6 +228,8 @@ int edison_debug_sqrt_q31(const int32_t *in, size_t n, int32_t *out);
  * exact Newton path on the device, and a 64-bit checksum of the exact results */
 int edison_debug_mag_sweep(uint32_t lo, uint32_t hi, unsigned long long *mismatches,
                            unsigned long long *checksum);
+/* the round-1 mma.sync build of K2, kept only so that tools/k2_time.py can time the two tensor paths side by side */
+int edison_debug_infer_q7_legacy_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, void *stream);
 
 #ifdef __cplusplus
 }

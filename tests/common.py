@@ -15,7 +15,8 @@ def _p(a):
 
 
 class Oracle:
-    """oracle/libedison_oracle.so (CPU restatement, pinned against oracle/_ref in test_oracle_vs_ref.py)"""
+    """oracle/libedison_oracle.so (CPU restatement, pinned against oracle/_ref in tests/test_oracle_cpu.py).
+    Default softmax mode = 1, the firmware build's SIMD branch of arm_softmax_q7, like edison_init(NULL)."""
 
     def __init__(self):
         self.L = ctypes.CDLL(os.path.join(ROOT, "oracle", "libedison_oracle.so"))
@@ -37,7 +38,7 @@ class Oracle:
             self.L.eo_net_input_row(_p(mfcc[i]), _p(out[i]))
         return out
 
-    def forward(self, net_in, mode=0):
+    def forward(self, net_in, mode=1):
         net_in = np.ascontiguousarray(net_in, dtype=np.int8).reshape(-1, 403)
         n = net_in.shape[0]
         lg = np.zeros((n, 10), dtype=np.int8)
@@ -45,7 +46,7 @@ class Oracle:
         assert self.L.eo_nnom_forward_batch(_p(net_in), ctypes.c_size_t(n), _p(lg), _p(sm), ctypes.c_int(mode)) == 0
         return lg, sm
 
-    def kws(self, pcm, n_clips, stride=31 * FRAME, mode=0):
+    def kws(self, pcm, n_clips, stride=31 * FRAME, mode=1):
         pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
         lg = np.zeros((n_clips, 10), dtype=np.int8)
         sm = np.zeros((n_clips, 10), dtype=np.int8)

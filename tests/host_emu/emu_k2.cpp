@@ -1,0 +1,142 @@
+// emu_k2.cpp -- host emulation of the K2 tcgen05 plan (TEST INFRASTRUCTURE).
+//
+// Runs edison_b200/csrc/k2_umma_plan.h -- the same MMA list, the same epilogue templates, the same weight image and the same
+// unit order as the CUDA kernel (nnom_q7_umma.cu) -- on a byte array standing in for shared memory and an int32 array
+// standing in for TMEM.  An MMA is emulated with the descriptor addressing that tools/ubench/umma_probe.cu verified on a
+// B200 (A[m][k] = smem[start + (m / 8) * 128 + (m % 8) * 16 + (k / 16) * LBO + k % 16]).  `eager` moves every unit's MMAs in
+// front of the previous unit's epilogue, the other extreme of what the hardware's asynchrony allows, so that a
+// write-after-read hazard between an epilogue and MMAs already in flight would show as a mismatch in one of the two orders.
+// It exists to check index arithmetic against the oracle in a container without a GPU; it is not part of
+// libedison_b200.so and never produces results: the -m gpu parity tests run the real kernel.
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "k2_umma_plan.h"
+#include "nnom_blob.h"
+
+using namespace edison;
+using namespace edison::k2;
+
+namespace {
+
+struct Emu {
+  std::vector<uint8_t> smem;
+  std::vector<int32_t> tmem;   // [128 lanes][512 columns]
+  Emu() : smem(SMEM_BYTES + 4096, 0xA5), tmem(128 * 512, 0x5a5a5a5a) {}
+
+  void mma(const MmaOp &op, int slot) {
+    for (int m = 0; m < 128; m++)
+      for (uint32_t n = 0; n < op.n; n++) {
+        int32_t &d = tmem[m * 512 + slot * 256 + op.col + n];
+        int32_t s = op.acc ? d : 0;
+        for (int k = 0; k < 32; k++) {
+          const uint32_t aa = op.a_off + (m / 8) * 128 + (m % 8) * 16 + (k / 16) * op.a_lbo + (k % 16);
+          const uint32_t ba = op.b_off + (n / 8) * 128 + (n % 8) * 16 + (k / 16) * op.b_lbo + (k % 16);
+          s += (int)(int8_t)smem[aa] * (int)(int8_t)smem[ba];
+        }
+        d = s;
+      }
+  }
+};
+
+struct Ctx {
+  Emu *e;
+  int slot, lane, q, g;
+  long long clip0;
+  int nclips;
+  int8_t *logits, *softmax;
+  int softmax_mode;
+  long long *hist;
+  void ld16(uint32_t col, uint32_t (&v)[16]) {
+    for (int j = 0; j < 16; j++) v[j] = (uint32_t)e->tmem[(q * 32 + lane) * 512 + slot * 256 + col + j];
+  }
+  void ld_wait() {}
+  void st16(uint32_t off, Vec16 v) { memcpy(&e->smem[off], &v, 16); }
+  int par(int i) { int32_t v; memcpy(&v, &e->smem[OFF_PAR + 4 * i], 4); return v; }
+  Int4 par4(int i) { Int4 v; memcpy(&v, &e->smem[OFF_PAR + 4 * i], 16); return v; }
+  void count(int cls) { if (hist) hist[cls]++; }
+};
+
+void transpose_in(Emu &E, const int8_t *net_in, long long n, long long batch) {
+  const long long clip0 = batch * NC;
+  const int nclips = (int)((n - clip0) < NC ? (n - clip0) : NC);
+  memset(&E.smem[OFF_RAW], 0x77, RAW_BYTES);
+  memcpy(&E.smem[OFF_RAW], net_in + clip0 * kNetIn, (size_t)nclips * kNetIn);
+  for (int row = 0; row < kInRowsUsed; row++)
+    for (int clip = 0; clip < NC; clip++) {
+      const uint32_t a = (uint32_t)clip * kNetIn + (uint32_t)row * 13;
+      uint32_t w[4];
+      memcpy(w, &E.smem[OFF_RAW + (a & ~3u)], 16);
+      const Vec16 v = input_chunk(w, a);
+      memcpy(&E.smem[c0_offset(row, clip)], &v, 16);
+    }
+}
+
+template <int POS> void run_mma(Emu &E, bool head, bool tail) {
+  constexpr Unit u = kSched[POS];
+  if (!(u.lag ? tail : head)) return;
+  for_each_mma<POS>([&](const MmaOp &op) { E.mma(op, POS & 1); });
+}
+
+template <int POS> void run_epi(Emu &E, bool head, bool tail, const int8_t *net_in, long long n, long long batch_of_it, long long next_batch,
+                                int8_t *logits, int8_t *softmax, int mode, long long *hist) {
+  constexpr Unit u = kSched[POS];
+  if (u.lag ? tail : head) {
+    for (int w = 0; w < kEpiWarps; w++)
+      for (int lane = 0; lane < 32; lane++) {
+        Ctx c;
+        c.e = &E; c.slot = POS & 1; c.lane = lane; c.q = w & 3; c.g = w >> 2;
+        const long long b = u.lag ? batch_of_it - 1 : batch_of_it;   // single-CTA emulation: consecutive batches
+        c.clip0 = b * NC;
+        c.nclips = (int)((n - c.clip0) < NC ? (n - c.clip0) : NC);
+        c.logits = logits; c.softmax = softmax; c.softmax_mode = mode; c.hist = hist;
+        epilogue<POS>(c);
+      }
+  }
+  if (POS == kPosTranspose && next_batch >= 0) transpose_in(E, net_in, n, next_batch);
+}
+
+template <int POS> struct Runner {
+  static void go(Emu &E, bool eager, bool head, bool tail, const int8_t *net_in, long long n, long long b, long long nb, int8_t *logits,
+                 int8_t *softmax, int mode, long long *hist) {
+    // lazy: MMA(p) epi(p);  eager: MMA(p + 1) is issued before epi(p) (it only had to wait for epi(p - 1))
+    if (!eager) run_mma<POS>(E, head, tail);
+    else if (POS == 0) { run_mma<0>(E, head, tail); run_mma<1>(E, head, tail); }
+    else if (POS + 1 < kUnits) run_mma<(POS + 1 < kUnits ? POS + 1 : 0)>(E, head, tail);
+    run_epi<POS>(E, head, tail, net_in, n, b, head && b + 1 < nb ? b + 1 : -1, logits, softmax, mode, hist);
+    if constexpr (POS + 1 < kUnits) Runner<POS + 1>::go(E, eager, head, tail, net_in, n, b, nb, logits, softmax, mode, hist);
+  }
+};
+
+}  // namespace
+
+// net_in [n][403] -> logits [n][10], softmax [n][10], hist [10] (any may be null); returns 0 or a negative code
+extern "C" int emu_k2_run(const char *blob_path, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax, int mode, long long *hist,
+                          int eager) {
+  KwsBlob blob;
+  char err[256] = "";
+  int r = read_kws_blob(blob_path, blob, err, sizeof err);
+  if (r) { fprintf(stderr, "emu_k2_run: %s\n", err); return r; }
+  const int8_t *w[5], *b[5];
+  int rs[5], ls[5];
+  for (int i = 0; i < 5; i++) { w[i] = blob.L[i].w; b[i] = blob.L[i].b; rs[i] = (int)blob.L[i].h[5]; ls[i] = (int)blob.L[i].h[6]; }
+  Emu E;
+  build_image(E.smem.data(), w, b, rs, ls);
+  if (hist) memset(hist, 0, 10 * sizeof(long long));
+  const long long nb = (n + NC - 1) / NC;
+  if (nb == 0) return 0;
+  transpose_in(E, net_in, n, 0);
+  for (long long it = 0; it <= nb; it++) {
+    const bool head = it < nb, tail = it > 0;
+    // in the eager order the first unit of the next iteration was already issued with the last epilogue of this one;
+    // the emulation restarts each iteration (the slot discipline makes iterations independent at this boundary)
+    Runner<0>::go(E, eager != 0, head, tail, net_in, n, it, nb, logits, softmax, mode, hist);
+  }
+  return 0;
+}
+
+extern "C" unsigned emu_k2_image_bytes(void) { return IMAGE_BYTES; }
+extern "C" unsigned emu_k2_smem_bytes(void) { return SMEM_BYTES; }

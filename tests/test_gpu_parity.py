@@ -91,7 +91,7 @@ def test_infer_q7_vs_oracle(edison, oracle, mode):
     try:
         lg, sm = edison.infer_q7_batch(x)
     finally:
-        edison.set_softmax_mode(0)
+        edison.set_softmax_mode(edison.SOFTMAX_CMSIS_SIMD)
     wl, ws = oracle.forward(x, mode)
     assert (lg == wl).all()
     assert (sm == ws).all()

@@ -8,7 +8,7 @@ from common import synth_frames
 pytestmark = pytest.mark.gpu
 
 
-def simulate(oracle, pcm_hops, mode=0):
+def simulate(oracle, pcm_hops, mode=1):
     """pcm_hops: int16 [hops, n, 1024].  Returns per hop (softmax, filt, detect) as the firmware would compute them."""
     hops, n, _ = pcm_hops.shape
     window = np.zeros((n, 31, 13), dtype=np.int8)

@@ -70,7 +70,7 @@ def test_gpu_generic_vs_reference_runtime(edison):
             assert m.in_shape == (63, 12, 1) and m.n_out == 35
             lg, sm = m.infer(g["x"])
     finally:
-        edison.set_softmax_mode(edison.SOFTMAX_CMSIS_REF)
+        edison.set_softmax_mode(edison.SOFTMAX_CMSIS_SIMD)
     assert np.array_equal(lg, g["logits"])
     assert np.array_equal(sm, g["softmax_local"])
 
@@ -94,7 +94,7 @@ def test_gpu_generic_random_models_vs_oracle(edison, oracle, tmp_path, case):
             with edison.Model(blob) as m:
                 lg, sm = m.infer(x)
         finally:
-            edison.set_softmax_mode(0)
+            edison.set_softmax_mode(edison.SOFTMAX_CMSIS_SIMD)
         assert np.array_equal(lg, want_lg), "logits, mode %d" % mode
         assert np.array_equal(sm, want_sm), "softmax, mode %d" % mode
     assert np.unique(want_lg).size > 8

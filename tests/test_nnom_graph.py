@@ -179,7 +179,7 @@ def test_gpu_graph_vs_reference_runtime(edison, key):
             assert (m.in_shape, m.n_out) == MODELS[key]
             lg, sm = m.infer(g[key + "_x"])
     finally:
-        edison.set_softmax_mode(edison.SOFTMAX_CMSIS_REF)
+        edison.set_softmax_mode(edison.SOFTMAX_CMSIS_SIMD)
     assert np.array_equal(lg, g[key + "_logits"])
     assert np.array_equal(sm, g[key + "_softmax_local"])
 
@@ -201,7 +201,7 @@ def test_gpu_random_graphs_vs_oracle(edison, oracle, tmp_path, case):
                 lg, sm = m.infer(x)
                 lg1, sm1 = m.infer(x[:1])                # a different batch size re-bases every arena offset
         finally:
-            edison.set_softmax_mode(0)
+            edison.set_softmax_mode(edison.SOFTMAX_CMSIS_SIMD)
         assert np.array_equal(lg, want_lg), "logits, mode %d" % mode
         assert np.array_equal(sm, want_sm), "softmax, mode %d" % mode
         assert np.array_equal(lg1, want_lg[:1]) and np.array_equal(sm1, want_sm[:1])
