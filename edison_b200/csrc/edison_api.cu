@@ -541,6 +541,16 @@ int edison_debug_mag_sweep(uint32_t lo, uint32_t hi, unsigned long long *mismatc
   return EDISON_OK;
 }
 
+// K2 with per-unit clock64() stamps of block 0's second batch: d_trace[4 * units] (device, int64), see nnom_q7_umma.cu
+int edison_debug_k2_trace_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, long long *d_trace, void *stream) {
+  if (!g.ready) return fail(EDISON_E_NOINIT, "edison_init() first");
+  if (!d_trace) return fail(EDISON_E_ARG, "null trace buffer");
+  DeviceScope device_scope_;
+  CU(launch_nnom_q7(g.d_model, d_net_in, (long long)n, d_logits, d_softmax, g.softmax_mode, g.sm_count,
+                    stream ? (cudaStream_t)stream : g.slot[0].stream, nullptr, d_trace));
+  return EDISON_OK;
+}
+
 // the round-1 mma.sync kernel, for A/B timing of the two tensor paths (tools/k2_time.py); device pointers only
 int edison_debug_infer_q7_legacy_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, void *stream) {
   if (!g.ready) return fail(EDISON_E_NOINIT, "edison_init() first");

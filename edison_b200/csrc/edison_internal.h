@@ -32,13 +32,14 @@ void nnom_free(NnomModel *m);
 cudaError_t nnom_configure(void);
 // K2 (tcgen05 kernel, nnom_q7_umma.cu).  class_counts: optional device int32[10], += number of clips per first-maximum logit class
 cudaError_t launch_nnom_q7(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits,
-                           int8_t *softmax, int softmax_mode, int sm_count, cudaStream_t stream, int *class_counts = nullptr);
+                           int8_t *softmax, int softmax_mode, int sm_count, cudaStream_t stream, int *class_counts = nullptr,
+                           long long *trace = nullptr);
 cudaError_t launch_nnom_q7_legacy(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax,
                                   int softmax_mode, int sm_count, cudaStream_t stream);   // round-1 mma.sync kernel (A/B timing only)
 cudaError_t nnom_umma_configure(void);
 int nnom_umma_upload(const int8_t *const w[5], const int8_t *const b[5], const int rs[5], const int ls[5], uint8_t **out_image);
 cudaError_t launch_nnom_q7_umma(const uint8_t *image, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax, int softmax_mode,
-                                int *class_counts, int sm_count, cudaStream_t stream);
+                                int *class_counts, int sm_count, cudaStream_t stream, long long *trace = nullptr);
 
 // incremental sliding-window inference (one new row per layer and hop); state rings live in one device allocation
 struct NnomIncrState { int8_t *c1, *p1, *c2, *p2, *c3; };

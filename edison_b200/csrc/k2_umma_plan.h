@@ -15,10 +15,13 @@
 //   * outputs at the wrap-around pixels of an image row (x >= W_out) are computed and dropped;
 //   * conv1 (one input channel) is a banded (Toeplitz) product instead: an A row is (clip, image row) with the 13 input
 //     bytes of that row (padded to 16) as one chunk, N = (x_out, channel) = 9 x 16, B = the 5x5 kernel laid out along x;
-//     even and odd conv rows go to two accumulator tiles of the same lane, so the 2x1 max pool is a max in registers;
-//   * accumulators live in TMEM (lane = 32 * pixel-in-tile + clip, column = output channel), two slots of 256 columns;
+//     even and odd conv rows are two column ranges of ONE MMA (same A rows, N = 2 x 48) and land in the same lane, so the
+//     2x1 max pool is a max in registers;
+//   * accumulators live in TMEM (lane = 32 * pixel-in-tile + clip, column = output channel), four slots of 128 columns;
 //     16 epilogue warps read them back with tcgen05.ld (lane = clip), add the bias seed, shift, saturate, ReLU, pool,
-//     pack 16 channels into one 16-byte store in the next layer's layout.
+//     pack 16 channels into one 16-byte store in the next layer's layout;
+//   * every MMA descriptor and epilogue job is a closed form of (unit, index): the issue path is unrolled at compile time
+//     (descriptors become immediates), the epilogue is one small loop.
 // int32 accumulation is exact and order independent, so the result has the reference's bits
 // (arm_convolve_HWC_q7_fast_nonsquare.c:74-375, arm_fully_connected_q7_opt.c:129-475, nnom_local.c:117-160, 425-484).
 #pragma once
@@ -35,23 +38,23 @@ namespace edison {
 namespace k2 {
 
 constexpr int NC = 32;                 // clips per batch
-constexpr int kEpiWarps = 16;          // warps 0..15: epilogue (lane quarter = warp & 3, work group = warp >> 2); warp 16 issues
+constexpr int kEpiWarps = 16;          // warps 0..15: epilogue (lane quarter = warp & 3, team = TMEM slot = warp >> 2); warp 16 issues
 constexpr int kThreads = (kEpiWarps + 1) * 32;
 constexpr uint32_t PX = NC * 16;       // bytes of one pixel in one 16-channel plane
 constexpr int kNetIn = 403;
 
 // ---- shared-memory map (byte offsets from the dynamic shared memory base) --------------------------------------------
 // weight image (built once on the host, copied in with one bulk copy)
-constexpr uint32_t W1_BLK = 144 * 16;                    // one K-chunk of a conv1 B matrix: 144 rows (x * 16 + c) x 16 bytes
-constexpr uint32_t OFF_W1 = 0;                           // 11 blocks: E0c0 E0c1 E1c0 E1c1 E2c0 Z O0c1 O1c0 O1c1 O2c0 O2c1
-constexpr uint32_t OFF_W2 = OFF_W1 + 11 * W1_BLK;        // 5 x [2][32][16]
+constexpr uint32_t W1_CHUNK = 288 * 16;                  // one K-chunk of a conv1 B matrix: rows [x third][tile E/O][px][c] x 16 bytes
+constexpr uint32_t OFF_W1 = 0;                           // 3 chunk pairs j x 2 chunks
+constexpr uint32_t OFF_W2 = OFF_W1 + 6 * W1_CHUNK;       // 5 x [2][32][16]
 constexpr uint32_t OFF_W3 = OFF_W2 + 5 * 1024;           // 9 x [2][64][16]
 constexpr uint32_t OFF_W4 = OFF_W3 + 9 * 2048;           // 18 x [2][32][16]
 constexpr uint32_t OFF_WD = OFF_W4 + 18 * 1024;          // 3 x [2][16][16]
 constexpr uint32_t OFF_PAR = OFF_WD + 3 * 512;           // int32: seed1[16] seed2[32] seed3[64] seed4[32] seedd[16] rs[5] hi[5]
 constexpr int PAR_SEED1 = 0, PAR_SEED2 = 16, PAR_SEED3 = 48, PAR_SEED4 = 112, PAR_SEEDD = 144, PAR_RS = 160, PAR_HI = 165;
 constexpr uint32_t PAR_BYTES = 704;
-constexpr uint32_t IMAGE_BYTES = OFF_PAR + PAR_BYTES;    // 69,568
+constexpr uint32_t IMAGE_BYTES = OFF_PAR + PAR_BYTES;
 // activations
 constexpr uint32_t OFF_C0 = IMAGE_BYTES;                 // input rows: [parity][row / 2 (14)][clip][16]; rows 28..30 never matter
 constexpr uint32_t C0_HALF = 14 * PX;
@@ -64,75 +67,78 @@ constexpr uint32_t OFF_C3 = OFF_C2P + 2 * PLANE2;        // conv3: 4 planes x (3
 constexpr uint32_t PLANE3 = 16 * PX;
 constexpr uint32_t OFF_C4 = OFF_C3 + 4 * PLANE3;         // conv4: 2 planes x (3 px + 3 read by the dense tile's unused rows)
 constexpr uint32_t PLANE4 = 6 * PX;
-constexpr uint32_t OFF_BAR = OFF_C4 + 2 * PLANE4;        // mbarriers, TMEM base
-constexpr uint32_t SMEM_BYTES = OFF_BAR + 128;            // 6 mbarriers (48 B), TMEM base (4 B), class histogram (40 B)
+constexpr uint32_t OFF_BAR = OFF_C4 + 2 * PLANE4;        // mbarriers full[4] empty[4] raw wts (80 B), TMEM base (+80), class histogram (+96, 40 B)
+constexpr uint32_t SMEM_BYTES = OFF_BAR + 144;
 static_assert(IMAGE_BYTES % 16 == 0 && RAW_BYTES % 16 == 0 && OFF_BAR % 16 == 0, "16-byte granularity");
 static_assert(SMEM_BYTES <= 232448, "more than the 227 KB a CTA can have");
 
 // ---- the schedule --------------------------------------------------------------------------------------------------------
-// One loop iteration runs 16 units: the head of batch b (conv1, conv2) interleaved with the tail of batch b - 1 (conv3, conv4,
-// dense, lag = 1), so that the tensor pipe never waits on the short serial tail and every unit's inputs were finished at
-// least two units earlier (the issuing thread only ever waits for the epilogue that frees its TMEM slot, slot = pos & 1).
+// TMEM: four slots of 128 columns, unit number u (counted over the whole kernel) uses slot u & 3, and each slot has its own
+// team of four epilogue warps (one per lane quarter), so up to four units are drained concurrently.  One loop iteration runs
+// 21 units (3 or 4 epilogue jobs per warp each, so that no slot is held much longer than the others): the head of batch b (conv1, conv2) interleaved with the tail of batch b - 1 (conv3, conv4, dense: lag = 1), ordered
+// so that every unit's inputs were produced at least four units earlier.  That distance is what makes the only wait of the
+// issuing thread -- "my slot's previous unit u - 4 has been drained" -- sufficient: a producer d <= u - 5 was drained before
+// unit d + 4 < u could be issued, and d = u - 4 is the slot wait itself.  An epilogue only starts after its own unit's MMAs
+// (hence all earlier MMAs: the tensor pipe is in order) have completed, so it never overwrites data an older MMA still reads.
 enum Kind { C1 = 0, C2 = 1, C3 = 2, C4 = 3, DN = 4 };
-struct Unit { int kind, a, b, lag; };   // C1: a = t (conv rows 8t..8t+7), b = x half; C2: a = pooled row; C3: a = first tile, b = tiles
-constexpr int kUnits = 16;
+struct Unit { int kind, a, b, lag; };   // C1: a = t (conv rows 8t..8t+7), b = x third; C2: a = pooled row; C3: a = first tile, b = tiles
+constexpr int kUnits = 21, kSlots = 4, kSlotCols = 128;
 constexpr Unit kSched[kUnits] = {
-    {C1, 0, 0, 0}, {C1, 0, 1, 0}, {C3, 0, 2, 1}, {C1, 1, 0, 0}, {C1, 1, 1, 0}, {C3, 2, 2, 1}, {C2, 0, 0, 0}, {C3, 4, 1, 1},
-    {C1, 2, 0, 0}, {C1, 2, 1, 0}, {C4, 0, 0, 1}, {C2, 1, 0, 0}, {C2, 2, 0, 0}, {DN, 0, 0, 1}, {C2, 3, 0, 0}, {C2, 4, 0, 0}};
-constexpr int kPosTranspose = 13;   // the epilogue of this unit also lays out the NEXT batch's input (c0 is free by then)
-constexpr int kPosNextRaw = 15;     // the issuing thread starts the bulk copy of the batch after that here (raw is free by then)
+    {C1, 0, 0, 0}, {C3, 0, 1, 1}, {C1, 0, 1, 0}, {C3, 1, 1, 1}, {C1, 0, 2, 0}, {C3, 2, 1, 1}, {C1, 1, 0, 0}, {C3, 3, 1, 1}, {C1, 1, 1, 0}, {C3, 4, 1, 1},
+    {C1, 1, 2, 0}, {C1, 2, 0, 0}, {C1, 2, 1, 0}, {C4, 0, 0, 1}, {C1, 2, 2, 0}, {C2, 0, 0, 0}, {C2, 1, 0, 0}, {DN, 0, 0, 1}, {C2, 2, 0, 0}, {C2, 3, 0, 0},
+    {C2, 4, 0, 0}};
+// Why this order is safe (checked by the eager / lazy host emulation, tests/test_k2_plan_cpu.py):
+//   producers >= 4 units before their consumers: C2(r) after the C1 rows 2r..2r+3 it reads; conv3 tile k of the previous batch after
+//   that batch's C2 rows (end of the previous iteration); C4' 4 after the last conv3 tile; DN' 4 after C4';
+//   an epilogue never overwrites what an older batch's MMAs still read: C2(r0) comes after conv3 tiles 0, 1 (the readers of c2p row
+//   0), C2(r1) after tile 3, C2(r2) after tile 4; the conv1 units of batch b + 1 come after every C2 of batch b.
+constexpr int kMmaPerIter = 9 * 3 + 5 * 20 + 5 * 9 + 18 + 3;   // 193 MMAs per iteration (checked against mma_count in the host emulation)
+constexpr int kPosTranspose = 15;   // the epilogue of this unit also lays out the NEXT batch's input (conv1 of this batch is done with c0)
+constexpr int kPosNextRaw = 19;     // same slot as 15: once it is free the raw buffer is too; the issuing thread starts the next bulk copy
 
-struct MmaOp { uint32_t a_off, a_lbo, b_off, b_lbo, n, col, acc; };   // SBO = 128 for every operand
+struct MmaOp { uint32_t a_off, a_lbo, b_off, b_lbo, n, col, acc; };   // SBO = 128 for every operand; col relative to the slot
 
-// calls f(MmaOp) for every MMA of unit `pos`, in issue order; col is relative to the unit's TMEM slot
-template <int POS, class F> K2_HD void for_each_mma(F &&f) {
-  constexpr Unit u = kSched[POS];
-  if constexpr (u.kind == C1) {
-    // lanes quarter i <-> conv rows 8t + 2i (tile E, columns 0..) and 8t + 2i + 1 (tile O, columns 128..); chunk pair j:
-    // input rows 2(4t + i + j) and 2(4t + i + j) + 1.  Same A for both tiles; B holds the kernel rows each tile needs.
-    constexpr uint32_t n = u.b ? 64 : 80, xoff = u.b ? 80 * 16 : 0;
-#pragma unroll
-    for (int j = 0; j < 3; j++) {
-      const uint32_t a = OFF_C0 + (uint32_t)(4 * u.a + j) * PX;
-      constexpr int blkE[3] = {0, 2, 4}, blkO[3] = {5, 7, 9};
-      f(MmaOp{a, C0_HALF, OFF_W1 + blkE[j] * W1_BLK + xoff, W1_BLK, n, 0, (uint32_t)(j > 0)});
-      f(MmaOp{a, C0_HALF, OFF_W1 + blkO[j] * W1_BLK + xoff, W1_BLK, n, 128, (uint32_t)(j > 0)});
-    }
-  } else if constexpr (u.kind == C2) {
-    // pooled row r: conv rows y = 2r + p (p = 0, 1), x halves h: tile (p, h) at columns (2p + h) * 32, pixels x = 4h..4h+3
-#pragma unroll
-    for (int p = 0; p < 2; p++)
-#pragma unroll
-      for (int h = 0; h < 2; h++) {
-        const uint32_t y = 2 * u.a + p, col = (2 * p + h) * 32;
-#pragma unroll
-        for (int m = 0; m < 3; m++)   // taps (m, 0) + (m, 1): next pixel
-          f(MmaOp{OFF_C1P + ((y + m) * 9 + 4 * h) * PX, PX, OFF_W2 + m * 1024, 512, 32, col, (uint32_t)(m > 0)});
-        f(MmaOp{OFF_C1P + (y * 9 + 4 * h + 2) * PX, 9 * PX, OFF_W2 + 3 * 1024, 512, 32, col, 1});        // taps (0, 2) + (1, 2): next row
-        f(MmaOp{OFF_C1P + ((y + 2) * 9 + 4 * h + 2) * PX, PX, OFF_W2 + 4 * 1024, 512, 32, col, 1});      // tap (2, 2) + zero weights
-      }
-  } else if constexpr (u.kind == C3) {
+// Closed forms instead of tables: the kernel's loops must stay small AND must not stream tables through the constant cache
+// (sixteen-plus specialised unit bodies were ~170 KB of SASS and every unit's code came from L2 once per iteration; 13 KB of
+// per-unit tables in constant memory missed that cache just as steadily: profiles/r02b_k2_trace.txt).
+K2_HD constexpr int mma_count(const Unit &u) { return u.kind == C1 ? 3 : u.kind == C2 ? 20 : u.kind == C3 ? 9 * u.b : u.kind == C4 ? 18 : 3; }
+K2_HD constexpr uint32_t mma_n(const Unit &u) { return u.kind == C1 ? 96u : u.kind == C3 ? 64u : u.kind == DN ? 16u : 32u; }
+
+// the m-th MMA of unit u, in issue order
+K2_HD constexpr MmaOp mma_op(const Unit &u, int m) {
+  if (u.kind == C1) {
+    // lanes quarter i <-> conv rows 8t + 2i (tile E, columns 0..47) and 8t + 2i + 1 (tile O, columns 48..95); chunk pair j = m:
+    // input rows 2(4t + i + j) and 2(4t + i + j) + 1.  Both tiles read the same A rows, so ONE MMA with N = 96 serves them:
+    // B rows 0..47 hold the kernel rows tile E needs from this chunk pair (ky = 2j, 2j + 1), rows 48..95 those of tile O
+    // (ky = 2j - 1, 2j), for the three output pixels of x third u.b.
+    return MmaOp{OFF_C0 + (uint32_t)(4 * u.a + m) * PX, C0_HALF, OFF_W1 + (uint32_t)m * 2 * W1_CHUNK + (uint32_t)u.b * 96 * 16, W1_CHUNK, 96, 0,
+                 (uint32_t)(m > 0)};
+  } else if (u.kind == C2) {
+    // pooled row r: conv rows y = 2r + p (p = 0, 1), x halves h: tile (p, h) at columns (2p + h) * 32, pixels x = 4h..4h+3;
+    // five MMAs per tile: taps (mm, 0) + (mm, 1) for mm = 0..2 (chunk 1 = next pixel), (0, 2) + (1, 2) (chunk 1 = next row),
+    // (2, 2) + zero weights
+    const int tile = m / 5, mm = m - 5 * tile, p = tile >> 1, h = tile & 1;
+    const uint32_t y = 2 * u.a + p, col = (uint32_t)tile * 32;
+    if (mm < 3) return MmaOp{OFF_C1P + ((y + mm) * 9 + 4 * h) * PX, PX, OFF_W2 + (uint32_t)mm * 1024, 512, 32, col, (uint32_t)(mm > 0)};
+    if (mm == 3) return MmaOp{OFF_C1P + (y * 9 + 4 * h + 2) * PX, 9 * PX, OFF_W2 + 3 * 1024, 512, 32, col, 1};
+    return MmaOp{OFF_C1P + ((y + 2) * 9 + 4 * h + 2) * PX, PX, OFF_W2 + 4 * 1024, 512, 32, col, 1};
+  } else if (u.kind == C3) {
     // tile tau: output positions q = 4 tau .. 4 tau + 3 on the 7-wide input grid (y = q / 7, x = q % 7; x >= 5 dropped)
-#pragma unroll
-    for (int tl = 0; tl < u.b; tl++)
-#pragma unroll
-      for (int tap = 0; tap < 9; tap++)
-        f(MmaOp{OFF_C2P + (uint32_t)(4 * (u.a + tl) + (tap / 3) * 7 + tap % 3) * PX, PLANE2, OFF_W3 + tap * 2048, 1024, 64,
-                (uint32_t)tl * 64, (uint32_t)(tap > 0)});
-  } else if constexpr (u.kind == C4) {
+    const int tl = m / 9, tap = m - 9 * tl, ky = tap / 3, kx = tap - 3 * ky;
+    return MmaOp{OFF_C2P + (uint32_t)(4 * (u.a + tl) + ky * 7 + kx) * PX, PLANE2, OFF_W3 + (uint32_t)tap * 2048, 1024, 64, (uint32_t)tl * 64,
+                 (uint32_t)(tap > 0)};
+  } else if (u.kind == C4) {
     // one tile: output positions x = 0..3 (3 dropped) on the 5-wide grid; per tap two MMAs (channels 0..31, 32..63)
-#pragma unroll
-    for (int tap = 0; tap < 9; tap++)
-#pragma unroll
-      for (int cp = 0; cp < 2; cp++)
-        f(MmaOp{OFF_C3 + (uint32_t)((tap / 3) * 5 + tap % 3) * PX + cp * 2 * PLANE3, PLANE3, OFF_W4 + (tap * 2 + cp) * 1024, 512, 32, 0,
-                (uint32_t)(tap + cp > 0)});
-  } else {
-    // dense: rows = clips (lanes 0..31; the other 96 rows read neighbouring pixels and are ignored), K = 3 px x 32 channels
-#pragma unroll
-    for (int m = 0; m < 3; m++) f(MmaOp{OFF_C4 + (uint32_t)m * PX, PLANE4, OFF_WD + m * 512, 256, 16, 0, (uint32_t)(m > 0)});
+    const int tap = m >> 1, cp = m & 1, ky = tap / 3, kx = tap - 3 * ky;
+    return MmaOp{OFF_C3 + (uint32_t)(ky * 5 + kx) * PX + (uint32_t)cp * 2 * PLANE3, PLANE3, OFF_W4 + (uint32_t)m * 1024, 512, 32, 0, (uint32_t)(m > 0)};
   }
+  // dense: rows = clips (lanes 0..31; the other 96 rows read neighbouring pixels and are ignored), K = 3 px x 32 channels
+  return MmaOp{OFF_C4 + (uint32_t)m * PX, PLANE4, OFF_WD + (uint32_t)m * 512, 256, 16, 0, (uint32_t)(m > 0)};
 }
+
+K2_HD constexpr uint32_t desc_lo(uint32_t off, uint32_t lbo) { return ((off >> 4) & 0x3fffu) | (((lbo >> 4) & 0x3fffu) << 16); }
+// cute::UMMA::InstrDescriptor for kind::i8: D = S32 (2 << 4), A = B = signed 8 bit (1 << 7, 1 << 10), K-major, N >> 3 at 17, M >> 4 at 24
+K2_HD constexpr uint32_t idesc_i8(uint32_t n) { return (2u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24); }
 
 // ---- quantisation epilogue -------------------------------------------------------------------------------------------
 // clamp((m + seed) >> rs, 0, 127) = (max(min(m + seed, hi), 0)) >> rs with hi = (128 << rs) - 1: SSAT8 then ReLU
@@ -212,97 +218,102 @@ K2_HD void softmax_q7(const int8_t *in, int8_t *out, int mode) {
   }
 }
 
-// What the epilogue of one unit needs from its executor (CUDA kernel or host emulation):
+// What an epilogue needs from its executor (CUDA kernel or host emulation):
 //   c.ld16(col, v)   : this thread's lane of TMEM columns col..col+15 of the unit's slot;  c.ld_wait() before using v
 //   c.st16(off, Vec16) : 16-byte shared-memory store;  c.par(i) / c.par4(i): int32 parameter(s) i (same for all lanes)
-//   c.lane, c.q (lane quarter = pixel in tile), c.g (work group)
-//   dense only: c.clip0 (first clip of the batch), c.nclips, c.logits, c.softmax (global, may be null), c.softmax_mode,
-//               c.count(cls) (class histogram hook)
-template <int POS, class Ctx> K2_HD void epilogue(Ctx &c) {
-  constexpr Unit u = kSched[POS];
-  if constexpr (u.kind == C1) {
-    constexpr int P = u.b ? 4 : 5;
-    const int rs = c.par(PAR_RS + 0), hi = c.par(PAR_HI + 0);
+//   c.lane (= clip), c.q (lane quarter = pixel within an M = 128 tile);  dense only: c.clip0 (first clip of the batch),
+//   c.nclips, c.logits, c.softmax (global, may be null), c.softmax_mode, c.count(cls) (class histogram hook)
+// One warp per lane quarter drains a whole unit: lean loops (a job = 16 accumulator columns -> one 16-byte store is ~75
+// instructions; evaluating a generic job descriptor per job tripled that and the epilogue is latency bound).
+struct JobParams { uint32_t col_e, col_o, seed, out; };
+
+// n jobs back to back, software pipelined: the tcgen05.ld of job j + 1 is in flight while job j is quantised and stored (the
+// epilogue is bound by latency -- ~250 cycles of TMEM load against ~100 of arithmetic per job -- not by issue slots)
+template <bool POOL, class Ctx, class P> K2_HD void job_stream(Ctx &c, int n, int rs, int hi, P params) {
+  if (n <= 0) return;
+  uint32_t e[16], o[16];
+  JobParams p = params(0);
+  c.ld16(p.col_e, e);
+  if (POOL) c.ld16(p.col_o, o);
+#pragma unroll 1
+  for (int j = 0; j < n; j++) {
     int seed[16];
-    load16(c, PAR_SEED1, seed);
-    const int r = 4 * u.a + c.q;   // pooled row
+    load16(c, (int)p.seed, seed);   // in flight with the tcgen05.ld
+    c.ld_wait();
+    int m[16];
 #pragma unroll
-    for (int k = 0; k < 2; k++) {
-      const int px = c.g + 4 * k;   // group g takes pixel g (and group 0 pixel 4 of the 5-pixel half)
-      if (px < P) {
-        uint32_t e[16], o[16];
-        c.ld16(px * 16, e);
-        c.ld16(128 + px * 16, o);
-        c.ld_wait();
-        c.st16(OFF_C1P + (uint32_t)(r * 9 + 5 * u.b + px) * PX + c.lane * 16, quant16<true>(e, o, seed, hi, rs));
-      }
+    for (int i = 0; i < 16; i++) m[i] = POOL ? imax((int)e[i], (int)o[i]) : (int)e[i];
+    const JobParams cur = p;
+    if (j + 1 < n) {
+      p = params(j + 1);
+      c.ld16(p.col_e, e);
+      if (POOL) c.ld16(p.col_o, o);
     }
-  } else if constexpr (u.kind == C2) {
-    const int rs = c.par(PAR_RS + 1), hi = c.par(PAR_HI + 1);
-    const int h = c.g >> 1, half = c.g & 1, x = 4 * h + c.q;
-    if (x < 7) {
-      int seed[16];
-      load16(c, PAR_SEED2 + half * 16, seed);
-      uint32_t e[16], o[16];
-      c.ld16(h * 32 + half * 16, e);
-      c.ld16((2 + h) * 32 + half * 16, o);
-      c.ld_wait();
-      c.st16(OFF_C2P + half * PLANE2 + (uint32_t)(u.a * 7 + x) * PX + c.lane * 16, quant16<true>(e, o, seed, hi, rs));
+    int v[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) v[i] = q7_relu(m[i], seed[i], hi, rs);
+    c.st16(cur.out, Vec16{pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7]), pack4(v[8], v[9], v[10], v[11]),
+                          pack4(v[12], v[13], v[14], v[15])});
+  }
+}
+
+template <class Ctx> K2_HD void epilogue_conv(Ctx &c, const Unit &u) {
+  const uint32_t lane16 = (uint32_t)c.lane * 16;
+  if (u.kind == C1) {
+    // lane quarter q is pooled row 4t + q; the unit holds the three pixels of x third u.b: tile E at columns 16 px, tile O at 48 + 16 px
+    const uint32_t out = OFF_C1P + (uint32_t)((4 * u.a + c.q) * 9 + 3 * u.b) * PX + lane16;
+    job_stream<true>(c, 3, c.par(PAR_RS + 0), c.par(PAR_HI + 0), [&](int j) {
+      return JobParams{(uint32_t)j * 16, 48 + (uint32_t)j * 16, (uint32_t)PAR_SEED1, out + (uint32_t)j * PX};
+    });
+  } else if (u.kind == C2) {
+    // pooled row u.a; job j: x half h = j >> 1, channel half j & 1; x = 4h + q (x = 7, i.e. q = 3 in the second half, is the
+    // wrap-around pixel); tile (p, h) at columns (2p + h) * 32
+    const uint32_t out = OFF_C2P + (uint32_t)(u.a * 7 + c.q) * PX + lane16;
+    job_stream<true>(c, c.q < 3 ? 4 : 2, c.par(PAR_RS + 1), c.par(PAR_HI + 1), [&](int j) {
+      const uint32_t h = (uint32_t)j >> 1, half = (uint32_t)j & 1;
+      return JobParams{h * 32 + half * 16, (2 + h) * 32 + half * 16, (uint32_t)PAR_SEED2 + half * 16, out + half * PLANE2 + h * 4 * PX};
+    });
+  } else if (u.kind == C3) {
+    // one tile: position idx = 4 u.a + q on the 7-wide grid (x >= 5 and row 3 are wrap-around positions); four 16-channel planes
+    const int idx = 4 * u.a + c.q, y = idx / 7, x = idx - 7 * y;
+    const uint32_t out = OFF_C3 + (uint32_t)(y * 5 + x) * PX + lane16;
+    job_stream<false>(c, (x < 5 && y < 3) ? 4 : 0, c.par(PAR_RS + 2), c.par(PAR_HI + 2), [&](int j) {
+      return JobParams{(uint32_t)j * 16, 0, (uint32_t)PAR_SEED3 + (uint32_t)j * 16, out + (uint32_t)j * PLANE3};
+    });
+  } else if (u.kind == C4) {
+    // x = q (3 is the wrap-around pixel); two 16-channel planes
+    const uint32_t out = OFF_C4 + (uint32_t)c.q * PX + lane16;
+    job_stream<false>(c, c.q < 3 ? 2 : 0, c.par(PAR_RS + 3), c.par(PAR_HI + 3), [&](int j) {
+      return JobParams{(uint32_t)j * 16, 0, (uint32_t)PAR_SEED4 + (uint32_t)j * 16, out + (uint32_t)j * PLANE4};
+    });
+  }
+}
+
+// Dense 96 -> 10 (nnom_dense.c:92-119): lane = clip (lane quarter 0 only); logits = SSAT8((acc + seed) >> rs); then softmax
+template <class Ctx> K2_HD void run_dense(Ctx &c) {
+  const int rs = c.par(PAR_RS + 4);
+  uint32_t e[16];
+  c.ld16(0, e);
+  c.ld_wait();
+  if (c.lane < c.nclips) {
+    int8_t lg[10];
+#pragma unroll
+    for (int i = 0; i < 10; i++) lg[i] = (int8_t)ssat8(((int)e[i] + c.par(PAR_SEEDD + i)) >> rs);
+    const long long clip = c.clip0 + c.lane;
+    if (c.logits)
+#pragma unroll
+      for (int i = 0; i < 10; i++) c.logits[clip * 10 + i] = lg[i];
+    if (c.softmax) {
+      int8_t sm[10];
+      softmax_q7(lg, sm, c.softmax_mode);
+#pragma unroll
+      for (int i = 0; i < 10; i++) c.softmax[clip * 10 + i] = sm[i];
     }
-  } else if constexpr (u.kind == C3) {
-    const int rs = c.par(PAR_RS + 2), hi = c.par(PAR_HI + 2);
-    const int tl = c.g >> 1, half = c.g & 1;          // tile in unit, 32-channel half
-    const int idx = 4 * (u.a + tl) + c.q, y = idx / 7, x = idx - y * 7;
-    if (tl < u.b && x < 5 && y < 3) {
+    int best = 0;   // first maximum of the logits: the class the firmware's arm_max would report on them
 #pragma unroll
-      for (int k = 0; k < 2; k++) {
-        const int plane = 2 * half + k;
-        int seed[16];
-        load16(c, PAR_SEED3 + plane * 16, seed);
-        uint32_t e[16];
-        c.ld16(tl * 64 + plane * 16, e);
-        c.ld_wait();
-        c.st16(OFF_C3 + plane * PLANE3 + (uint32_t)(y * 5 + x) * PX + c.lane * 16, quant16<false>(e, e, seed, hi, rs));
-      }
-    }
-  } else if constexpr (u.kind == C4) {
-    const int rs = c.par(PAR_RS + 3), hi = c.par(PAR_HI + 3);
-    if (c.g < 2 && c.q < 3) {
-      int seed[16];
-      load16(c, PAR_SEED4 + c.g * 16, seed);
-      uint32_t e[16];
-      c.ld16(c.g * 16, e);
-      c.ld_wait();
-      c.st16(OFF_C4 + c.g * PLANE4 + (uint32_t)c.q * PX + c.lane * 16, quant16<false>(e, e, seed, hi, rs));
-    }
-  } else {
-    // Dense 96 -> 10 (nnom_dense.c:92-119): lane = clip; logits = SSAT8((acc + seed) >> rs); then softmax
-    if (c.g == 0 && c.q == 0) {
-      const int rs = c.par(PAR_RS + 4);
-      uint32_t e[16];
-      c.ld16(0, e);
-      c.ld_wait();
-      if (c.lane < c.nclips) {
-        int8_t lg[10];
-#pragma unroll
-        for (int i = 0; i < 10; i++) lg[i] = (int8_t)ssat8(((int)e[i] + c.par(PAR_SEEDD + i)) >> rs);
-        const long long clip = c.clip0 + c.lane;
-        if (c.logits)
-#pragma unroll
-          for (int i = 0; i < 10; i++) c.logits[clip * 10 + i] = lg[i];
-        if (c.softmax) {
-          int8_t sm[10];
-          softmax_q7(lg, sm, c.softmax_mode);
-#pragma unroll
-          for (int i = 0; i < 10; i++) c.softmax[clip * 10 + i] = sm[i];
-        }
-        int best = 0;   // first maximum of the logits: the class the firmware's arm_max would report on them
-#pragma unroll
-        for (int i = 1; i < 10; i++)
-          if (lg[i] > lg[best]) best = i;
-        c.count(best);
-      }
-    }
+    for (int i = 1; i < 10; i++)
+      if (lg[i] > lg[best]) best = i;
+    c.count(best);
   }
 }
 
@@ -327,18 +338,19 @@ constexpr int kInRowsUsed = 28;   // conv rows 24..26 only feed the pooled row t
 // left shifts (weights.h:72-105).  dense weights already de-interleaved to [10][96].
 inline void build_image(uint8_t *img, const int8_t *const w[5], const int8_t *const b[5], const int rs[5], const int ls[5]) {
   memset(img, 0, IMAGE_BYTES);
-  // conv1: block (tile p, pair j, chunk h) holds kernel row ky = 2j + h (E) or 2j - 1 + h (O) along x:
-  //   row n = x * 16 + c, byte kk = input x: w1[c][ky][kk - x]
-  const int blk_of[2][3][2] = {{{0, 1}, {2, 3}, {4, 5}}, {{5, 6}, {7, 8}, {9, 10}}};
-  for (int p = 0; p < 2; p++)
-    for (int j = 0; j < 3; j++)
-      for (int h = 0; h < 2; h++) {
+  // conv1: chunk (pair j, chunk h) = 288 rows x 16 bytes; row = xs * 96 + p * 48 + px * 16 + c for output pixel x = 3 xs + px of
+  // tile p (0 = even conv rows, 1 = odd); byte kk = input x; the row holds kernel row ky = 2j + h (E) or 2j - 1 + h (O):
+  //   w1[c][ky][kk - x] for 0 <= kk - x < 5, zero elsewhere and for ky outside 0..4
+  for (int j = 0; j < 3; j++)
+    for (int h = 0; h < 2; h++)
+      for (int p = 0; p < 2; p++) {
         const int ky = p ? 2 * j - 1 + h : 2 * j + h;
-        if (ky < 0 || ky > 4) continue;   // the shared zero block
-        uint8_t *blk = img + OFF_W1 + blk_of[p][j][h] * W1_BLK;
+        if (ky < 0 || ky > 4) continue;
+        uint8_t *chunk = img + OFF_W1 + (j * 2 + h) * W1_CHUNK;
         for (int x = 0; x < 9; x++)
           for (int c = 0; c < 16; c++)
-            for (int kx = 0; kx < 5; kx++) blk[(x * 16 + c) * 16 + x + kx] = (uint8_t)w[0][(c * 5 + ky) * 5 + kx];
+            for (int kx = 0; kx < 5; kx++)
+              chunk[((x / 3) * 96 + p * 48 + (x % 3) * 16 + c) * 16 + x + kx] = (uint8_t)w[0][(c * 5 + ky) * 5 + kx];
       }
   // conv2: matrix m = [chunk][n][16]; taps per chunk as in for_each_mma
   const int tap2[5][2] = {{0, 1}, {3, 4}, {6, 7}, {2, 5}, {8, -1}};

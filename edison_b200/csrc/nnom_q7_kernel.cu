@@ -563,10 +563,10 @@ cudaError_t nnom_configure(void) {
 static uint8_t *g_umma_image = nullptr;
 
 cudaError_t launch_nnom_q7(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax,
-                           int softmax_mode, int sm_count, cudaStream_t stream, int *class_counts) {
+                           int softmax_mode, int sm_count, cudaStream_t stream, int *class_counts, long long *trace) {
   (void)model;
   if (!g_umma_image) return cudaErrorNotReady;
-  return launch_nnom_q7_umma(g_umma_image, net_in, n, logits, softmax, softmax_mode, class_counts, sm_count, stream);
+  return launch_nnom_q7_umma(g_umma_image, net_in, n, logits, softmax, softmax_mode, class_counts, sm_count, stream, trace);
 }
 
 // the round-1 mma.sync kernel: kept for tools/k2_time.py (A/B timing of the two tensor paths), not reachable from the C ABI

@@ -4,7 +4,7 @@
 // epilogues -- is k2_umma_plan.h (also run on the host by tests/host_emu/emu_k2.cpp); this file is its executor:
 //
 //   * persistent grid, one CTA per SM, 32 clips per batch, activations of a batch never leave shared memory;
-//   * warp 16, one thread: waits for the TMEM slot of the next unit (mbarrier empty[slot]), issues the unit's MMAs from
+//   * warp 16 (converged, one lane issuing): waits for the TMEM slot of the next unit (mbarrier empty[slot]), issues the unit's MMAs from
 //     shared-memory descriptors (operands are never copied: a filter tap is a shifted start address), commits them to
 //     mbarrier full[slot]; it also starts the bulk copies (cp.async.bulk -> SASS UBLKCP) of the weight image and of each
 //     batch's 32 x 403 input bytes;
@@ -29,20 +29,22 @@ namespace {
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-// cute::UMMA::SmemDescriptor, no swizzle, K-major: start >> 4 [0,14), LBO >> 4 [16,30), SBO >> 4 = 8 [32,46), version 1 [46,48)
-__device__ __forceinline__ uint64_t make_desc(uint32_t addr, uint32_t lbo) {
-  return (uint64_t)(((addr >> 4) & 0x3fffu) | (((lbo >> 4) & 0x3fffu) << 16)) | ((uint64_t)(8u | (1u << 14)) << 32);
-}
-// cute::UMMA::InstrDescriptor for kind::i8: D = S32 (2 << 4), A = B = signed 8 bit (1 << 7, 1 << 10), K-major, N >> 3 at 17, M >> 4 at 24
-__host__ __device__ constexpr uint32_t make_idesc_i8(uint32_t n) { return (2u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24); }
-
+// The issuing warp runs converged; every instruction that one thread issues on behalf of the CTA is predicated on elect.sync
+// inside the same asm block (the form ptxas recognises as single-thread issue: ELECT + predicated UTCIMMA, no divergence loop).
+// elect.sync over the full mask names the same lane every time, which tcgen05.commit needs (it tracks the MMAs of ITS thread).
 __device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
-  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-               "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n"
+  asm volatile("{\n\t.reg .pred p, e;\n\t.reg .b32 r;\n\telect.sync r|e, 0xffffffff;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "@e tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}\n"
                :: "r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+  asm volatile("{\n\t.reg .pred e;\n\t.reg .b32 r;\n\telect.sync r|e, 0xffffffff;\n\t"
+               "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}\n" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t e;
+  asm volatile("{\n\t.reg .pred e;\n\t.reg .b32 r;\n\telect.sync r|e, 0xffffffff;\n\tselp.u32 %0, 1, 0, e;\n\t}\n" : "=r"(e));
+  return e != 0;
 }
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
@@ -76,13 +78,18 @@ struct DevCtx {
   int8_t *logits, *softmax;
   int softmax_mode;
   int *hist;        // shared-memory class histogram
+  long long t_ld;   // TRACE builds: clock64() when the last tcgen05.ld had landed
+  bool tracing;
   __device__ __forceinline__ void ld16(uint32_t col, uint32_t (&v)[16]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
                  : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
                    "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
                  : "r"(taddr + col));
   }
-  __device__ __forceinline__ void ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+  __device__ __forceinline__ void ld_wait() {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    if (tracing) t_ld = clock64();
+  }
   __device__ __forceinline__ void st16(uint32_t off, Vec16 v) { *reinterpret_cast<uint4 *>(smem + off) = make_uint4(v.x, v.y, v.z, v.w); }
   __device__ __forceinline__ int par(int i) const { return reinterpret_cast<const int *>(smem + OFF_PAR)[i]; }
   __device__ __forceinline__ Int4 par4(int i) const {
@@ -102,17 +109,16 @@ struct Job {
   __device__ __forceinline__ bool bulk(int k) const { return aligned && (batch(k) + 1) * NC <= n; }
 };
 
-// input layout step for this CTA's k-th batch: raw [clip][403] -> c0[row & 1][row >> 1][clip][16]; tid in 0..511
-__device__ __forceinline__ void transpose_in(uint8_t *smem, const Job &J, int k, uint32_t raw_bar, int tid) {
+// input layout step for this CTA's k-th batch: raw [clip][403] -> c0[row & 1][row >> 1][clip][16]; tid in 0..nthreads-1
+__device__ __forceinline__ void transpose_in(uint8_t *smem, const Job &J, int k, uint32_t raw_bar, int tid, int nthreads = 128) {
   const long long clip0 = J.batch(k) * NC;
   const int nclips = (int)min((long long)NC, J.n - clip0);
   const bool bulk = J.bulk(k);
   if (bulk) mbar_wait(raw_bar, (uint32_t)k & 1u);
   const int clip = tid & 31;
-#pragma unroll
-  for (int round = 0; round < 2; round++) {
-    const int row = (tid >> 5) + 16 * round;
-    if (row < kInRowsUsed) {
+#pragma unroll 1
+  for (int row = tid >> 5; row < kInRowsUsed; row += nthreads >> 5) {
+    {
       const uint32_t a = (uint32_t)clip * kNetIn + (uint32_t)row * 13;
       uint32_t w[4];
       Vec16 v;
@@ -135,68 +141,59 @@ __device__ __forceinline__ void transpose_in(uint8_t *smem, const Job &J, int k,
   }
 }
 
-struct Bars { uint32_t full[2], empty[2], raw, wts; };
+__constant__ Unit c_sched[kUnits];   // k2::kSched for the epilogue loop, uploaded once by nnom_umma_configure (304 bytes: stays cached)
 
-template <int POS> __device__ __forceinline__ void issue_unit(const Job &J, const Bars &B, uint32_t sbase, uint32_t tmem, int it) {
-  constexpr Unit u = kSched[POS];
-  const bool valid = u.lag ? it > 0 : it < J.nbc;
-  mbar_wait(B.empty[POS & 1], (uint32_t)(((POS >> 1) & 1) ^ 1));   // the epilogue of this slot's previous unit is done
-  tc_fence_after();
-  if (POS == kPosNextRaw && it + 2 < J.nbc && J.bulk(it + 2)) {    // raw was consumed by the transpose of unit kPosTranspose
-    mbar_expect_tx(B.raw, NC * kNetIn);
-    bulk_g2s(sbase + OFF_RAW, J.net_in + J.batch(it + 2) * NC * kNetIn, NC * kNetIn, B.raw);
-  }
-  if (valid)
-    for_each_mma<POS>([&](const MmaOp &op) {
-      mma_i8(tmem + (POS & 1) * 256 + op.col, make_desc(sbase + op.a_off, op.a_lbo), make_desc(sbase + op.b_off, op.b_lbo), make_idesc_i8(op.n),
-             op.acc);
-    });
-  umma_commit(B.full[POS & 1]);
-}
+__device__ __forceinline__ uint64_t desc_from_lo(uint32_t lo) { return (uint64_t)lo | ((uint64_t)(8u | (1u << 14)) << 32); }
 
-template <int POS> __device__ __forceinline__ void drain_unit(const Job &J, const Bars &B, DevCtx &c, uint32_t tmem_q, int it, int tid) {
-  constexpr Unit u = kSched[POS];
-  const bool valid = u.lag ? it > 0 : it < J.nbc;
-  mbar_wait(B.full[POS & 1], (uint32_t)((POS >> 1) & 1));          // the unit's MMAs (and every earlier one) have completed
-  tc_fence_after();
-  if (valid) {
-    c.taddr = tmem_q + (POS & 1) * 256;
-    if (u.kind == DN) {
-      c.clip0 = J.batch(it - 1) * NC;
-      c.nclips = (int)min((long long)NC, J.n - c.clip0);
+// The issue path is unrolled at compile time: every descriptor is (shared-memory base >> 4) + an immediate, the code is a
+// straight line of ~7 instructions per MMA that ptxas software-pipelines.  (Working descriptors out at run time -- from tables
+// in constant memory, in closed form per unit, or broadcast from registers -- made the single issuing warp the bottleneck:
+// 150-200 cycles per MMA against ~45 of tensor time; profiles/r02b_k2_trace.txt.)
+template <int POS, int M> struct IssueMmas {
+  static __device__ __forceinline__ void go(uint32_t tm, uint32_t sb4) {
+    constexpr Unit U = kSched[POS];
+    if constexpr (M < mma_count(U)) {
+      constexpr MmaOp op = mma_op(U, M);
+      mma_i8(tm + op.col, desc_from_lo(desc_lo(op.a_off, op.a_lbo) + sb4), desc_from_lo(desc_lo(op.b_off, op.b_lbo) + sb4), idesc_i8(op.n), op.acc);
+      IssueMmas<POS, M + 1>::go(tm, sb4);
     }
-    epilogue<POS>(c);
-  }
-  if (POS == kPosTranspose && it + 1 < J.nbc) transpose_in(c.smem, J, it + 1, B.raw, tid);
-  fence_async_smem();   // this thread's shared-memory stores -> visible to the MMAs that will read them
-  tc_fence_before();
-  mbar_arrive(B.empty[POS & 1]);
-}
-
-template <int POS> struct IssueAll {
-  static __device__ __forceinline__ void go(const Job &J, const Bars &B, uint32_t sbase, uint32_t tmem, int it) {
-    issue_unit<POS>(J, B, sbase, tmem, it);
-    if constexpr (POS + 1 < kUnits) IssueAll<POS + 1>::go(J, B, sbase, tmem, it);
-  }
-};
-template <int POS> struct DrainAll {
-  static __device__ __forceinline__ void go(const Job &J, const Bars &B, DevCtx &c, uint32_t tmem_q, int it, int tid) {
-    drain_unit<POS>(J, B, c, tmem_q, it, tid);
-    if constexpr (POS + 1 < kUnits) DrainAll<POS + 1>::go(J, B, c, tmem_q, it, tid);
   }
 };
 
+template <int POS, bool TRACE> struct IssueUnits {
+  static __device__ __forceinline__ void go(const Job &J, uint32_t bars, uint32_t bar_raw, uint32_t sbase, uint32_t sb4, uint32_t tmem, int it,
+                                            uint32_t &gpos, int lane, long long *trace) {
+    constexpr Unit U = kSched[POS];
+    const uint32_t slot = gpos & (kSlots - 1), par = (gpos >> 2) & 1;
+    if (TRACE && trace && it == 1 && lane == 0) trace[4 * POS + 0] = clock64();
+    mbar_wait(bars + 32 + 8 * slot, par ^ 1);            // the team of this slot has drained its previous unit
+    tc_fence_after();
+    if (TRACE && trace && it == 1 && lane == 0) trace[4 * POS + 1] = clock64();
+    if (POS == kPosNextRaw && it + 2 < J.nbc && J.bulk(it + 2) && elect_one()) {   // raw was consumed by unit kPosTranspose's epilogue (same slot)
+      mbar_expect_tx(bar_raw, NC * kNetIn);
+      bulk_g2s(sbase + OFF_RAW, J.net_in + J.batch(it + 2) * NC * kNetIn, NC * kNetIn, bar_raw);
+    }
+    if (U.lag ? it > 0 : it < J.nbc) IssueMmas<POS, 0>::go(tmem + slot * kSlotCols, sb4);
+    umma_commit(bars + 8 * slot);
+    gpos++;
+    if constexpr (POS + 1 < kUnits) IssueUnits<POS + 1, TRACE>::go(J, bars, bar_raw, sbase, sb4, tmem, it, gpos, lane, trace);
+  }
+};
+
+// TRACE: block 0 records clock64() per unit of its second iteration -- issuing lane: [4 pos] = before the slot wait, [4 pos + 1] =
+// slot free; thread 0: [4 pos + 2] = accumulators ready, [4 pos + 3] = slot released (tools/k2_trace.py prints the timeline)
+template <bool TRACE>
 __global__ void __launch_bounds__(kThreads, 1)
 nnom_q7_umma_kernel(const uint8_t *image, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax, int softmax_mode,
-                    int *class_counts) {
+                    int *class_counts, long long *trace) {
   extern __shared__ __align__(128) uint8_t smem[];
+  if (TRACE && blockIdx.x != 0) trace = nullptr;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const uint32_t sbase = smem_u32(smem);
-  Bars B;
-  B.full[0] = sbase + OFF_BAR; B.full[1] = sbase + OFF_BAR + 8; B.empty[0] = sbase + OFF_BAR + 16; B.empty[1] = sbase + OFF_BAR + 24;
-  B.raw = sbase + OFF_BAR + 32; B.wts = sbase + OFF_BAR + 40;
-  volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(smem + OFF_BAR + 48);
-  int *hist = reinterpret_cast<int *>(smem + OFF_BAR + 64);
+  const uint32_t sbase = smem_u32(smem), bars = sbase + OFF_BAR;
+  // mbarriers: full[slot] = bars + 8 slot, empty[slot] = bars + 32 + 8 slot, raw = bars + 64, weights = bars + 72
+  const uint32_t bar_raw = bars + 64, bar_wts = bars + 72;
+  volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(smem + OFF_BAR + 80);
+  int *hist = reinterpret_cast<int *>(smem + OFF_BAR + 96);
   Job J;
   J.image = image; J.net_in = net_in; J.n = n; J.nb = (n + NC - 1) / NC;
   J.nbc = (long long)blockIdx.x < J.nb ? (int)((J.nb - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
@@ -204,19 +201,21 @@ nnom_q7_umma_kernel(const uint8_t *image, const int8_t *net_in, long long n, int
 
   if (warp == kEpiWarps) {
     if (lane == 0) {
-      mbar_init(B.full[0], 1); mbar_init(B.full[1], 1);
-      mbar_init(B.empty[0], kEpiWarps * 32); mbar_init(B.empty[1], kEpiWarps * 32);
-      mbar_init(B.raw, 1); mbar_init(B.wts, 1);
+      for (int s = 0; s < kSlots; s++) {
+        mbar_init(bars + 8 * s, 1);
+        mbar_init(bars + 32 + 8 * s, 128);                      // one team of four warps per slot
+      }
+      mbar_init(bar_raw, 1); mbar_init(bar_wts, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-      mbar_expect_tx(B.wts, IMAGE_BYTES);
-      bulk_g2s(sbase, image, IMAGE_BYTES, B.wts);
+      mbar_expect_tx(bar_wts, IMAGE_BYTES);
+      bulk_g2s(sbase, image, IMAGE_BYTES, bar_wts);
       if (J.nbc > 0 && J.bulk(0)) {
-        mbar_expect_tx(B.raw, NC * kNetIn);
-        bulk_g2s(sbase + OFF_RAW, net_in + J.batch(0) * NC * kNetIn, NC * kNetIn, B.raw);
+        mbar_expect_tx(bar_raw, NC * kNetIn);
+        bulk_g2s(sbase + OFF_RAW, net_in + J.batch(0) * NC * kNetIn, NC * kNetIn, bar_raw);
       }
     }
     __syncwarp();
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(sbase + OFF_BAR + 48), "r"(512) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(bars + 80), "r"(512) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   if (tid < 10) hist[tid] = 0;
@@ -224,25 +223,62 @@ nnom_q7_umma_kernel(const uint8_t *image, const int8_t *net_in, long long n, int
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-  mbar_wait(B.wts, 0);                                       // weights and parameters are in shared memory
-  if (warp < kEpiWarps && J.nbc > 0) transpose_in(smem, J, 0, B.raw, tid);
+  mbar_wait(bar_wts, 0);                                       // weights and parameters are in shared memory
+  if (warp < kEpiWarps && J.nbc > 0) transpose_in(smem, J, 0, bar_raw, tid, kEpiWarps * 32);
   fence_async_smem();
   __syncthreads();
 
-  if (warp == kEpiWarps) {
-    if (lane == 0 && J.nbc > 0) {
-      if (J.nbc > 1 && J.bulk(1)) {
-        mbar_expect_tx(B.raw, NC * kNetIn);
-        bulk_g2s(sbase + OFF_RAW, net_in + J.batch(1) * NC * kNetIn, NC * kNetIn, B.raw);
+  if (J.nbc > 0) {
+    if (warp == kEpiWarps) {
+      // ---- issuing warp (converged; elect.sync picks the lane that issues) ------------------------------------------------
+      if (J.nbc > 1 && J.bulk(1) && elect_one()) {
+        mbar_expect_tx(bar_raw, NC * kNetIn);
+        bulk_g2s(sbase + OFF_RAW, net_in + J.batch(1) * NC * kNetIn, NC * kNetIn, bar_raw);
       }
-      for (int it = 0; it <= J.nbc; it++) IssueAll<0>::go(J, B, sbase, tmem, it);
+      const uint32_t sb4 = sbase >> 4;
+      uint32_t gpos = 0;
+#pragma unroll 1
+      for (int it = 0; it <= J.nbc; it++) IssueUnits<0, TRACE>::go(J, bars, bar_raw, sbase, sb4, tmem, it, gpos, lane, trace);
+    } else {
+      // ---- epilogue warps: team = warp >> 2 drains the units of TMEM slot `team`; within a team warp q owns lane quarter q ------
+      DevCtx c;
+      c.smem = smem; c.lane = lane; c.q = warp & 3; c.g = 0;
+      c.clip0 = 0; c.nclips = 0; c.logits = logits; c.softmax = softmax; c.softmax_mode = softmax_mode; c.hist = hist;
+      c.t_ld = 0; c.tracing = false;
+      const uint32_t team = warp >> 2, ttid = tid & 127;
+      const uint32_t tmem_q = tmem + ((uint32_t)(c.q * 32) << 16) + team * kSlotCols;
+      const uint32_t bar_full = bars + 8 * team, bar_empty = bars + 32 + 8 * team;
+      const uint32_t total = (uint32_t)(J.nbc + 1) * kUnits;
+      c.taddr = tmem_q;
+#pragma unroll 1
+      for (uint32_t gpos = team; gpos < total; gpos += kSlots) {
+        const int it = (int)(gpos / kUnits), pos = (int)(gpos - (uint32_t)it * kUnits);
+        const Unit U = c_sched[pos];
+        mbar_wait(bar_full, (gpos >> 2) & 1);                  // the unit's MMAs (and every earlier one) have completed
+        tc_fence_after();
+        const bool stamp = TRACE && trace && it == 1 && ttid == 0;
+        if (stamp) trace[4 * pos + 2] = clock64();
+        if (TRACE) c.tracing = stamp && pos == kPosTranspose;  // fine stamps of one unit: [4 kUnits] last ld landed, [+1] stored, [+2] fenced
+        if (U.lag ? it > 0 : it < J.nbc) {
+          if (U.kind == DN) {
+            if (c.q == 0) {
+              c.clip0 = J.batch(it - 1) * NC;
+              c.nclips = (int)min((long long)NC, J.n - c.clip0);
+              run_dense(c);
+            }
+          } else {
+            epilogue_conv(c, U);
+          }
+        }
+        if (stamp && c.tracing) { trace[4 * kUnits] = c.t_ld; trace[4 * kUnits + 1] = clock64(); }
+        if (pos == kPosTranspose && it + 1 < J.nbc) transpose_in(smem, J, it + 1, bar_raw, (int)ttid);
+        fence_async_smem();   // this thread's shared-memory stores -> visible to the MMAs that will read them
+        tc_fence_before();
+        if (stamp && c.tracing) trace[4 * kUnits + 2] = clock64();
+        mbar_arrive(bar_empty);
+        if (stamp) trace[4 * pos + 3] = clock64();
+      }
     }
-  } else if (J.nbc > 0) {
-    DevCtx c;
-    c.smem = smem; c.lane = lane; c.q = warp & 3; c.g = warp >> 2;
-    c.clip0 = 0; c.nclips = 0; c.logits = logits; c.softmax = softmax; c.softmax_mode = softmax_mode; c.hist = hist;
-    const uint32_t tmem_q = tmem + ((uint32_t)(c.q * 32) << 16);
-    for (int it = 0; it <= J.nbc; it++) DrainAll<0>::go(J, B, c, tmem_q, it, tid);
   }
   tc_fence_before();
   __syncthreads();
@@ -255,7 +291,11 @@ nnom_q7_umma_kernel(const uint8_t *image, const int8_t *net_in, long long n, int
 
 // ---- host side -----------------------------------------------------------------------------------------------------------
 cudaError_t nnom_umma_configure(void) {
-  return cudaFuncSetAttribute(nnom_q7_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+  cudaError_t e = cudaMemcpyToSymbol(c_sched, kSched, sizeof(kSched));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(nnom_q7_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(nnom_q7_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
 }
 
 // builds the weight image of k2_umma_plan.h from the five layers and uploads it; *out_image is a device pointer
@@ -276,11 +316,14 @@ int nnom_umma_upload(const int8_t *const w[5], const int8_t *const b[5], const i
 }
 
 cudaError_t launch_nnom_q7_umma(const uint8_t *image, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax, int softmax_mode,
-                                int *class_counts, int sm_count, cudaStream_t stream) {
+                                int *class_counts, int sm_count, cudaStream_t stream, long long *trace) {
   if (n <= 0) return cudaSuccess;
   const long long nb = (n + NC - 1) / NC;
   const unsigned ctas = (unsigned)(nb < (long long)sm_count ? nb : (long long)sm_count);
-  nnom_q7_umma_kernel<<<ctas, kThreads, SMEM_BYTES, stream>>>(image, net_in, n, logits, softmax, softmax_mode, class_counts);
+  if (trace)
+    nnom_q7_umma_kernel<true><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, net_in, n, logits, softmax, softmax_mode, class_counts, trace);
+  else
+    nnom_q7_umma_kernel<false><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, net_in, n, logits, softmax, softmax_mode, class_counts, nullptr);
   count_launch();
   return cudaGetLastError();
 }

@@ -228,6 +228,8 @@ int edison_debug_sqrt_q31(const int32_t *in, size_t n, int32_t *out);
  * exact Newton path on the device, and a 64-bit checksum of the exact results */
 int edison_debug_mag_sweep(uint32_t lo, uint32_t hi, unsigned long long *mismatches,
                            unsigned long long *checksum);
+/* K2 with clock64() stamps per schedule unit of block 0's second batch (d_trace: 96 int64 on the device; tools/k2_trace.py) */
+int edison_debug_k2_trace_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, long long *d_trace, void *stream);
 /* the round-1 mma.sync build of K2, kept only so that tools/k2_time.py can time the two tensor paths side by side */
 int edison_debug_infer_q7_legacy_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, void *stream);
 

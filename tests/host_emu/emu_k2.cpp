@@ -4,7 +4,7 @@
 // unit order as the CUDA kernel (nnom_q7_umma.cu) -- on a byte array standing in for shared memory and an int32 array
 // standing in for TMEM.  An MMA is emulated with the descriptor addressing that tools/ubench/umma_probe.cu verified on a
 // B200 (A[m][k] = smem[start + (m / 8) * 128 + (m % 8) * 16 + (k / 16) * LBO + k % 16]).  `eager` moves every unit's MMAs in
-// front of the previous unit's epilogue, the other extreme of what the hardware's asynchrony allows, so that a
+// front of the epilogues of the three units before it, the other extreme of what the slot ring allows, so that a
 // write-after-read hazard between an epilogue and MMAs already in flight would show as a mismatch in one of the two orders.
 // It exists to check index arithmetic against the oracle in a container without a GPU; it is not part of
 // libedison_b200.so and never produces results: the -m gpu parity tests run the real kernel.
@@ -27,14 +27,19 @@ struct Emu {
   std::vector<int32_t> tmem;   // [128 lanes][512 columns]
   Emu() : smem(SMEM_BYTES + 4096, 0xA5), tmem(128 * 512, 0x5a5a5a5a) {}
 
+  // one MMA, decoded from what the kernel hands to tcgen05.mma (descriptor low words, instruction descriptor)
   void mma(const MmaOp &op, int slot) {
+    const uint32_t a_lo = desc_lo(op.a_off, op.a_lbo), b_lo = desc_lo(op.b_off, op.b_lbo), idesc = idesc_i8(op.n);
+    const uint32_t a_off = (a_lo & 0x3fff) << 4, a_lbo = ((a_lo >> 16) & 0x3fff) << 4;
+    const uint32_t b_off = (b_lo & 0x3fff) << 4, b_lbo = ((b_lo >> 16) & 0x3fff) << 4;
+    const uint32_t n = ((idesc >> 17) & 0x3f) << 3, col = op.col, acc = op.acc;
     for (int m = 0; m < 128; m++)
-      for (uint32_t n = 0; n < op.n; n++) {
-        int32_t &d = tmem[m * 512 + slot * 256 + op.col + n];
-        int32_t s = op.acc ? d : 0;
+      for (uint32_t j = 0; j < n; j++) {
+        int32_t &d = tmem[m * 512 + slot * kSlotCols + col + j];
+        int32_t s = acc ? d : 0;
         for (int k = 0; k < 32; k++) {
-          const uint32_t aa = op.a_off + (m / 8) * 128 + (m % 8) * 16 + (k / 16) * op.a_lbo + (k % 16);
-          const uint32_t ba = op.b_off + (n / 8) * 128 + (n % 8) * 16 + (k / 16) * op.b_lbo + (k % 16);
+          const uint32_t aa = a_off + (m / 8) * 128 + (m % 8) * 16 + (k / 16) * a_lbo + (k % 16);
+          const uint32_t ba = b_off + (j / 8) * 128 + (j % 8) * 16 + (k / 16) * b_lbo + (k % 16);
           s += (int)(int8_t)smem[aa] * (int)(int8_t)smem[ba];
         }
         d = s;
@@ -51,7 +56,7 @@ struct Ctx {
   int softmax_mode;
   long long *hist;
   void ld16(uint32_t col, uint32_t (&v)[16]) {
-    for (int j = 0; j < 16; j++) v[j] = (uint32_t)e->tmem[(q * 32 + lane) * 512 + slot * 256 + col + j];
+    for (int j = 0; j < 16; j++) v[j] = (uint32_t)e->tmem[(q * 32 + lane) * 512 + slot * kSlotCols + col + j];
   }
   void ld_wait() {}
   void st16(uint32_t off, Vec16 v) { memcpy(&e->smem[off], &v, 16); }
@@ -75,41 +80,33 @@ void transpose_in(Emu &E, const int8_t *net_in, long long n, long long batch) {
     }
 }
 
-template <int POS> void run_mma(Emu &E, bool head, bool tail) {
-  constexpr Unit u = kSched[POS];
-  if (!(u.lag ? tail : head)) return;
-  for_each_mma<POS>([&](const MmaOp &op) { E.mma(op, POS & 1); });
+void run_mma(Emu &E, int pos, long long gpos, bool head, bool tail) {
+  const Unit U = kSched[pos];
+  if (!(U.lag ? tail : head)) return;
+  for (int m = 0; m < mma_count(U); m++) E.mma(mma_op(U, m), (int)(gpos & (kSlots - 1)));
 }
 
-template <int POS> void run_epi(Emu &E, bool head, bool tail, const int8_t *net_in, long long n, long long batch_of_it, long long next_batch,
-                                int8_t *logits, int8_t *softmax, int mode, long long *hist) {
-  constexpr Unit u = kSched[POS];
-  if (u.lag ? tail : head) {
-    for (int w = 0; w < kEpiWarps; w++)
+void run_epi(Emu &E, int pos, long long gpos, bool head, bool tail, const int8_t *net_in, long long n, long long batch_of_it, long long next_batch,
+             int8_t *logits, int8_t *softmax, int mode, long long *hist) {
+  const Unit U = kSched[pos];
+  if (U.lag ? tail : head) {
+    for (int q = 0; q < 4; q++)   // the four warps of the slot's team
       for (int lane = 0; lane < 32; lane++) {
         Ctx c;
-        c.e = &E; c.slot = POS & 1; c.lane = lane; c.q = w & 3; c.g = w >> 2;
-        const long long b = u.lag ? batch_of_it - 1 : batch_of_it;   // single-CTA emulation: consecutive batches
+        c.e = &E; c.slot = (int)(gpos & (kSlots - 1)); c.lane = lane; c.q = q; c.g = 0;
+        const long long b = U.lag ? batch_of_it - 1 : batch_of_it;   // single-CTA emulation: consecutive batches
         c.clip0 = b * NC;
         c.nclips = (int)((n - c.clip0) < NC ? (n - c.clip0) : NC);
         c.logits = logits; c.softmax = softmax; c.softmax_mode = mode; c.hist = hist;
-        epilogue<POS>(c);
+        if (U.kind == DN) {
+          if (q == 0) run_dense(c);
+        } else {
+          epilogue_conv(c, U);
+        }
       }
   }
-  if (POS == kPosTranspose && next_batch >= 0) transpose_in(E, net_in, n, next_batch);
+  if (pos == kPosTranspose && next_batch >= 0) transpose_in(E, net_in, n, next_batch);
 }
-
-template <int POS> struct Runner {
-  static void go(Emu &E, bool eager, bool head, bool tail, const int8_t *net_in, long long n, long long b, long long nb, int8_t *logits,
-                 int8_t *softmax, int mode, long long *hist) {
-    // lazy: MMA(p) epi(p);  eager: MMA(p + 1) is issued before epi(p) (it only had to wait for epi(p - 1))
-    if (!eager) run_mma<POS>(E, head, tail);
-    else if (POS == 0) { run_mma<0>(E, head, tail); run_mma<1>(E, head, tail); }
-    else if (POS + 1 < kUnits) run_mma<(POS + 1 < kUnits ? POS + 1 : 0)>(E, head, tail);
-    run_epi<POS>(E, head, tail, net_in, n, b, head && b + 1 < nb ? b + 1 : -1, logits, softmax, mode, hist);
-    if constexpr (POS + 1 < kUnits) Runner<POS + 1>::go(E, eager, head, tail, net_in, n, b, nb, logits, softmax, mode, hist);
-  }
-};
 
 }  // namespace
 
@@ -126,14 +123,25 @@ extern "C" int emu_k2_run(const char *blob_path, const int8_t *net_in, long long
   Emu E;
   build_image(E.smem.data(), w, b, rs, ls);
   if (hist) memset(hist, 0, 10 * sizeof(long long));
+  int total_mma = 0;
+  for (int p = 0; p < kUnits; p++) total_mma += mma_count(kSched[p]);
+  if (total_mma != kMmaPerIter) { fprintf(stderr, "emu_k2_run: kMmaPerIter is %d, the schedule has %d\n", kMmaPerIter, total_mma); return -1; }
   const long long nb = (n + NC - 1) / NC;
   if (nb == 0) return 0;
   transpose_in(E, net_in, n, 0);
-  for (long long it = 0; it <= nb; it++) {
+  // lazy: MMA(u) right before epilogue(u).  eager: the issuing thread runs as far ahead as the slot ring lets it, i.e. the MMAs of
+  // unit u + 3 execute before the epilogue of unit u (they only had to wait for the epilogue of u - 1).
+  const long long total = (nb + 1) * kUnits;
+  const int ahead = eager ? kSlots - 1 : 0;
+  long long issued = 0;
+  for (long long u = 0; u < total; u++) {
+    for (; issued <= u + ahead && issued < total; issued++) {
+      const long long it = issued / kUnits;
+      run_mma(E, (int)(issued % kUnits), issued, it < nb, it > 0);
+    }
+    const long long it = u / kUnits;
     const bool head = it < nb, tail = it > 0;
-    // in the eager order the first unit of the next iteration was already issued with the last epilogue of this one;
-    // the emulation restarts each iteration (the slot discipline makes iterations independent at this boundary)
-    Runner<0>::go(E, eager != 0, head, tail, net_in, n, it, nb, logits, softmax, mode, hist);
+    run_epi(E, (int)(u % kUnits), u, head, tail, net_in, n, it, head && it + 1 < nb ? it + 1 : -1, logits, softmax, mode, hist);
   }
   return 0;
 }
