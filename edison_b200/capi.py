@@ -51,7 +51,6 @@ def lib():
         L.edison_sync.argtypes = [vp]
         L.edison_kws_counts_dev.argtypes = [vp, sz, sz, vp, vp, vp, vp, vp]
         L.edison_infer_q7_counts_dev.argtypes = [vp, sz, vp, vp, vp, vp]
-        L.edison_debug_infer_q7_legacy_dev.argtypes = [vp, sz, vp, vp, vp]
         L.edison_mfccf_create.argtypes = [ci, ci, ci, ci, ctypes.c_float, ctypes.POINTER(vp)]
         L.edison_mfccf_delete.argtypes = [vp]
         L.edison_mfccf_delete.restype = None
@@ -80,6 +79,8 @@ def lib():
         L.edison_streams_close.restype = None
         L.edison_streams_push_hop.argtypes = [vp, vp, vp, vp, vp]
         L.edison_streams_push_hop_dev.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.edison_streams_submit_hop.argtypes = [vp, vp]
+        L.edison_streams_collect_hop.argtypes = [vp, vp, vp, vp]
         L.edison_streams_set_incremental.argtypes = [vp, ci]
         L.edison_streams_hops.argtypes = [vp]
         L.edison_streams_hops.restype = ctypes.c_ulonglong
@@ -275,7 +276,7 @@ class Streams:
     push_hop(pcm[n,1024]) -> (softmax int8 [n,10], filt float32 [n,10], detect int32 [n]); detect is the class index when
     the filtered maximum exceeds 0.5, -1 when it does not, -2 while the 31-row window is still filling."""
 
-    def __init__(self, n, incremental=True):
+    def __init__(self, n, incremental=False):
         self.n = int(n)
         self._h = ctypes.c_void_p()
         check(lib().edison_streams_open(self.n, ctypes.byref(self._h)), "edison_streams_open")
@@ -308,6 +309,21 @@ class Streams:
         fl = np.empty((self.n, N_CLASSES), dtype=np.float32)
         dt = np.empty(self.n, dtype=np.int32)
         check(lib().edison_streams_push_hop(self._h, _p(pcm), _p(sm), _p(fl), _p(dt)), "edison_streams_push_hop")
+        return sm, fl, dt
+
+    def submit_hop(self, pcm):
+        """pipelined form: start hop h + 1 while hop h computes (at most two in flight); pcm must stay alive until collected"""
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16).reshape(-1)
+        if pcm.size != self.n * FRAME_LEN:
+            raise ValueError("a hop is %d x 1024 samples, got %d" % (self.n, pcm.size))
+        check(lib().edison_streams_submit_hop(self._h, _p(pcm)), "edison_streams_submit_hop")
+        return pcm
+
+    def collect_hop(self):
+        sm = np.empty((self.n, N_CLASSES), dtype=np.int8)
+        fl = np.empty((self.n, N_CLASSES), dtype=np.float32)
+        dt = np.empty(self.n, dtype=np.int32)
+        check(lib().edison_streams_collect_hop(self._h, _p(sm), _p(fl), _p(dt)), "edison_streams_collect_hop")
         return sm, fl, dt
 
     def window(self, i):

@@ -234,7 +234,7 @@ static int mfcc_dev(const int16_t *d_pcm, size_t n_clips, size_t fpc, size_t str
   if (d_mfcc && (reinterpret_cast<uintptr_t>(d_mfcc) & 15u)) return fail(EDISON_E_ARG, "d_mfcc must be 16-byte aligned");
   MfccLaunch L;
   L.pcm = d_pcm; L.n_clips = (long long)n_clips; L.frames_per_clip = (int)fpc; L.clip_stride = (long long)stride;
-  L.mfcc = d_mfcc; L.net_in = d_net_in; L.tables = g.d_tables;
+  L.mfcc = d_mfcc; L.net_in = d_net_in; L.net_in_stride = EDISON_N_COEFF; L.tables = g.d_tables;
   CU(launch_mfcc_q15(L, g.sm_count, st));
   return EDISON_OK;
 }
@@ -242,7 +242,9 @@ static int mfcc_dev(const int16_t *d_pcm, size_t n_clips, size_t fpc, size_t str
 static int infer_dev(const int8_t *d_in, size_t n, int8_t *d_logits, int8_t *d_softmax, int32_t *d_counts, cudaStream_t st) {
   if (!n) return EDISON_OK;
   if (!d_in || (!d_logits && !d_softmax && !d_counts)) return fail(EDISON_E_ARG, "null pointer");
-  CU(launch_nnom_q7(g.d_model, d_in, (long long)n, d_logits, d_softmax, g.softmax_mode, g.sm_count, st, d_counts));
+  K2Launch k{};
+  k.net_in = d_in; k.n = (long long)n; k.logits = d_logits; k.softmax = d_softmax; k.softmax_mode = g.softmax_mode; k.class_counts = d_counts;
+  CU(launch_nnom_q7(g.d_model, k, g.sm_count, st));
   return EDISON_OK;
 }
 
@@ -546,17 +548,9 @@ int edison_debug_k2_trace_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits
   if (!g.ready) return fail(EDISON_E_NOINIT, "edison_init() first");
   if (!d_trace) return fail(EDISON_E_ARG, "null trace buffer");
   DeviceScope device_scope_;
-  CU(launch_nnom_q7(g.d_model, d_net_in, (long long)n, d_logits, d_softmax, g.softmax_mode, g.sm_count,
-                    stream ? (cudaStream_t)stream : g.slot[0].stream, nullptr, d_trace));
-  return EDISON_OK;
-}
-
-// the round-1 mma.sync kernel, for A/B timing of the two tensor paths (tools/k2_time.py); device pointers only
-int edison_debug_infer_q7_legacy_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, void *stream) {
-  if (!g.ready) return fail(EDISON_E_NOINIT, "edison_init() first");
-  DeviceScope device_scope_;
-  CU(launch_nnom_q7_legacy(g.d_model, d_net_in, (long long)n, d_logits, d_softmax, g.softmax_mode, g.sm_count,
-                           stream ? (cudaStream_t)stream : g.slot[0].stream));
+  K2Launch k{};
+  k.net_in = d_net_in; k.n = (long long)n; k.logits = d_logits; k.softmax = d_softmax; k.softmax_mode = g.softmax_mode; k.trace = d_trace;
+  CU(launch_nnom_q7(g.d_model, k, g.sm_count, stream ? (cudaStream_t)stream : g.slot[0].stream));
   return EDISON_OK;
 }
 

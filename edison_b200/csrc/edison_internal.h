@@ -15,7 +15,8 @@ struct MfccLaunch {
   int frames_per_clip;
   long long clip_stride;       // samples
   int16_t *mfcc;               // device [n_clips*frames_per_clip][32] or nullptr
-  int8_t *net_in;              // device [n_clips*frames_per_clip][13] or nullptr
+  int8_t *net_in;              // device: 13 int8 per frame at net_in + frame * net_in_stride, or nullptr
+  long long net_in_stride;     // bytes between consecutive frames' rows: 13 = packed [n_frames][13]; 403 = one row of n windows
   const MfccTables *tables;    // device
 };
 // fills the twiddle / split / sqrt-exception tables (formula-generated, checksummed against the
@@ -30,22 +31,28 @@ int nnom_load(const char *blob_path, NnomModel **out_dev_model, int *in_scale, i
               char *err, size_t errlen);
 void nnom_free(NnomModel *m);
 cudaError_t nnom_configure(void);
-// K2 (tcgen05 kernel, nnom_q7_umma.cu).  class_counts: optional device int32[10], += number of clips per first-maximum logit class
-cudaError_t launch_nnom_q7(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits,
-                           int8_t *softmax, int softmax_mode, int sm_count, cudaStream_t stream, int *class_counts = nullptr,
-                           long long *trace = nullptr);
-cudaError_t launch_nnom_q7_legacy(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax,
-                                  int softmax_mode, int sm_count, cudaStream_t stream);   // round-1 mma.sync kernel (A/B timing only)
+// K2 (tcgen05 kernel, nnom_q7_umma.cu)
+struct K2Launch {
+  const int8_t *net_in;     // device [n][403]; row r of window i is at net_in + i * 403 + ((r + row0) % 31) * 13
+  long long n;
+  int8_t *logits, *softmax; // device [n][10], either may be null
+  int softmax_mode;
+  int *class_counts;        // optional device int32[10], += number of clips per first-maximum logit class
+  int row0;                 // 0 for plain batches; the streaming windows are rings of rows (stream.cu)
+  float *filt;              // optional streaming post-processing fused into the dense epilogue (app.c:336-350):
+  int32_t *detect;          //   filt[n][10] moving average (in / out), detect[n] = spotted class or -1
+  long long *trace;         // debug: clock64() stamps of block 0 (edison_debug_k2_trace_dev)
+};
+cudaError_t launch_nnom_q7(const NnomModel *model, const K2Launch &k, int sm_count, cudaStream_t stream);
 cudaError_t nnom_umma_configure(void);
 int nnom_umma_upload(const int8_t *const w[5], const int8_t *const b[5], const int rs[5], const int ls[5], uint8_t **out_image);
-cudaError_t launch_nnom_q7_umma(const uint8_t *image, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax, int softmax_mode,
-                                int *class_counts, int sm_count, cudaStream_t stream, long long *trace = nullptr);
+cudaError_t launch_nnom_q7_umma(const uint8_t *image, const K2Launch &k, int sm_count, cudaStream_t stream);
 
 // incremental sliding-window inference (one new row per layer and hop); state rings live in one device allocation
 struct NnomIncrState { int8_t *c1, *p1, *c2, *p2, *c3; };
 size_t nnom_incr_state_bytes(long long n_streams);
 void nnom_incr_state_bind(NnomIncrState *st, int8_t *base, long long n_streams);
-cudaError_t launch_nnom_q7_incremental(const NnomModel *model, const int8_t *window, const NnomIncrState &st, long long n,
+cudaError_t launch_nnom_q7_incremental(const NnomModel *model, const int8_t *window, int row0, const NnomIncrState &st, long long n,
                                        long long newest_row, int8_t *logits, int8_t *softmax, int softmax_mode, int sm_count,
                                        cudaStream_t stream);
 

@@ -222,7 +222,8 @@ K2_HD void softmax_q7(const int8_t *in, int8_t *out, int mode) {
 //   c.ld16(col, v)   : this thread's lane of TMEM columns col..col+15 of the unit's slot;  c.ld_wait() before using v
 //   c.st16(off, Vec16) : 16-byte shared-memory store;  c.par(i) / c.par4(i): int32 parameter(s) i (same for all lanes)
 //   c.lane (= clip), c.q (lane quarter = pixel within an M = 128 tile);  dense only: c.clip0 (first clip of the batch),
-//   c.nclips, c.logits, c.softmax (global, may be null), c.softmax_mode, c.count(cls) (class histogram hook)
+//   c.nclips, c.logits, c.softmax (global, may be null), c.softmax_mode, c.count(cls) (class histogram hook),
+//   c.filt (null or the streaming filter state) with c.post(clip, softmax)
 // One warp per lane quarter drains a whole unit: lean loops (a job = 16 accumulator columns -> one 16-byte store is ~75
 // instructions; evaluating a generic job descriptor per job tripled that and the epilogue is latency bound).
 struct JobParams { uint32_t col_e, col_o, seed, out; };
@@ -303,11 +304,13 @@ template <class Ctx> K2_HD void run_dense(Ctx &c) {
     if (c.logits)
 #pragma unroll
       for (int i = 0; i < 10; i++) c.logits[clip * 10 + i] = lg[i];
-    if (c.softmax) {
+    if (c.softmax || c.filt) {
       int8_t sm[10];
       softmax_q7(lg, sm, c.softmax_mode);
+      if (c.softmax)
 #pragma unroll
-      for (int i = 0; i < 10; i++) c.softmax[clip * 10 + i] = sm[i];
+        for (int i = 0; i < 10; i++) c.softmax[clip * 10 + i] = sm[i];
+      if (c.filt) c.post(clip, sm);   // streaming: moving average, argmax, threshold (app.c:336-350)
     }
     int best = 0;   // first maximum of the logits: the class the firmware's arm_max would report on them
 #pragma unroll
@@ -329,6 +332,12 @@ K2_HD Vec16 input_chunk(const uint32_t (&w)[4], uint32_t a) {
   v.z = (w[2] >> sh) | (w[3] << (32 - sh));
   v.w = w[3] >> sh;
   return v;
+}
+// byte offset of input row `row` of clip `clip` in raw [clip][403]; windows of the streaming path are rings of rows: logical row r
+// lives at physical row (r + row0) % 31
+K2_HD uint32_t raw_offset(int clip, int row, int row0) {
+  const int phys = row + row0 >= 31 ? row + row0 - 31 : row + row0;
+  return (uint32_t)clip * kNetIn + (uint32_t)phys * 13;
 }
 K2_HD uint32_t c0_offset(int row, int clip) { return OFF_C0 + (uint32_t)(row & 1) * C0_HALF + (uint32_t)(row >> 1) * PX + (uint32_t)clip * 16; }
 constexpr int kInRowsUsed = 28;   // conv rows 24..26 only feed the pooled row that conv2's pooling drops (and row 26 nothing)

@@ -120,7 +120,7 @@ __device__ __forceinline__ void group_tail(const MfccLaunch &P, const MfccTables
   if (P.net_in) {  // 8 frames x 13 int8 (mfccToNetInput)
     for (int idx = lane; idx < kGroup * kNCoeff; idx += 32) {
       const int fr = idx / kNCoeff, c = idx - fr * kNCoeff;
-      if (f0 + fr < n_frames) P.net_in[(f0 + fr) * kNCoeff + c] = (int8_t)net_input_q7(out[32 * fr + c], T);
+      if (f0 + fr < n_frames) P.net_in[(f0 + fr) * P.net_in_stride + c] = (int8_t)net_input_q7(out[32 * fr + c], T);
     }
   }
   __syncwarp();

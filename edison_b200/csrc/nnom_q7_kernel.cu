@@ -1,25 +1,21 @@
-// nnom_q7_kernel.cu -- K2: the int8 NNoM keyword-spotting net (firmware/src/ai/nnom/kws_nnom/weights.h:138-161)
-// over a batch of 31x13 inputs, as implicit GEMMs on the int8 tensor cores.
+// nnom_q7_kernel.cu -- the model loader of K2 and the INCREMENTAL sliding-window variant of the int8 NNoM keyword-spotting net
+// (firmware/src/ai/nnom/kws_nnom/weights.h:138-161).
 //
-// Replaces model_run (firmware/src/ai/nnom/src/core/nnom.c:996-1041) for this graph:
-//   Input(31,13,1) -> Conv 16@5x5 -> ReLU -> MaxPool(2,1) -> Conv 32@3x3 -> ReLU -> MaxPool(2,1)
-//   -> Conv 64@3x3 -> ReLU -> Conv 32@3x3 -> ReLU -> Dense 10 -> Softmax
-// with the arithmetic of arm_convolve_HWC_q7_{basic,fast}_nonsquare / local_convolve_HWC_q7_nonsquare
-// (nnom_local.c:425-484), local_maxpool_q7_HWC (nnom_local.c:117-160), arm_fully_connected_q7_opt
-// (weights de-interleaved at conversion time) and the three softmax variants:
-//   out = SSAT8( ((bias << bias_lshift) + (1 << (out_rshift-1)) + sum in*w) >> out_rshift )
-// int32 accumulation is exact and order independent (|acc| < 2^24), so any MMA tiling gives the
-// reference's bits.
+// K2 itself -- the whole 31x13 window through the net -- is nnom_q7_umma.cu (tcgen05.mma.kind::i8, TMEM accumulators).  This file
+// keeps (a) nnom_load: blob -> device model + the tcgen05 kernel's weight image, and (b) nnom_q7_incr_kernel, the opt-in
+// streaming mode that advances one new row per layer and hop from HBM rings.  (b) still issues
+// mma.sync.m16n8k32.s8 (SASS IMMA) on 3-row images; since the tcgen05 kernel the full window is FASTER than it (100,000 streams:
+// 0.21 ms against 0.40 ms per hop), so edison_streams_* default to the full window and (b) is kept for its ring design.
 //
-// Layout: a CTA keeps a tile of 16 clips in shared memory through all layers (activations never
-// touch HBM: 403 B in, 10 + 10 B out per clip).  Every layer is D[M x N] = A[M x K] * B[K x N] with
-//   M = output pixels of the 16 clips (for the pooled layers: row g / g+8 of an m16 tile are the two
-//       conv rows under one pooled pixel, so max-pool happens inside a thread's accumulators),
-//   K = (ky, kx, c) in the reference's O,H,W,I weight order, N = output channels,
-// issued as mma.sync.m16n8k32.s8.s8.s32.  A fragments are 32-bit loads straight from the HWC
-// activation buffers (implicit im2col; C = 32 / 64 buffers are XOR-swizzled per pixel so those loads
-// are bank-conflict free), B fragments are pre-packed in fragment order at model load.
-// Epilogue, fused: >> out_rshift, SSAT8, ReLU, (2x1 max pool), int8 store in the next layer's layout.
+// Arithmetic of both: arm_convolve_HWC_q7_{basic,fast}_nonsquare / local_convolve_HWC_q7_nonsquare (nnom_local.c:425-484),
+// local_maxpool_q7_HWC (nnom_local.c:117-160), arm_fully_connected_q7_opt (weights de-interleaved at conversion time) and the
+// three softmax variants:   out = SSAT8( ((bias << bias_lshift) + (1 << (out_rshift-1)) + sum in*w) >> out_rshift )
+// int32 accumulation is exact and order independent (|acc| < 2^24), so any MMA tiling gives the reference's bits.
+//
+// Incremental kernel layout: every layer is D[M x N] = A[M x K] * B[K x N] with M = output pixels of 16 streams, K = (ky, kx, c) in
+// the reference's O,H,W,I weight order, N = output channels.  A fragments are 32-bit loads straight from HWC activation buffers
+// (implicit im2col; C = 32 / 64 buffers are XOR-swizzled per pixel so those loads are bank-conflict free), B fragments are
+// pre-packed in fragment order at model load.  Epilogue, fused: >> out_rshift, SSAT8, ReLU, int8 store in the next layer's layout.
 #include <stddef.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -56,16 +52,6 @@ constexpr int kNetThreads = 256;
 constexpr int kNetWarps = kNetThreads / 32;
 constexpr int kInStride = EDISON_NET_IN;   // 403: a tile's 16 inputs stay contiguous, exactly as they lie in HBM (conv1 fetches unaligned)
 constexpr int kPix1 = 13 * 9, kPix2 = 5 * 7, kPix3 = 3 * 5, kPix4 = 3;   // pixels per clip after each conv(+pool)
-constexpr int kRegionX = kNC * kPix2 * kC2;   // holds: input [16][416] | act2 [16][35][32] | act4 [16][3][32]
-constexpr int kRegionY = kNC * kPix1 * kC1;   // holds: act1 [16][117][16] | act3 [16][15][64] | logits [16][16]
-static_assert(kRegionX >= kNC * kInStride + 64 && kRegionY >= kNC * kPix3 * kC3, "regions");
-
-struct NetSmem {
-  NnomModel M;
-  alignas(16) int8_t X[kRegionX];
-  alignas(16) int8_t Y[kRegionY];
-};
-
 __device__ __forceinline__ void mma_s8(int (&d)[4], const uint32_t (&a)[4], uint2 b) {
   asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
@@ -161,150 +147,6 @@ __device__ __forceinline__ uint32_t ld_unaligned32(const uint32_t *words, int by
   return __funnelshift_r(words[wa], words[wa + 1], (byte_addr & 3) * 8);
 }
 
-// Two tiles per trip: the twelve input fetches of both are issued before the first MMA (one tile at a time is a chain
-// fetch -> funnel shift -> MMA -> epilogue with nothing to overlap, and the CTA has only 8 warps).
-__device__ __forceinline__ void conv1_mma(const int8_t *__restrict__ in, int8_t *__restrict__ out, const uint2 *__restrict__ frag,
-                                          const int *__restrict__ seed, int rs, int nclips) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
-  const int rows_total = nclips * kPix1;   // pooled pixels
-  const int n_tiles = (rows_total + 7) / 8;
-  const uint32_t *__restrict__ inw = reinterpret_cast<const uint32_t *>(in);
-  uint2 fr[4];
-#pragma unroll
-  for (int i = 0; i < 4; i++) fr[i] = frag[i * 32 + lane];
-  const int sd[4] = {seed[2 * t], seed[2 * t + 1], seed[8 + 2 * t], seed[8 + 2 * t + 1]};
-  for (int tile = warp; tile < n_tiles; tile += 2 * kNetWarps) {
-    int q0[2], base[2];
-    bool v0[2];
-#pragma unroll
-    for (int u = 0; u < 2; u++) {
-      q0[u] = (tile + u * kNetWarps) * 8 + g;
-      v0[u] = q0[u] < rows_total;
-      const int qa = v0[u] ? q0[u] : 0;
-      const int ca = qa / kPix1, ra = qa - ca * kPix1, yp = ra / 9, x = ra - yp * 9;
-      base[u] = ca * kInStride + (2 * yp) * kInW + x;   // byte address of in[2 yp][x]; row g + 8 is one row down
-    }
-    uint32_t a[2][2][4];
-#pragma unroll
-    for (int u = 0; u < 2; u++)
-#pragma unroll
-      for (int ks = 0; ks < 2; ks++)
-#pragma unroll
-        for (int h = 0; h < 2; h++) {
-          const int ky = 4 * ks + 2 * h + (t >> 1), kx0 = 4 * (t & 1);
-          if (4 * ks + 2 * h >= 5) {   // kernel rows 6, 7 (and 5, fetched beside row 4) have zero weights: nothing to fetch
-            a[u][ks][2 * h] = a[u][ks][2 * h + 1] = 0;
-          } else {
-            a[u][ks][2 * h] = ld_unaligned32(inw, base[u] + ky * kInW + kx0);
-            a[u][ks][2 * h + 1] = ld_unaligned32(inw, base[u] + (ky + 1) * kInW + kx0);
-          }
-        }
-#pragma unroll
-    for (int u = 0; u < 2; u++) {
-      int acc[2][4];
-#pragma unroll
-      for (int n = 0; n < 2; n++) {
-        acc[n][0] = acc[n][2] = sd[2 * n];
-        acc[n][1] = acc[n][3] = sd[2 * n + 1];
-      }
-#pragma unroll
-      for (int ks = 0; ks < 2; ks++) {
-        mma_s8(acc[0], a[u][ks], fr[ks * 2 + 0]);
-        mma_s8(acc[1], a[u][ks], fr[ks * 2 + 1]);
-      }
-      if (v0[u]) {
-#pragma unroll
-        for (int n = 0; n < 2; n++) {
-          const int lo = q7_relu(max(acc[n][0], acc[n][2]), rs), hi = q7_relu(max(acc[n][1], acc[n][3]), rs);
-          reinterpret_cast<uint16_t *>(out)[(q0[u] * kC1 + 8 * n + 2 * t) >> 1] = (uint16_t)(lo | (hi << 8));
-        }
-      }
-    }
-  }
-}
-
-__global__ void __launch_bounds__(kNetThreads, 2) nnom_q7_kernel(const NnomModel *model, const int8_t *net_in, long long n,
-                                                                  int8_t *logits, int8_t *softmax, int softmax_mode) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  NetSmem &S = *reinterpret_cast<NetSmem *>(smem_raw);
-  {
-    const int4 *src = reinterpret_cast<const int4 *>(model);
-    int4 *dst = reinterpret_cast<int4 *>(&S.M);
-    for (int i = threadIdx.x; i < (int)(sizeof(NnomModel) / 16); i += kNetThreads) dst[i] = src[i];
-  }
-  const NnomModel &M = S.M;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
-  const long long n_tiles = (n + kNC - 1) / kNC;
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const long long c0 = tile * kNC;
-    const int nclips = (int)min((long long)kNC, n - c0);
-    __syncthreads();   // previous tile's readers are done (and, first time, the model copy is visible)
-    // input: the tile's nclips x 403 bytes are contiguous in HBM and 16-byte aligned when the tile is full (16 x 403 = 403
-    // int4): two independent 128-bit loads per thread.  Bytes past a clip's end only ever meet zero weights.
-    {
-      const int8_t *src = net_in + c0 * EDISON_NET_IN;
-      const int bytes = nclips * EDISON_NET_IN;
-      if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
-        const int n16 = bytes >> 4;
-        int4 v[2];
-#pragma unroll
-        for (int it = 0; it < 2; it++) {
-          const int i = threadIdx.x + it * kNetThreads;
-          if (i < n16) v[it] = __ldg(reinterpret_cast<const int4 *>(src) + i);
-        }
-#pragma unroll
-        for (int it = 0; it < 2; it++) {
-          const int i = threadIdx.x + it * kNetThreads;
-          if (i < n16) reinterpret_cast<int4 *>(S.X)[i] = v[it];
-        }
-        for (int i = (n16 << 4) + threadIdx.x; i < bytes; i += kNetThreads) S.X[i] = src[i];
-      } else {
-        for (int i = threadIdx.x; i < bytes; i += kNetThreads) S.X[i] = src[i];
-      }
-    }
-    __syncthreads();
-    conv1_mma(S.X, S.Y, &M.f1[0][0][0], M.seed1, M.rs[0], nclips);                                          // -> act1 [13][9][16]
-    __syncthreads();
-    conv3x3_mma<9, kPix1, kC1, kC2, 5, 7, true, true, 1>(S.Y, S.X, &M.f2[0][0][0], M.seed2, M.rs[1], nclips);   // -> act2 [5][7][32]
-    __syncthreads();
-    conv3x3_mma<7, kPix2, kC2, kC3, 3, 5, false, true, 2>(S.X, S.Y, &M.f3[0][0][0], M.seed3, M.rs[2], nclips);  // -> act3 [3][5][64]
-    __syncthreads();
-    conv3x3_mma<5, kPix3, kC3, kC4, 1, 3, false, false, 4>(S.Y, S.X, &M.f4[0][0][0], M.seed4, M.rs[3], nclips); // -> act4 [1][3][32]
-    __syncthreads();
-    // Dense 96 -> 10 (nnom_dense.c:92-119): rows = clips, one m16 tile, two n8 tiles on warps 0 and 1
-    if (warp < 2) {
-      const uint32_t *aw = reinterpret_cast<const uint32_t *>(S.X);
-      const int r0 = g < nclips ? g : 0, r1 = g + 8 < nclips ? g + 8 : 0;
-      int acc[4];
-      acc[0] = acc[2] = M.seedd[8 * warp + 2 * t];
-      acc[1] = acc[3] = M.seedd[8 * warp + 2 * t + 1];
-#pragma unroll
-      for (int ks = 0; ks < 3; ks++) {
-        uint32_t a[4];
-        a[0] = aw[r0 * 24 + 8 * ks + t];     a[1] = aw[r1 * 24 + 8 * ks + t];
-        a[2] = aw[r0 * 24 + 8 * ks + 4 + t]; a[3] = aw[r1 * 24 + 8 * ks + 4 + t];
-        mma_s8(acc, a, M.fd[ks][warp][lane]);
-      }
-      const int rs = M.rs[4];
-#pragma unroll
-      for (int j = 0; j < 4; j++) {
-        const int clip = g + 8 * (j >> 1), col = 8 * warp + 2 * t + (j & 1);
-        if (clip < nclips && col < kDenseOut) {
-          const int8_t v = (int8_t)ssat8(acc[j] >> rs);
-          S.Y[clip * 16 + col] = v;
-          if (logits) logits[(c0 + clip) * kDenseOut + col] = v;
-        }
-      }
-    }
-    __syncthreads();
-    if (softmax && threadIdx.x < nclips) {
-      int8_t sm[kDenseOut];
-      softmax_q7(&S.Y[threadIdx.x * 16], sm, softmax_mode);
-      for (int i = 0; i < kDenseOut; i++) softmax[(c0 + threadIdx.x) * kDenseOut + i] = sm[i];
-    }
-  }
-}
-
 // ---- incremental sliding-window inference (app.c:706-719 advances the window one row per hop) ----------
 // A window that starts at global row s is  conv1 rows s..s+26 -> pool pairs (s+2i, s+2i+1) -> conv2 rows on pooled rows
 // (a, a+2, a+4), a = s+2i -> pool pairs (a, a+2), a = s+4j -> conv3 on (a, a+4, a+8) -> conv4 on c3[s], c3[s+4], c3[s+8].
@@ -380,7 +222,7 @@ __device__ __forceinline__ uint32_t max_s8x4(uint32_t a, uint32_t b) { return __
 
 // window: [n][403] after this hop's push (rows r-30..r).  r = index of the newest row (hop count - 1).
 __global__ void __launch_bounds__(kNetThreads, 2)
-nnom_q7_incr_kernel(const NnomModel *model, const int8_t *window, NnomIncrState st, long long n, long long r, int8_t *logits,
+nnom_q7_incr_kernel(const NnomModel *model, const int8_t *window, int row0, NnomIncrState st, long long n, long long r, int8_t *logits,
                     int8_t *softmax, int softmax_mode) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   IncrSmem &S = *reinterpret_cast<IncrSmem *>(smem_raw);
@@ -447,7 +289,7 @@ nnom_q7_incr_kernel(const NnomModel *model, const int8_t *window, NnomIncrState 
 #pragma unroll
       for (int it = 0; it < kInIter; it++) {
         const int i = tid + it * kNetThreads, s = i / 65, j = i - s * 65;
-        b[it] = s < ns ? window[(c0 + s) * EDISON_NET_IN + 26 * 13 + j] : (int8_t)0;
+        b[it] = s < ns ? window[(c0 + s) * EDISON_NET_IN + k2::raw_offset(0, 26 + j / 13, row0) + j % 13] : (int8_t)0;   // ring of rows
       }
 #pragma unroll
       for (int it = 0; it < kInIter; it++) {
@@ -539,13 +381,13 @@ void nnom_incr_state_bind(NnomIncrState *st, int8_t *base, long long n) {
   st->c3 = st->p2 + (size_t)n * kRowC2 * kDepthP2;
 }
 
-cudaError_t launch_nnom_q7_incremental(const NnomModel *model, const int8_t *window, const NnomIncrState &st, long long n,
+cudaError_t launch_nnom_q7_incremental(const NnomModel *model, const int8_t *window, int row0, const NnomIncrState &st, long long n,
                                        long long newest_row, int8_t *logits, int8_t *softmax, int softmax_mode, int sm_count,
                                        cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   const long long n_tiles = (n + kNC - 1) / kNC;
   long long ctas = n_tiles < (long long)sm_count * 2 ? n_tiles : (long long)sm_count * 2;
-  nnom_q7_incr_kernel<<<(unsigned)ctas, kNetThreads, sizeof(IncrSmem), stream>>>(model, window, st, n, newest_row, logits, softmax,
+  nnom_q7_incr_kernel<<<(unsigned)ctas, kNetThreads, sizeof(IncrSmem), stream>>>(model, window, row0, st, n, newest_row, logits, softmax,
                                                                                 softmax_mode);
   count_launch();
   return cudaGetLastError();
@@ -554,30 +396,16 @@ cudaError_t launch_nnom_q7_incremental(const NnomModel *model, const int8_t *win
 cudaError_t nnom_configure(void) {
   cudaError_t e = cudaFuncSetAttribute(nnom_q7_incr_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IncrSmem));
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(nnom_q7_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NetSmem));
-  if (e != cudaSuccess) return e;
   return nnom_umma_configure();
 }
 
 // weight image of the tcgen05 kernel (nnom_q7_umma.cu); one model per process, like the firmware
 static uint8_t *g_umma_image = nullptr;
 
-cudaError_t launch_nnom_q7(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax,
-                           int softmax_mode, int sm_count, cudaStream_t stream, int *class_counts, long long *trace) {
+cudaError_t launch_nnom_q7(const NnomModel *model, const K2Launch &kl, int sm_count, cudaStream_t stream) {
   (void)model;
   if (!g_umma_image) return cudaErrorNotReady;
-  return launch_nnom_q7_umma(g_umma_image, net_in, n, logits, softmax, softmax_mode, class_counts, sm_count, stream, trace);
-}
-
-// the round-1 mma.sync kernel: kept for tools/k2_time.py (A/B timing of the two tensor paths), not reachable from the C ABI
-cudaError_t launch_nnom_q7_legacy(const NnomModel *model, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax,
-                                  int softmax_mode, int sm_count, cudaStream_t stream) {
-  if (n <= 0) return cudaSuccess;
-  const long long n_tiles = (n + kNC - 1) / kNC;
-  long long ctas = n_tiles < (long long)sm_count * 2 ? n_tiles : (long long)sm_count * 2;
-  nnom_q7_kernel<<<(unsigned)ctas, kNetThreads, sizeof(NetSmem), stream>>>(model, net_in, n, logits, softmax, softmax_mode);
-  count_launch();
-  return cudaGetLastError();
+  return launch_nnom_q7_umma(g_umma_image, kl, sm_count, stream);
 }
 
 // ---- blob loader (tools/convert_nnom_weights.py) -> device model ----------------------------------------------------

@@ -78,6 +78,8 @@ struct DevCtx {
   int8_t *logits, *softmax;
   int softmax_mode;
   int *hist;        // shared-memory class histogram
+  float *filt;      // streaming post-processing (null: none)
+  int32_t *detect;
   long long t_ld;   // TRACE builds: clock64() when the last tcgen05.ld had landed
   bool tracing;
   __device__ __forceinline__ void ld16(uint32_t col, uint32_t (&v)[16]) {
@@ -97,12 +99,28 @@ struct DevCtx {
     return Int4{v.x, v.y, v.z, v.w};
   }
   __device__ __forceinline__ void count(int cls) { atomicAdd(&hist[cls], 1); }
+  // app.c:336-350: netOutFilt = 0.9 netOutFilt + (1.0 - 0.9) netOutFloat, evaluated in double (the literals are doubles, the
+  // firmware has no -fsingle-precision-constant) and stored as float; arm_max_f32 (first maximum); spotted when > 0.5
+  __device__ __forceinline__ void post(long long clip, const int8_t *sm) {
+    const double alpha = 0.9, beta = 1.0 - 0.9;
+    float best = 0.f;
+    int idx = 0;
+#pragma unroll
+    for (int i = 0; i < 10; i++) {
+      const double o = (double)(float)sm[i];
+      const float f = (float)__dadd_rn(__dmul_rn(alpha, (double)filt[clip * 10 + i]), __dmul_rn(beta, o));
+      filt[clip * 10 + i] = f;
+      if (i == 0 || f > best) { best = f; idx = i; }
+    }
+    if (detect) detect[clip] = best > 0.5f ? idx : -1;
+  }
 };
 
 struct Job {
   const uint8_t *image;
   const int8_t *net_in;
   long long n, nb;      // clips, batches
+  int row0;             // ring offset of the input rows (0 for plain batches)
   int nbc;              // batches of this CTA: blockIdx.x + k * gridDim.x, k < nbc
   bool aligned;         // net_in is 16-byte aligned: full batches come in by bulk copy
   __device__ __forceinline__ long long batch(int k) const { return (long long)blockIdx.x + (long long)k * gridDim.x; }
@@ -119,7 +137,7 @@ __device__ __forceinline__ void transpose_in(uint8_t *smem, const Job &J, int k,
 #pragma unroll 1
   for (int row = tid >> 5; row < kInRowsUsed; row += nthreads >> 5) {
     {
-      const uint32_t a = (uint32_t)clip * kNetIn + (uint32_t)row * 13;
+      const uint32_t a = raw_offset(clip, row, J.row0);
       uint32_t w[4];
       Vec16 v;
       if (bulk) {
@@ -130,7 +148,7 @@ __device__ __forceinline__ void transpose_in(uint8_t *smem, const Job &J, int k,
       } else {   // partial last batch or unaligned caller buffer: byte loads straight from HBM
         w[0] = w[1] = w[2] = w[3] = 0;
         if (clip < nclips) {
-          const uint8_t *src = reinterpret_cast<const uint8_t *>(J.net_in) + (clip0 + clip) * kNetIn + row * 13;
+          const uint8_t *src = reinterpret_cast<const uint8_t *>(J.net_in) + clip0 * kNetIn + raw_offset(clip, row, J.row0);
 #pragma unroll
           for (int j = 0; j < 13; j++) w[j >> 2] |= (uint32_t)src[j] << (8 * (j & 3));
         }
@@ -184,10 +202,14 @@ template <int POS, bool TRACE> struct IssueUnits {
 // slot free; thread 0: [4 pos + 2] = accumulators ready, [4 pos + 3] = slot released (tools/k2_trace.py prints the timeline)
 template <bool TRACE>
 __global__ void __launch_bounds__(kThreads, 1)
-nnom_q7_umma_kernel(const uint8_t *image, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax, int softmax_mode,
-                    int *class_counts, long long *trace) {
+nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
   extern __shared__ __align__(128) uint8_t smem[];
-  if (TRACE && blockIdx.x != 0) trace = nullptr;
+  const int8_t *net_in = K.net_in;
+  const long long n = K.n;
+  int8_t *logits = K.logits, *softmax = K.softmax;
+  const int softmax_mode = K.softmax_mode;
+  int *class_counts = K.class_counts;
+  long long *trace = (TRACE && blockIdx.x == 0) ? K.trace : nullptr;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t sbase = smem_u32(smem), bars = sbase + OFF_BAR;
   // mbarriers: full[slot] = bars + 8 slot, empty[slot] = bars + 32 + 8 slot, raw = bars + 64, weights = bars + 72
@@ -195,7 +217,7 @@ nnom_q7_umma_kernel(const uint8_t *image, const int8_t *net_in, long long n, int
   volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(smem + OFF_BAR + 80);
   int *hist = reinterpret_cast<int *>(smem + OFF_BAR + 96);
   Job J;
-  J.image = image; J.net_in = net_in; J.n = n; J.nb = (n + NC - 1) / NC;
+  J.image = image; J.net_in = net_in; J.n = n; J.nb = (n + NC - 1) / NC; J.row0 = K.row0;
   J.nbc = (long long)blockIdx.x < J.nb ? (int)((J.nb - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
   J.aligned = (reinterpret_cast<uintptr_t>(net_in) & 15) == 0;
 
@@ -244,7 +266,7 @@ nnom_q7_umma_kernel(const uint8_t *image, const int8_t *net_in, long long n, int
       DevCtx c;
       c.smem = smem; c.lane = lane; c.q = warp & 3; c.g = 0;
       c.clip0 = 0; c.nclips = 0; c.logits = logits; c.softmax = softmax; c.softmax_mode = softmax_mode; c.hist = hist;
-      c.t_ld = 0; c.tracing = false;
+      c.t_ld = 0; c.tracing = false; c.filt = K.filt; c.detect = K.detect;
       const uint32_t team = warp >> 2, ttid = tid & 127;
       const uint32_t tmem_q = tmem + ((uint32_t)(c.q * 32) << 16) + team * kSlotCols;
       const uint32_t bar_full = bars + 8 * team, bar_empty = bars + 32 + 8 * team;
@@ -315,15 +337,12 @@ int nnom_umma_upload(const int8_t *const w[5], const int8_t *const b[5], const i
   return EDISON_OK;
 }
 
-cudaError_t launch_nnom_q7_umma(const uint8_t *image, const int8_t *net_in, long long n, int8_t *logits, int8_t *softmax, int softmax_mode,
-                                int *class_counts, int sm_count, cudaStream_t stream, long long *trace) {
-  if (n <= 0) return cudaSuccess;
-  const long long nb = (n + NC - 1) / NC;
+cudaError_t launch_nnom_q7_umma(const uint8_t *image, const K2Launch &k, int sm_count, cudaStream_t stream) {
+  if (k.n <= 0) return cudaSuccess;
+  const long long nb = (k.n + NC - 1) / NC;
   const unsigned ctas = (unsigned)(nb < (long long)sm_count ? nb : (long long)sm_count);
-  if (trace)
-    nnom_q7_umma_kernel<true><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, net_in, n, logits, softmax, softmax_mode, class_counts, trace);
-  else
-    nnom_q7_umma_kernel<false><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, net_in, n, logits, softmax, softmax_mode, class_counts, nullptr);
+  if (k.trace) nnom_q7_umma_kernel<true><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, k);
+  else nnom_q7_umma_kernel<false><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, k);
   count_launch();
   return cudaGetLastError();
 }

@@ -200,25 +200,34 @@ int edison_sync(void *stream);
 
 /* ---- section 3b: continuous streaming (appMicMfccInfereContinuous, firmware/src/app.c:288-394, and its ISR
  *      appAudioEvent app.c:635-661) over n concurrent streams pinned to this GPU.  Per hop of 1024 new samples
- *      per stream: one MFCC row, mfccToNetInputPush (window of 31 rows shifts up by one), one full inference,
+ *      per stream: one MFCC row, mfccToNetInputPush (window of 31 rows advances by one), one full inference,
  *      netOutFilt = 0.9 netOutFilt + (1.0 - 0.9) out (double arithmetic, stored as float; app.c:35-39, 342),
  *      argmax (arm_max_f32: first maximum), "spotted" when the maximum exceeds 0.5 (app.c:34, 344-350).
  *      Like the firmware, inference and the filter start once the window has been filled and one more hop
- *      has arrived (hop count >= 32); before that detect[] is -2 and filt[] stays 0. ------------------------ */
+ *      has arrived (hop count >= 32); before that detect[] is -2 and filt[] stays 0.
+ *      On the device a hop is two launches: K1 stores each stream's row straight into its window (a ring of rows),
+ *      K2 runs the windows with the filter / argmax / threshold fused into its last epilogue. ------------------ */
 typedef struct edison_streams edison_streams;
 int edison_streams_open(size_t n_streams, edison_streams **out);
 void edison_streams_close(edison_streams *s);
-/* hop_pcm[n_streams][1024] host or device.  Outputs (host or device like hop_pcm, any may be NULL):
- * softmax[n][10] int8, filt[n][10] float, detect[n] int32 = class index if spotted, -1 if not, -2 while filling. */
+/* hop_pcm[n_streams][1024] host or device.  Outputs (host or device, any may be NULL):
+ * softmax[n][10] int8, filt[n][10] float, detect[n] int32 = class index if spotted, -1 if not, -2 while filling.
+ * Synchronous: = edison_streams_submit_hop + edison_streams_collect_hop. */
 int edison_streams_push_hop(edison_streams *s, const int16_t *hop_pcm, int8_t *softmax, float *filt, int32_t *detect);
-/* device pointers + stream, asynchronous */
+/* Pipelined form for host callers: up to two hops may be in flight.  submit starts the host -> device copy of the hop on a copy
+ * stream and queues its kernels behind it (hop_pcm must stay valid until the matching collect returns; pinned memory lets the
+ * copy of hop h + 1 overlap the kernels of hop h); collect waits for the OLDEST hop in flight and hands out its results. */
+int edison_streams_submit_hop(edison_streams *s, const int16_t *hop_pcm);
+int edison_streams_collect_hop(edison_streams *s, int8_t *softmax, float *filt, int32_t *detect);
+/* device pointers + stream (NULL = the handle's own stream), asynchronous */
 int edison_streams_push_hop_dev(edison_streams *s, const int16_t *d_hop_pcm, int8_t *d_softmax, float *d_filt,
                                 int32_t *d_detect, void *stream);
 unsigned long long edison_streams_hops(const edison_streams *s);
-/* 1 (default): the net advances one new row per layer and hop from cached rows (bit-identical, ~4x less work);
- * 0: the whole 31-row window goes through the net every hop, as the firmware does.  Only before the first hop. */
+/* 0 (default): the whole 31-row window goes through K2 (tcgen05) every hop, as the firmware does;
+ * 1: the net advances one new row per layer and hop from cached rows in HBM (bit-identical, 4x fewer MACs, but an mma.sync
+ *    kernel that is slower than the full window since K2 moved to tcgen05: DESIGN.md 4d).  Only before the first hop. */
 int edison_streams_set_incremental(edison_streams *s, int on);
-/* copy one stream's 31x13 window (netInput, app.c:71-93) to the host, for inspection */
+/* copy one stream's 31x13 window (netInput, app.c:71-93), oldest row first, to the host, for inspection */
 int edison_streams_window(edison_streams *s, size_t stream_index, int8_t *window403);
 
 /* ---- section 4: self-checks used by the tests (device arithmetic against itself) ------------- */
@@ -230,8 +239,6 @@ int edison_debug_mag_sweep(uint32_t lo, uint32_t hi, unsigned long long *mismatc
                            unsigned long long *checksum);
 /* K2 with clock64() stamps per schedule unit of block 0's second batch (d_trace: 96 int64 on the device; tools/k2_trace.py) */
 int edison_debug_k2_trace_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, long long *d_trace, void *stream);
-/* the round-1 mma.sync build of K2, kept only so that tools/k2_time.py can time the two tensor paths side by side */
-int edison_debug_infer_q7_legacy_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, void *stream);
 
 #ifdef __cplusplus
 }

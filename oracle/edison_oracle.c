@@ -5,7 +5,7 @@
  * arithmetic is the firmware's own build: CMSIS-DSP with ARM_MATH_DSP (Cortex-M4 SIMD
  * branches, firmware/Makefile:30), i.e. oracle/_ref/libref_mfcc_simd.so.
  *
- * Parity status: PINNED against oracle/_ref (tests/test_oracle_vs_ref.py) and the
+ * Parity status: PINNED against oracle/_ref (tests/test_oracle_cpu.py) and the
  * golden vectors in tests/golden/ generated from it.
  *
  * Written from scratch in an unpacked (re, im as separate int32) form; the M4's packed
@@ -47,7 +47,7 @@ static inline cq15 twiddle(int32_t co, int32_t si, cq15 v)
 /* ------------------------------------------------------------------------------------------
  * Tables.  arm_common_tables.c is missing from the reference tree (.MISSING_LARGE_BLOBS:4);
  * formulas below reproduce the data inside libarm_cortexM4lf_math.a bit for bit
- * (checked in tests/test_oracle_tables.py against oracle/_ref/tables_manifest.json).
+ * (checked in tests/test_oracle_cpu.py against oracle/_ref/tables_manifest.json).
  * ---------------------------------------------------------------------------------------- */
 static int16_t tw1024[1536];
 static int16_t tw16[24];

@@ -55,6 +55,8 @@ struct Ctx {
   int8_t *logits, *softmax;
   int softmax_mode;
   long long *hist;
+  float *filt = nullptr;
+  void post(long long, const int8_t *) {}
   void ld16(uint32_t col, uint32_t (&v)[16]) {
     for (int j = 0; j < 16; j++) v[j] = (uint32_t)e->tmem[(q * 32 + lane) * 512 + slot * kSlotCols + col + j];
   }
@@ -72,7 +74,7 @@ void transpose_in(Emu &E, const int8_t *net_in, long long n, long long batch) {
   memcpy(&E.smem[OFF_RAW], net_in + clip0 * kNetIn, (size_t)nclips * kNetIn);
   for (int row = 0; row < kInRowsUsed; row++)
     for (int clip = 0; clip < NC; clip++) {
-      const uint32_t a = (uint32_t)clip * kNetIn + (uint32_t)row * 13;
+      const uint32_t a = raw_offset(clip, row, 0);
       uint32_t w[4];
       memcpy(w, &E.smem[OFF_RAW + (a & ~3u)], 16);
       const Vec16 v = input_chunk(w, a);

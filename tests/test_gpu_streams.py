@@ -74,3 +74,29 @@ def test_streams_bad_arguments(edison):
     h = ctypes.c_void_p()
     assert L.edison_streams_open(0, ctypes.byref(h)) == -1
     assert L.edison_streams_push_hop(None, None, None, None, None) == -1
+
+
+def test_streams_pipelined_submit_collect(edison, oracle):
+    """two hops in flight (copy of hop h + 1 overlaps the kernels of hop h): same results, in order, as the synchronous calls"""
+    n, hops = 19, 45
+    pcm = synth_frames(hops * n, seed=123).reshape(hops, n, 1024)
+    want = simulate(oracle, pcm)
+    got = []
+    with edison.Streams(n) as st:
+        keep = [st.submit_hop(pcm[0])]
+        for h in range(1, hops):
+            keep.append(st.submit_hop(pcm[h]))
+            got.append(st.collect_hop())
+            keep.pop(0)
+        got.append(st.collect_hop())
+        L = edison.lib()
+        assert L.edison_streams_collect_hop(st.handle, None, None, None) == -1          # nothing in flight
+        st.submit_hop(pcm[0]); st.submit_hop(pcm[1])
+        assert L.edison_streams_submit_hop(st.handle, pcm[2].ctypes.data) == -1           # a third hop must wait for a collect
+        st.collect_hop(); st.collect_hop()
+    for h in range(hops):
+        sm, fl, dt = got[h]
+        assert np.array_equal(dt, want[h][2]), "detect, hop %d" % h
+        assert np.array_equal(fl.view(np.uint32), want[h][1].view(np.uint32)), "filter bits, hop %d" % h
+        if h + 1 > 31:
+            assert np.array_equal(sm, want[h][0]), "softmax, hop %d" % h
