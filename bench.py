@@ -29,11 +29,28 @@ E2E_CLIPS = 32768               # host-buffer leg: 2.08 GB of pinned PCM per ste
 CLIP = 31 * 1024
 K1_BYTES_PER_FRAME = 2048 + 13  # algorithmic: PCM read + int8 net-input row written
 N_STREAMS = 100000              # config #5
-# dram__bytes_read.sum + dram__bytes_write.sum of one mfcc_q15_kernel launch over 131,072 x 31 frames, from the ncu
-# --set full capture summarised in profiles/r01k_k1_group_lockstep.txt (8.322 GB read + 9.7 MB written): no re-reads.
-K1_NCU_DRAM_BYTES = 8.332e9
-# smsp__inst_executed.sum / frames of the same capture: what actually bounds K1 (integer issue, SURVEY F9 / DESIGN.md section 3)
-K1_WARP_INST_PER_FRAME = 2435
+
+
+def k1_ncu():
+    """dram bytes per launch and warp instructions per frame of K1 from the committed ncu summary (profiles/k1_ncu.json, written by
+    tools/ncu_summary.py --json from an `ncu --set full` capture of this bench's K1 launch): (traffic, inst/frame, source)"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "k1_ncu.json")) as fh:
+            d = json.load(fh)
+        return float(d["dram_bytes_per_launch"]) * (CLIPS_PER_GPU * 31) / float(d["frames"]), float(d["warp_inst_per_frame"]), d.get("source")
+    except Exception:
+        return None, None, None
+
+
+def int8_peak():
+    """dense int8 tensor rate measured on this pool's B200 with tcgen05.mma.kind::i8 from shared memory on all SMs
+    (tools/ubench/umma_probe.cu -> profiles/r02a_umma_probe.json); 2 x the measured bf16 rate only if that file is missing"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02a_umma_probe.json")) as fh:
+            return float(json.load(fh)["int8_tops_measured"]), "measured (tools/ubench/umma_probe.cu, profiles/r02a_umma_probe.json)"
+    except Exception:
+        bf = peaks_bf16()
+        return 2 * bf[0], "2 x bf16 " + bf[1]
 
 
 def bind_to_gpu_numa(index):
@@ -158,23 +175,30 @@ def synth_clips_gpu(torch, n_clips, stride, seed, dev):
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's own CPU implementation on the host cores (rank 0 only)."""
+    """--impl reference: the reference's own CPU implementation on the host cores (rank 0 only).  The line's value is B1, the
+    firmware-true build (the arithmetic the GPU arm reproduces bit for bit); B2 (the reference's plain-C path at -O3) and the
+    oracle's plain-C port are timed beside it and reported in the same line, so that a reader can take the fastest as denominator."""
     if rank != 0:
         return
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import cpu_baseline
     cores = os.cpu_count() or 1
-    per = 64
-    res = cpu_baseline.run(clips_per_proc=per, procs=cores, mfcc_only=False, reps=args.warmup + args.steps)
-    steps = res["step_s"][args.warmup:]
+    per = 32
+    res = cpu_baseline.run(clips_per_proc=per, procs=cores, mfcc_only=False, reps=args.steps, warmup=args.warmup)
+    steps = res["step_s"]
     ms = 1e3 * sum(steps) / len(steps)
     val = res["clips"] / (ms / 1e3)
+    others = {}
+    for which in ("reference_o3", "port"):
+        r2 = cpu_baseline.run(clips_per_proc=per, procs=cores, reps=3, warmup=1, which=which)
+        others[r2["kind"]] = {"value": r2["clips_per_s"], "unit": "clips/s", "cores": r2["cores"], "sample": r2["sample"]}
     line = {"impl": "reference", "metric": "kws_clips_per_s", "value": val, "unit": "clips/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "q15/int8", "data": "synthetic",
             "config": {"workload": "config#3 shard: clips x 31 frames x 1024 int16, q15 MFCC + int8 NNoM net",
                        "sample": res["sample"]},
             "cpu_baseline": {"value": val, "unit": "clips/s", "cores": cores, "kind": res["kind"], "sample": res["sample"]},
+            "cpu_baseline_other_builds": others,
             "e2e": {"value": val, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "mfcc_frames_per_s": val * 31, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -205,17 +229,22 @@ def run_ours(args, rank, world, local_rank):
     logits = torch.empty(n, 10, dtype=torch.int8, device=dev)
     softmax = torch.empty(n, 10, dtype=torch.int8, device=dev)
     gathered = torch.empty(world * n, 10, dtype=torch.int8, device=dev) if world > 1 else None
-    counts = torch.zeros(10, dtype=torch.int64, device=dev)
+    counts = torch.zeros(10, dtype=torch.int32, device=dev)     # class histogram, accumulated by K2's dense epilogue on the device
+    total_counts = None
 
     def step(ev=None):
         if ev: ev[0].record(st)
         chk(L.edison_mfcc_q15_clips_dev(P(pcm), n, 31, CLIP, None, P(net_in), sp))
         if ev: ev[1].record(st)
-        chk(L.edison_infer_q7_batch_dev(P(net_in), n, P(logits), P(softmax), sp))
+        chk(L.edison_infer_q7_counts_dev(P(net_in), n, P(logits), P(softmax), P(counts), sp))
         if ev: ev[2].record(st)
-        if world > 1:  # the path's only exchange: final gather of logits + class counts
+
+    def final_exchange():
+        """the path's only exchange, once after the last batch: gather of the logits, sum of the class counts"""
+        if world > 1:
             dist.all_gather_into_tensor(gathered, logits)
-            counts.copy_(shard.class_counts(dist, logits))
+            return shard.reduce_counts(dist, counts)
+        return counts.to(torch.int64)
 
     def barrier():
         torch.cuda.synchronize()
@@ -225,6 +254,8 @@ def run_ours(args, rank, world, local_rank):
 
     for _ in range(args.warmup):
         step()
+    final_exchange()
+    counts.zero_()
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -234,19 +265,43 @@ def run_ours(args, rank, world, local_rank):
     t_begin.record(st)
     for k in range(args.steps):
         step(evs[k])
+    t_comm = torch.cuda.Event(enable_timing=True)
+    t_comm.record(st)
+    total_counts = final_exchange()          # inside the timed region: the job is K batches, then the exchange
     t_end.record(st)
     barrier()
     launches = ed.launch_count() - l0
     total_ms = t_begin.elapsed_time(t_end)
+    comm_ms = t_comm.elapsed_time(t_end)
     k1_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
     k2_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
     clocks = sampler.summary()
     if world > 1:
-        t = torch.tensor([total_ms, k1_ms, k2_ms], device=dev, dtype=torch.float64)
+        t = torch.tensor([total_ms, k1_ms, k2_ms, comm_ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms, k1_ms, k2_ms = t.tolist()
+        total_ms, k1_ms, k2_ms, comm_ms = t.tolist()
     ms_per_step = total_ms / args.steps
     value = world * n / (ms_per_step / 1e3)
+
+    # ---- what the timed region computed, checked AFTER it: sampled clips of the last step against the CPU oracle (bit-exact),
+    # and the device-side class histogram against an argmax of the logits it was built from
+    parity = None
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import numpy as np
+        import common
+        pick = np.linspace(0, n - 1, 256).astype(np.int64)
+        host_pcm = torch.stack([pcm[int(c) * CLIP:(int(c) + 1) * CLIP] for c in pick]).cpu().numpy()
+        want_lg, want_sm, want_ni = common.Oracle().kws(host_pcm.reshape(-1), len(pick))
+        idx = torch.from_numpy(pick).to(dev)
+        got_lg, got_sm = logits[idx].cpu().numpy(), softmax[idx].cpu().numpy()
+        got_ni = net_in.view(n, 403)[idx].cpu().numpy()
+        hist_ok = bool((counts.to(torch.int64) == args.steps * torch.bincount(logits.to(torch.int64).argmax(dim=1), minlength=10)).all().item())
+        parity = {"clips_checked": int(len(pick)), "net_input_exact": bool((got_ni == want_ni).all()), "logits_exact": bool((got_lg == want_lg).all()),
+                  "softmax_exact": bool((got_sm == want_sm).all()), "class_histogram_matches_logits": hist_ok,
+                  "class_counts_total": int(total_counts.sum().item()), "against": "oracle/libedison_oracle.so (pinned to oracle/_ref)"}
+        parity["ok"] = parity["net_input_exact"] and parity["logits_exact"] and parity["softmax_exact"] and hist_ok and \
+            parity["class_counts_total"] == args.steps * world * n
 
     # ---- MFCC-only on config #2 (65,536 one-second clips -> 15 frames each), device resident
     pcm2 = pcm[: CFG2_CLIPS * CFG2_STRIDE]
@@ -331,20 +386,23 @@ def run_ours(args, rank, world, local_rank):
     del d_tmp
     same = bool((h_logits.to(dev) == logits[:ne]).all().item())
 
-    # ---- streaming (config #5): N_STREAMS concurrent streams, one hop = 1024 new samples per stream, device resident.
-    # Hop latency = K1 (one frame per stream) + window push + K2 (full window per stream) + filter/argmax.
+    # ---- streaming (config #5): N_STREAMS concurrent streams, one hop = 1024 new samples per stream.
+    # A hop is two launches: K1 (one frame per stream, rows stored straight into the ring windows) and K2 (full window per stream,
+    # filter / argmax / threshold fused).  Device-resident hops are timed with CUDA events; the ingest leg takes the hop PCM from
+    # pinned host memory through the pipelined submit / collect calls (copy of hop h + 1 under the kernels of hop h).
     stream_stats = None
     if world == 1:
         ns = N_STREAMS
         d_sm = torch.empty(ns, 10, dtype=torch.int8, device=dev)
         d_fl = torch.empty(ns, 10, dtype=torch.float32, device=dev)
         d_dt = torch.empty(ns, dtype=torch.int32, device=dev)
+        pct = lambda v, q: v[min(len(v) - 1, int(len(v) * q))]
         with ed.Streams(ns) as ss:
-            hop = lambda h: chk(L.edison_streams_push_hop_dev(ss.handle, P(pcm[(h % 36) * ns * 1024:]), P(d_sm), P(d_fl), P(d_dt), sp))
+            hop = lambda h: chk(L.edison_streams_push_hop_dev(ss.handle, P(pcm[(h % 36) * ns * 1024:]), None, None, None, sp))
             for h in range(34):   # fill the 31-row windows, then two full hops as warm-up
                 hop(h)
             torch.cuda.synchronize()
-            n_hops = 200
+            n_hops = 2000
             hev = [torch.cuda.Event(enable_timing=True) for _ in range(n_hops + 1)]
             hev[0].record(st)
             for h in range(n_hops):
@@ -352,43 +410,59 @@ def run_ours(args, rank, world, local_rank):
                 hev[h + 1].record(st)
             torch.cuda.synchronize()
             lat = sorted(hev[i].elapsed_time(hev[i + 1]) for i in range(n_hops))
-            p50, p99 = lat[n_hops // 2], lat[min(n_hops - 1, int(n_hops * 0.99))]
-            # ingest + device: hop PCM from pinned host memory, detections back to the host, every hop
-            h_hop = torch.empty(ns * 1024, dtype=torch.int16).pin_memory()
-            h_hop.copy_(pcm[: ns * 1024])
+            p50, p99 = pct(lat, 0.5), pct(lat, 0.99)
+        with ed.Streams(ns) as ss:
+            h_hop = [torch.empty(ns * 1024, dtype=torch.int16).pin_memory() for _ in range(2)]
+            for b_ in h_hop:
+                b_.copy_(pcm[: ns * 1024])
             h_sm = torch.empty(ns, 10, dtype=torch.int8).pin_memory()
             h_fl = torch.empty(ns, 10, dtype=torch.float32).pin_memory()
             h_dt = torch.empty(ns, dtype=torch.int32).pin_memory()
-            lat_e2e = []
-            for h in range(40):
+            n_ing = 500
+            chk(L.edison_streams_submit_hop(ss.handle, P(h_hop[0])))
+            stamps = []
+            for h in range(1, 34 + n_ing):
+                chk(L.edison_streams_submit_hop(ss.handle, P(h_hop[h & 1])))
+                chk(L.edison_streams_collect_hop(ss.handle, P(h_sm), P(h_fl), P(h_dt)))
+                stamps.append(time.perf_counter())
+            chk(L.edison_streams_collect_hop(ss.handle, P(h_sm), P(h_fl), P(h_dt)))
+            lat_e2e = sorted((stamps[i + 1] - stamps[i]) * 1e3 for i in range(33, len(stamps) - 1))
+        small = {}
+        with ed.Streams(1024) as s2:
+            for h in range(34):
+                chk(L.edison_streams_push_hop_dev(s2.handle, P(pcm[(h % 36) * 1024 * 1024:]), None, None, None, sp))
+            torch.cuda.synchronize()
+            lat2 = []
+            for h in range(500):
                 t0 = time.perf_counter()
-                chk(L.edison_streams_push_hop(ss.handle, P(h_hop), P(h_sm), P(h_fl), P(h_dt)))
-                lat_e2e.append((time.perf_counter() - t0) * 1e3)
-            lat_e2e = sorted(lat_e2e[8:])
-            small = {}
-            with ed.Streams(1024) as s2:
-                for h in range(34):
-                    chk(L.edison_streams_push_hop_dev(s2.handle, P(pcm[(h % 36) * 1024 * 1024:]), P(d_sm), P(d_fl), P(d_dt), sp))
+                chk(L.edison_streams_push_hop_dev(s2.handle, P(pcm[(h % 36) * 1024 * 1024:]), None, None, None, sp))
                 torch.cuda.synchronize()
-                lat2 = []
-                for h in range(100):
-                    t0 = time.perf_counter()
-                    chk(L.edison_streams_push_hop_dev(s2.handle, P(pcm[(h % 36) * 1024 * 1024:]), P(d_sm), P(d_fl), P(d_dt), sp))
-                    torch.cuda.synchronize()
-                    lat2.append((time.perf_counter() - t0) * 1e3)
-                lat2.sort()
-                small = {"streams": 1024, "hop_ms_p50": lat2[50], "hop_ms_p99": lat2[98], "note": "host wall clock, launch to completion"}
-            stream_stats = {"workload": "config#5: %d concurrent streams, hop 1024 samples (64 ms), window 31 rows, device resident" % ns,
-                            "hop_ms_p50": p50, "hop_ms_p99": p99, "hops_timed": n_hops,
-                            "stream_hops_per_s": ns / (p50 / 1e3), "realtime_streams_per_gpu": int(ns * 64.0 / p99),
-                            "ingest_hop_ms_p50": lat_e2e[len(lat_e2e) // 2], "ingest_hop_ms_p99": lat_e2e[-1],
-                            "ingest_bytes_per_hop": ns * 2048, "small_batch": small, "ingest_realtime_streams_per_gpu": int(ns * 64.0 / lat_e2e[-1])}
+                lat2.append((time.perf_counter() - t0) * 1e3)
+            lat2.sort()
+            ev2 = [torch.cuda.Event(enable_timing=True) for _ in range(501)]
+            ev2[0].record(st)
+            for h in range(500):
+                chk(L.edison_streams_push_hop_dev(s2.handle, P(pcm[(h % 36) * 1024 * 1024:]), None, None, None, sp))
+                ev2[h + 1].record(st)
+            torch.cuda.synchronize()
+            dev2 = sorted(ev2[i].elapsed_time(ev2[i + 1]) for i in range(500))
+            small = {"streams": 1024, "hop_ms_p50": pct(lat2, 0.5), "hop_ms_p99": pct(lat2, 0.99), "hops_timed": 500,
+                     "note": "host wall clock, launch to completion, one hop at a time",
+                     "device_hop_ms_p50": pct(dev2, 0.5), "device_hop_ms_p99": pct(dev2, 0.99), "launches_per_hop": 2}
+        stream_stats = {"workload": "config#5: %d concurrent streams, hop 1024 samples (64 ms), window 31 rows, device resident" % ns,
+                        "hop_ms_p50": p50, "hop_ms_p99": p99, "hops_timed": n_hops, "launches_per_hop": 2,
+                        "stream_hops_per_s": ns / (p50 / 1e3), "realtime_streams_per_gpu": int(ns * 64.0 / p99),
+                        "ingest_hop_ms_p50": pct(lat_e2e, 0.5), "ingest_hop_ms_p99": pct(lat_e2e, 0.99), "ingest_hops_timed": len(lat_e2e),
+                        "ingest_bytes_per_hop": ns * 2048, "ingest_note": "pinned host PCM, submit(h + 1) / collect(h) pipelining, results to pinned host memory every hop",
+                        "small_batch": small, "ingest_realtime_streams_per_gpu": int(ns * 64.0 / pct(lat_e2e, 0.99))}
 
     if rank == 0:
         peak, peak_kind = peaks()
         sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
         k1_bytes = n * 31 * K1_BYTES_PER_FRAME
         achieved = k1_bytes / (k1_ms / 1e3) / 1e9
+        k1_traffic, k1_inst, k1_src = k1_ncu()
+        K1_WARP_INST_PER_FRAME = k1_inst or 0.0
         line = {"metric": "kws_clips_per_s", "value": value, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "q15/int8", "data": "synthetic",
@@ -398,11 +472,14 @@ def run_ours(args, rank, world, local_rank):
                 "mfcc_frames_per_s": world * n * 31 / (k1_ms / 1e3), "audio_seconds_per_s": value * 31 * 0.064,
                 # BASELINE.json words the metric in "1 s 16 kHz" clips; the net's own window is 31 frames = 1.984 s
                 "one_second_equiv_clips_per_s": value * 31 / 15.625,
-                "k1_ms": k1_ms, "k2_ms": k2_ms,
+                "k1_ms": k1_ms, "k2_ms": k2_ms, "comm_ms": comm_ms,
+                "comm": "one all_gather of the int8 logits + all_reduce of the int32[10] class counts after the last step (inside the timed region)"
+                        if world > 1 else "single GPU: no exchange",
+                "parity_checked": parity,
                 "cfg2_mfcc": {"workload": "config#2: 65,536 x 1 s clips (15 frames each), q15 MFCC only, 1 GPU",
                               "frames_per_s": cfg2_fps, "clips_per_s": CFG2_CLIPS / (cfg2_ms / 1e3), "ms": cfg2_ms},
                 "roofline": {"kernel": "mfcc_q15_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": K1_NCU_DRAM_BYTES * (k1_bytes / (131072 * 31 * K1_BYTES_PER_FRAME)), "bytes_per_launch": k1_bytes,
+                             "frac": achieved / peak, "traffic": k1_traffic, "traffic_source": k1_src, "bytes_per_launch": k1_bytes,
                              # the bound that actually binds: 4 warp-instructions per clock per SM (measured pipe rates, profiles/)
                              "secondary": {"bound": "int-issue", "unit": "G warp-inst/s", "warp_inst_per_frame": K1_WARP_INST_PER_FRAME,
                                            "achieved": n * 31 / (k1_ms / 1e3) * K1_WARP_INST_PER_FRAME / 1e9,
@@ -416,25 +493,34 @@ def run_ours(args, rank, world, local_rank):
                 "gpu_launches": int(launches), "clocks": clocks}
         if stream_stats:
             line["streaming"] = stream_stats
-        # the CNN's own roofline (BASELINE.json: "% tensor peak"): 784,752 MAC = 1,569,504 int8 ops per clip;
-        # the dense int8 tensor rate is taken as 2 x the measured bf16 rate of MEASURED_PEAKS.json (nominal 4.5 vs 2.25 PFLOP/s)
-        bf16 = peaks_bf16()
+        # the CNN's own roofline (BASELINE.json: "% tensor peak"): 784,752 MAC = 1,569,504 int8 ops per clip against the
+        # int8 tensor rate MEASURED on this pool (tcgen05.mma.kind::i8 on all SMs, tools/ubench/umma_probe.cu)
+        i8_peak, i8_kind = int8_peak()
         k2_tops = n * 1569504 / (k2_ms / 1e3) / 1e12
-        line["cnn_roofline"] = {"kernel": "nnom_q7_kernel", "bound": "tensor", "achieved": k2_tops, "peak": 2 * bf16[0], "unit": "TOP/s (int8)",
-                                "frac": k2_tops / (2 * bf16[0]), "peak_kind": "2 x bf16 " + bf16[1], "share_of_step": k2_ms / ms_per_step}
+        line["cnn_roofline"] = {"kernel": "nnom_q7_umma_kernel (tcgen05.mma.kind::i8, TMEM accumulators)", "bound": "tensor", "achieved": k2_tops,
+                                "peak": i8_peak, "unit": "TOP/s (int8)", "frac": k2_tops / i8_peak, "peak_kind": i8_kind,
+                                "share_of_step": k2_ms / ms_per_step,
+                                "note": "algorithmic ops; the kernel issues ~1.6x more (wrap-around pixels, Toeplitz conv1) and is bound by "
+                                        "epilogue latency, not by the tensor pipe (DESIGN.md 4)"}
         line["cfg4_float_cnn"] = cfg4
         line["float_mfcc"] = dict(float_stats, workload="mfcc_utils.mfcc arithmetic on 65,536 x 1 s clips (15 frames each), 1 GPU")
         if world == 1 and not args.no_cpu:
             sys.path.insert(0, os.path.join(ROOT, "oracle"))
             import cpu_baseline
-            res = cpu_baseline.run(clips_per_proc=64, procs=os.cpu_count() or 1, reps=1)
+            ncpu = os.cpu_count() or 1
+            res = cpu_baseline.run(clips_per_proc=32, procs=ncpu, reps=3, warmup=1)
             line["cpu_baseline"] = {"value": res["clips_per_s"], "unit": "clips/s", "cores": res["cores"], "kind": res["kind"],
-                                    "sample": res["sample"]}
-            # the "fair CPU" figure of BASELINE.md (B2): the oracle's plain-C restatement at -O2 (bit-identical results, no
-            # host emulation of M4 intrinsics, audioprocessing.c's -O0 not needed), same sample, all cores
-            res2 = cpu_baseline.run(clips_per_proc=64, procs=os.cpu_count() or 1, reps=1, which="port")
-            line["cpu_baseline_port"] = {"value": res2["clips_per_s"], "unit": "clips/s", "cores": res2["cores"], "kind": "port",
-                                         "sample": res2["sample"]}
+                                    "sample": res["sample"], "build": "B1 firmware-true: audioprocessing.c -O0 + CMSIS SIMD branches on emulated M4 intrinsics"}
+            # B2 of SURVEY 8(d), the fair CPU figure: the reference's plain-C CMSIS path at -O3 (AVX2) + NNoM local backend; and the
+            # oracle's plain-C restatement.  All cores and one core each.
+            extra = {}
+            for which in ("reference", "reference_o3", "port"):
+                for procs in (ncpu, 1):
+                    r2 = cpu_baseline.run(clips_per_proc=32 if procs > 1 else 48, procs=procs, reps=3, warmup=1, which=which)
+                    extra["%s_%s" % (r2["kind"], "all_cores" if procs > 1 else "1_core")] = {
+                        "value": r2["clips_per_s"], "unit": "clips/s", "cores": r2["cores"], "sample": r2["sample"]}
+            line["cpu_baseline_builds"] = extra
+            line["cpu_baseline_port"] = dict(extra.get("port_all_cores", {}), kind="port")
             # config #1's CPU side: the numpy restatement of mfcc_utils.mfcc (pinned to the reference module's own outputs) on one core
             import mfcc_float as mf
             rng = __import__("numpy").random.default_rng(20)

@@ -32,3 +32,11 @@ def class_counts(dist, logits_local, n_classes=10):
         torch.zeros(n_classes, dtype=torch.int64, device=logits_local.device)
     dist.all_reduce(c)
     return c
+
+
+def reduce_counts(dist, counts_local):
+    """sum of the per-rank class histograms that K2 accumulates on the device (edison_kws_counts_dev): int64 [10] on every rank"""
+    import torch
+    c = counts_local.to(torch.int64)
+    dist.all_reduce(c)
+    return c

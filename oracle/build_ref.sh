@@ -40,15 +40,15 @@ DSP_SRCS="TransformFunctions/arm_cfft_q15.c TransformFunctions/arm_cfft_radix4_q
           TransformFunctions/arm_rfft_init_q15.c TransformFunctions/arm_bitreversal2.c TransformFunctions/arm_bitreversal.c
           FastMathFunctions/arm_sqrt_q31.c SupportFunctions/arm_copy_q15.c CommonTables/arm_const_structs.c"
 
-build_mfcc () {  # $1 = variant name, $2 = extra flags for the CMSIS sources
-  local v="$1" extra="$2" objs=""
+build_mfcc () {  # $1 = variant name, $2 = extra flags for the CMSIS sources, $3 = optimisation of the CMSIS sources, $4 = of audioprocessing.c
+  local v="$1" extra="$2" opt="${3:--O2}" uopt="${4:--O0}" objs=""
   mkdir -p "$TMP/$v"
   for s in $DSP_SRCS; do
     o="$TMP/$v/$(basename "$s" .c).o"
-    $CC $COMMON -O2 $extra -c "$DSP/Source/$s" -o "$o"; objs="$objs $o"
+    $CC $COMMON $opt $extra -c "$DSP/Source/$s" -o "$o"; objs="$objs $o"
   done
-  # user code: -O0, like the firmware (Makefile:42) -- and required, see SURVEY F6
-  $CC $COMMON -O0 $extra -c "$TMP/fw/audioprocessing.c" -o "$TMP/$v/audioprocessing.o"
+  # user code: -O0, like the firmware (Makefile:42) -- and required, see SURVEY F6 (the B2 variant below is the exception)
+  $CC $COMMON $uopt $extra -c "$TMP/fw/audioprocessing.c" -o "$TMP/$v/audioprocessing.o"
   $CC $COMMON -O2 -c "$TMP/cmsis_tables.c" -o "$TMP/$v/cmsis_tables.o"
   $CC $COMMON -O2 -c "$HERE/drivers/ref_mfcc_driver.c" -o "$TMP/$v/driver.o"
   $CC -shared -o "$OUT/libref_mfcc_$v.so" $objs "$TMP/$v/audioprocessing.o" "$TMP/$v/cmsis_tables.o" "$TMP/$v/driver.o" \
@@ -56,6 +56,11 @@ build_mfcc () {  # $1 = variant name, $2 = extra flags for the CMSIS sources
 }
 build_mfcc simd "-include arm_math.h -include $HERE/shim/define_dsp.h"
 build_mfcc c ""
+# B2 of SURVEY 8(d), the "fair CPU" baseline: the reference's plain-C CMSIS path at -O3 for AVX2 hosts (x86-64-v3 rather than
+# -march=native: the .so is built in one container and timed on another host).  audioprocessing.c goes to -O2 here: the
+# out-of-bounds tail of cmpl_mag_q15's 2048-element call (F6) lands in the neighbouring static buffer either way and is never
+# read; tests/test_oracle_cpu.py checks that this build's outputs equal libref_mfcc_c.so's.
+build_mfcc c_o3 "" "-O3 -march=x86-64-v3" "-O2 -march=x86-64-v3"
 
 # ---- float MFCC of firmware/src/audio/mfcc.c: mfcc.c + CMSIS f32 real FFT, compiled where they lie
 build_mfccf () {
@@ -90,9 +95,9 @@ NN_SRCS="ConvolutionFunctions/arm_convolve_HWC_q7_basic_nonsquare.c ConvolutionF
          NNSupportFunctions/arm_nntables.c NNSupportFunctions/arm_nn_mult_q7.c NNSupportFunctions/arm_nn_add_q7.c"
 
 build_nnom () {  # $1 = variant, $2 = port dir (selects NNOM_USING_CMSIS_NN), $3 = extra flags, $4 = with CMSIS-NN sources (0/1)
-  local v="$1" port="$2" extra="$3" with_nn="$4" objs=""
+  local v="$1" port="$2" extra="$3" with_nn="$4" opt="${5:--O2}" objs=""
   mkdir -p "$TMP/nn_$v"
-  local inc="-fPIC -w -O2 -ffunction-sections -fdata-sections -I$NNOM -I$port -I$NNOM/inc -D__GNUC_PYTHON__ -D__RESTRICT=__restrict -I$NN/Include -I$DSP/Include"
+  local inc="-fPIC -w $opt -ffunction-sections -fdata-sections -I$NNOM -I$port -I$NNOM/inc -D__GNUC_PYTHON__ -D__RESTRICT=__restrict -I$NN/Include -I$DSP/Include"
   local i=0
   for s in $NNOM_SRCS; do
     o="$TMP/nn_$v/n$i.o"; i=$((i+1))
@@ -110,6 +115,7 @@ build_nnom () {  # $1 = variant, $2 = port dir (selects NNOM_USING_CMSIS_NN), $3
 }
 # local backend: the submodule's port header (NNOM_USING_CMSIS_NN commented out)
 build_nnom local "$REF/audio/edison/deploy/nnom/port" "" 0
+build_nnom local_o3 "$REF/audio/edison/deploy/nnom/port" "" 0 "-O3 -march=x86-64-v3"   # B2
 # CMSIS-NN reference branches: firmware's port header (NNOM_USING_CMSIS_NN on), ARM_MATH_DSP unset
 build_nnom cmsis "$NNOM/port" "" 1
 # CMSIS-NN SIMD branches == firmware build
