@@ -92,6 +92,7 @@ __device__ __forceinline__ void mel_mma(int lane, int half, const MfccTables &T,
 }
 
 // dct2_q15 + outputs for the 8 frames of group grp, whose mel spectra sit in W.mel
+template <bool STRIDED>
 __device__ __forceinline__ void group_tail(const MfccLaunch &P, const MfccTables &T, WarpSmem &W, int lane, long long grp,
                                            long long n_frames) {
   // dct2_q15 for the 8 frames of the group, 4 lanes per frame
@@ -120,13 +121,16 @@ __device__ __forceinline__ void group_tail(const MfccLaunch &P, const MfccTables
   if (P.net_in) {  // 8 frames x 13 int8 (mfccToNetInput)
     for (int idx = lane; idx < kGroup * kNCoeff; idx += 32) {
       const int fr = idx / kNCoeff, c = idx - fr * kNCoeff;
-      if (f0 + fr < n_frames) P.net_in[(f0 + fr) * P.net_in_stride + c] = (int8_t)net_input_q7(out[32 * fr + c], T);
+            // STRIDED (the streaming path: one row of each stream's window) is a separate instantiation: with the stride as a run-time
+      // value in the batch kernel, bench.py's launch went from 10.87 to 11.29 ms (register allocation of the hot loop shifts)
+      if (f0 + fr < n_frames)
+        P.net_in[(f0 + fr) * (STRIDED ? P.net_in_stride : (long long)kNCoeff) + c] = (int8_t)net_input_q7(out[32 * fr + c], T);
     }
   }
   __syncwarp();
 }
 
-template <bool ALIGNED>
+template <bool ALIGNED, bool STRIDED>
 __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   CtaSmem &S = *reinterpret_cast<CtaSmem *>(smem_raw);
@@ -195,14 +199,16 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
         __syncwarp();
       }
     }
-    group_tail(P, T, W, lane, grp, n_frames);
+    group_tail<STRIDED>(P, T, W, lane, grp, n_frames);
   }
 }
 
 cudaError_t mfcc_q15_configure(void) {
-  cudaError_t e = cudaFuncSetAttribute(mfcc_q15_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
-  if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(mfcc_q15_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
+  cudaError_t e = cudaFuncSetAttribute(mfcc_q15_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(mfcc_q15_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(mfcc_q15_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(mfcc_q15_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
+  return e;
 }
 
 cudaError_t launch_mfcc_q15(const MfccLaunch &p, int sm_count, cudaStream_t stream) {
@@ -216,8 +222,11 @@ cudaError_t launch_mfcc_q15(const MfccLaunch &p, int sm_count, cudaStream_t stre
   warps = warps >= kWarpsPerCta ? kWarpsPerCta : (warps + 3) / 4 * 4;
   const unsigned threads = (unsigned)warps * 32;
   const bool aligned = (reinterpret_cast<uintptr_t>(p.pcm) & 3u) == 0 && (p.clip_stride & 1) == 0;
-  if (aligned) mfcc_q15_kernel<true><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
-  else mfcc_q15_kernel<false><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
+  const bool strided = p.net_in && p.net_in_stride != kNCoeff;
+  if (aligned && !strided) mfcc_q15_kernel<true, false><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
+  else if (!strided) mfcc_q15_kernel<false, false><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
+  else if (aligned) mfcc_q15_kernel<true, true><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
+  else mfcc_q15_kernel<false, true><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
   count_launch();
   return cudaGetLastError();
 }
