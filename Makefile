@@ -11,9 +11,9 @@ CSRC      := edison_b200/csrc
 OBJDIR    := build
 LIB       := edison_b200/libedison_b200.so
 
-CU_SRCS   := $(CSRC)/mfcc_q15_kernel.cu $(CSRC)/nnom_q7_kernel.cu $(CSRC)/nnom_q7_umma.cu $(CSRC)/edison_api.cu $(CSRC)/stream.cu $(CSRC)/mfcc_float.cu $(CSRC)/cube_f32_kernel.cu $(CSRC)/nnom_generic.cu
+CU_SRCS   := $(CSRC)/mfcc_q15_kernel.cu $(CSRC)/nnom_q7_kernel.cu $(CSRC)/nnom_q7_umma.cu $(CSRC)/edison_api.cu $(CSRC)/stream.cu $(CSRC)/mfcc_float.cu $(CSRC)/cube_f32_kernel.cu $(CSRC)/nnom_generic.cu $(CSRC)/noalloc.cu
 HDRS      := $(CSRC)/k2_umma_plan.h $(CSRC)/nnom_blob.h $(CSRC)/q15_arith.cuh $(CSRC)/mfcc_q15_core.cuh $(CSRC)/edison_internal.h include/edison_b200.h
-OBJS      := $(OBJDIR)/mfcc_q15_kernel.o $(OBJDIR)/nnom_q7_kernel.o $(OBJDIR)/nnom_q7_umma.o $(OBJDIR)/edison_api.o $(OBJDIR)/stream.o $(OBJDIR)/mfcc_float.o $(OBJDIR)/cube_f32_kernel.o $(OBJDIR)/nnom_generic.o $(OBJDIR)/tables.o $(OBJDIR)/firmware_api.o
+OBJS      := $(OBJDIR)/mfcc_q15_kernel.o $(OBJDIR)/nnom_q7_kernel.o $(OBJDIR)/nnom_q7_umma.o $(OBJDIR)/edison_api.o $(OBJDIR)/stream.o $(OBJDIR)/mfcc_float.o $(OBJDIR)/cube_f32_kernel.o $(OBJDIR)/nnom_generic.o $(OBJDIR)/noalloc.o $(OBJDIR)/tables.o $(OBJDIR)/firmware_api.o
 
 all: $(LIB)
 

@@ -48,6 +48,7 @@ def lib():
         L.edison_mfcc_q15_clips_dev.argtypes = [vp, sz, sz, sz, vp, vp, vp]
         L.edison_infer_q7_batch_dev.argtypes = [vp, sz, vp, vp, vp]
         L.edison_kws_batch_dev.argtypes = [vp, sz, sz, vp, vp, vp, vp]
+        L.edison_kws_batch_noalloc_dev.argtypes = [vp, sz, sz, vp, vp, vp]
         L.edison_sync.argtypes = [vp]
         L.edison_kws_counts_dev.argtypes = [vp, sz, sz, vp, vp, vp, vp, vp]
         L.edison_infer_q7_counts_dev.argtypes = [vp, sz, vp, vp, vp, vp]

@@ -197,6 +197,20 @@ int edison_kws_counts_dev(const int16_t *d_pcm, size_t n_clips, size_t clip_stri
 int edison_infer_q7_counts_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax,
                                int32_t *d_class_counts, void *stream);
 int edison_sync(void *stream);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  edison_kws_batch_dev without the caller-provided
+ * d_net_in scratch: the [n_clips][403] network input that K1 writes and K2 reads lives in a static device array of
+ * EDISON_NOALLOC_MAX_CLIPS x 403 bytes (3.15 MiB, held by every GPU that loads the library until the process exits).
+ * The call performs no cudaMalloc / cudaFree / cudaMallocHost and calls no allocating library routine; it therefore does
+ * NOT initialise the library: EDISON_E_NOINIT unless edison_init() succeeded before.  n_clips beyond the maximum is
+ * EDISON_E_ARG (split the batch or use edison_kws_batch_dev).  Asynchronous on `stream` like the other _dev variants;
+ * results are the same bytes edison_kws_batch_dev produces.  All calls share the one array: calls whose kernels may
+ * overlap on the GPU (different streams without a dependency) race; calls on one stream are ordered and safe.  Nothing
+ * in the array needs clearing between calls (K1 stores every byte K2 reads).  The first call on a device looks the
+ * array's address up (cudaGetSymbolAddress, no allocation): make it once before starting a graph capture. */
+#define EDISON_NOALLOC_MAX_CLIPS 8192
+int edison_kws_batch_noalloc_dev(const int16_t *d_pcm, size_t n_clips, size_t clip_stride_samples,
+                                 int8_t *d_logits, int8_t *d_softmax, void *stream);
 
 /* ---- section 3b: continuous streaming (appMicMfccInfereContinuous, firmware/src/app.c:288-394, and its ISR
  *      appAudioEvent app.c:635-661) over n concurrent streams pinned to this GPU.  Per hop of 1024 new samples
