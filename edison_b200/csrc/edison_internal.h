@@ -18,6 +18,7 @@ struct MfccLaunch {
   int8_t *net_in;              // device: 13 int8 per frame at net_in + frame * net_in_stride, or nullptr
   long long net_in_stride;     // bytes between consecutive frames' rows: 13 = packed [n_frames][13]; 403 = one row of n windows
   const MfccTables *tables;    // device
+  int group_frames = 8;        // set by launch_mfcc_q15: frames per warp group (8; 1, 2 or 4 for small launches)
 };
 // fills the twiddle / split / sqrt-exception tables (formula-generated, checksummed against the
 // values of the reference's CMSIS build) and copies the mel blob in; returns 0 or EDISON_E_*

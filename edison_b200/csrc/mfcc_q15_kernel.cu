@@ -92,9 +92,10 @@ __device__ __forceinline__ void mel_mma(int lane, int half, const MfccTables &T,
 }
 
 // dct2_q15 + outputs for the 8 frames of group grp, whose mel spectra sit in W.mel
-template <bool STRIDED>
+// SMALL: a group holds only `gf` (1, 2 or 4) frames -- f0 = grp * gf, slots gf..7 carry stale data and are not stored
+template <bool STRIDED, bool SMALL>
 __device__ __forceinline__ void group_tail(const MfccLaunch &P, const MfccTables &T, WarpSmem &W, int lane, long long grp,
-                                           long long n_frames) {
+                                           long long n_frames, int gf) {
   // dct2_q15 for the 8 frames of the group, 4 lanes per frame
   I2 *z = reinterpret_cast<I2 *>(W.x);
   int *out = reinterpret_cast<int *>(W.x) + 2 * kGroup * 16;
@@ -105,10 +106,10 @@ __device__ __forceinline__ void group_tail(const MfccLaunch &P, const MfccTables
 #pragma unroll
   for (int it = 0; it < 4; it++) dct_split(32 * it + lane, T, z, out);
   __syncwarp();
-  const long long f0 = grp * kGroup;
+  const long long f0 = grp * (SMALL ? gf : kGroup);
   if (P.mfcc) {  // 8 frames x 64 B, one 16-byte store per lane
     const int fr = lane >> 2, part = lane & 3;
-    if (f0 + fr < n_frames) {
+    if (f0 + fr < n_frames && (!SMALL || fr < gf)) {
       const int *o = out + 32 * fr + 8 * part;
       uint4 v;
       v.x = (uint32_t)(o[0] & 0xffff) | ((uint32_t)o[1] << 16);
@@ -123,14 +124,17 @@ __device__ __forceinline__ void group_tail(const MfccLaunch &P, const MfccTables
       const int fr = idx / kNCoeff, c = idx - fr * kNCoeff;
             // STRIDED (the streaming path: one row of each stream's window) is a separate instantiation: with the stride as a run-time
       // value in the batch kernel, bench.py's launch went from 10.87 to 11.29 ms (register allocation of the hot loop shifts)
-      if (f0 + fr < n_frames)
+      if (f0 + fr < n_frames && (!SMALL || fr < gf))
         P.net_in[(f0 + fr) * (STRIDED ? P.net_in_stride : (long long)kNCoeff) + c] = (int8_t)net_input_q7(out[32 * fr + c], T);
     }
   }
   __syncwarp();
 }
 
-template <bool ALIGNED, bool STRIDED>
+// SMALL (latency path, launches of < 11,841 frames): groups of P.group_frames = 1, 2 or 4 frames instead of 8, so that a hop of a
+// thousand streams is one frame on each of a thousand warps spread over all SMs instead of eight frames in a row on 128 warps.
+// The batch instantiations do not read P.group_frames: their hot loop is unchanged.
+template <bool ALIGNED, bool STRIDED, bool SMALL>
 __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   CtaSmem &S = *reinterpret_cast<CtaSmem *>(smem_raw);
@@ -144,7 +148,8 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpSmem &W = S.w[warp];
   const long long n_frames = P.n_clips * P.frames_per_clip;
-  const long long n_groups = (n_frames + kGroup - 1) / kGroup;
+  const int gf = SMALL ? P.group_frames : kGroup;   // frames per group
+  const long long n_groups = (n_frames + gf - 1) / gf;
   const int warps_per_cta = blockDim.x >> 5;   // a multiple of 4, at most kWarpsPerCta (small launches run fewer warps)
   // work is dealt to barrier groups (4 warps) CTA-minor: the last, partial trip then leaves a group or two busy on EVERY SM
   // instead of filling the first few SMs completely (a 100,000-frame hop of the streaming path is 4.2 trips)
@@ -154,7 +159,7 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   uint32_t w[16];
 #pragma unroll
   for (int q = 0; q < 16; q++) w[q] = 0;
-  if (warp_global < n_groups) load_frame<ALIGNED>(P, warp_global * kGroup, lane, w);
+  if (warp_global < n_groups) load_frame<ALIGNED>(P, warp_global * gf, lane, w);
   // Lockstep in groups of four warps, one warp per scheduler (named barrier 1 + warp/4, once per frame).  Warps that run
   // the same code at the same time share their instruction fetches (free-running warps: 12.2 ms for bench.py's launch), but
   // warps that share a SCHEDULER then also want the same pipe at the same time -- the FFT stages are ALU/IMAD throughput
@@ -167,15 +172,15 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
   for (long long it = 0, grp = warp_global; it < n_iter; it++, grp += warp_stride) {
     if (grp - (warp & 3) >= n_groups) break;   // none of the four warps of this barrier group has work left: all four leave
 #pragma unroll 1
-    for (int g = 0; g < kGroup; g++) {
-      const long long f = grp * kGroup + g;
+    for (int g = 0; g < gf; g++) {
+      const long long f = grp * gf + g;
       uint32_t *row = W.spect + (g & (kSub - 1)) * kSpectRowWords;
       asm volatile("bar.sync %0, 128;" ::"r"(bar_id));
       const bool sat = __reduce_max_sync(0xffffffffu, lane_peak(w)) > kNoSatPeak;
 #pragma unroll 1
       for (int e = 0; e < 2; e++) phase_a(lane, e, w, T, W.x);
       // prefetch the next frame this warp will process; it lands while phases B, C and mel run
-      const long long fn = g + 1 < kGroup ? f + 1 : (grp + warp_stride) * kGroup;
+      const long long fn = g + 1 < gf ? f + 1 : (grp + warp_stride) * gf;
       if (fn < n_frames) load_frame<ALIGNED>(P, fn, lane, w);
       __syncwarp();
       if (sat) {
@@ -194,39 +199,60 @@ __global__ void __launch_bounds__(kThreads, 1) mfcc_q15_kernel(MfccLaunch P) {
         for (int s = 0; s < 2; s++) phase_c<false>(lane, s, T, W.x, row);
       }
       __syncwarp();
-      if ((g & (kSub - 1)) == kSub - 1) {
+      if ((g & (kSub - 1)) == kSub - 1 || (SMALL && g == gf - 1)) {
         mel_mma(lane, g / kSub, T, W.spect, W.mel);
         __syncwarp();
       }
     }
-    group_tail<STRIDED>(P, T, W, lane, grp, n_frames);
+    group_tail<STRIDED, SMALL>(P, T, W, lane, grp, n_frames, gf);
   }
 }
 
+template <bool A, bool S, bool M> static cudaError_t configure_one(void) {
+  return cudaFuncSetAttribute(mfcc_q15_kernel<A, S, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
+}
 cudaError_t mfcc_q15_configure(void) {
-  cudaError_t e = cudaFuncSetAttribute(mfcc_q15_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(mfcc_q15_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(mfcc_q15_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(mfcc_q15_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CtaSmem));
+  cudaError_t e = configure_one<true, false, false>();
+  if (e == cudaSuccess) e = configure_one<false, false, false>();
+  if (e == cudaSuccess) e = configure_one<true, true, false>();
+  if (e == cudaSuccess) e = configure_one<false, true, false>();
+  if (e == cudaSuccess) e = configure_one<true, false, true>();
+  if (e == cudaSuccess) e = configure_one<false, false, true>();
+  if (e == cudaSuccess) e = configure_one<true, true, true>();
+  if (e == cudaSuccess) e = configure_one<false, true, true>();
   return e;
 }
 
-cudaError_t launch_mfcc_q15(const MfccLaunch &p, int sm_count, cudaStream_t stream) {
+template <bool A, bool S> static void launch_one(const MfccLaunch &p, bool small, unsigned ctas, unsigned threads, cudaStream_t stream) {
+  if (small) mfcc_q15_kernel<A, S, true><<<ctas, threads, sizeof(CtaSmem), stream>>>(p);
+  else mfcc_q15_kernel<A, S, false><<<ctas, threads, sizeof(CtaSmem), stream>>>(p);
+}
+
+cudaError_t launch_mfcc_q15(const MfccLaunch &p_in, int sm_count, cudaStream_t stream) {
+  MfccLaunch p = p_in;
   const long long n_frames = p.n_clips * p.frames_per_clip;
   if (n_frames <= 0) return cudaSuccess;
-  const long long n_groups = (n_frames + kGroup - 1) / kGroup;
-  long long ctas = (n_groups + kWarpsPerCta - 1) / kWarpsPerCta;
+  // frames per group: 8, or -- when that would leave warp slots of the machine idle -- the smallest of 1, 2, 4 whose groups still
+  // fit the machine's warps in one trip (a small launch is a latency problem: frames in parallel on many warps, not in a row on few)
+  const long long slots = (long long)sm_count * kWarpsPerCta;
+  int gf = kGroup;
+  for (int c = 1; c < kGroup; c *= 2)
+    if ((n_frames + c - 1) / c <= slots) { gf = c; break; }
+  p.group_frames = gf;
+  const long long n_groups = (n_frames + gf - 1) / gf;
+  // barrier groups of four warps are dealt across the SMs first: CTAs = min(SMs, groups of four), then as many warps per CTA as needed
+  long long ctas = (n_groups + 3) / 4;
   if (ctas > sm_count) ctas = sm_count;
-  // warps per CTA: whole barrier groups of four, no more than the work needs
   long long warps = (n_groups + ctas - 1) / ctas;
   warps = warps >= kWarpsPerCta ? kWarpsPerCta : (warps + 3) / 4 * 4;
   const unsigned threads = (unsigned)warps * 32;
   const bool aligned = (reinterpret_cast<uintptr_t>(p.pcm) & 3u) == 0 && (p.clip_stride & 1) == 0;
   const bool strided = p.net_in && p.net_in_stride != kNCoeff;
-  if (aligned && !strided) mfcc_q15_kernel<true, false><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
-  else if (!strided) mfcc_q15_kernel<false, false><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
-  else if (aligned) mfcc_q15_kernel<true, true><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
-  else mfcc_q15_kernel<false, true><<<(unsigned)ctas, threads, sizeof(CtaSmem), stream>>>(p);
+  const bool small = gf != kGroup;
+  if (aligned && !strided) launch_one<true, false>(p, small, (unsigned)ctas, threads, stream);
+  else if (!strided) launch_one<false, false>(p, small, (unsigned)ctas, threads, stream);
+  else if (aligned) launch_one<true, true>(p, small, (unsigned)ctas, threads, stream);
+  else launch_one<false, true>(p, small, (unsigned)ctas, threads, stream);
   count_launch();
   return cudaGetLastError();
 }
