@@ -341,7 +341,14 @@ static const char *parse_v1(edison_model *m, std::vector<int8_t> &wbuf, const st
     uint32_t h[9];
     if (off + 36 > raw.size()) return "truncated";
     memcpy(h, &raw[off], 36);
-    off += 36 + (size_t)h[1] * h[2] * h[3] * h[4] + h[1];
+    // every factor is bounded by the blob size before it is multiplied in: a hostile header cannot wrap size_t
+    size_t nw = 1;
+    for (int k = 1; k <= 4; k++) {
+      if (h[k] == 0 || h[k] > raw.size() || nw > raw.size() / h[k]) return "truncated (layer larger than the blob)";
+      nw *= h[k];
+    }
+    if (nw + h[1] > raw.size() - off - 36) return "truncated";
+    off += 36 + nw + h[1];
     off = (off + 3) & ~(size_t)3;
   }
   if (off + 24 > raw.size()) return "trailer missing";

@@ -117,3 +117,10 @@ def test_gpu_generic_rejects_bad_blobs(edison, tmp_path):
     p = tmp_path / "bad.bin"
     p.write_bytes(b"EDNNQ7\0\0" + struct.pack("<II", 1, 1) + struct.pack("<9I", 2, 10, 1, 1, 999, 8, 0, 0, 0) + bytes(9990 + 10 + 24 + 8))
     assert L.edison_model_load(os.fsencode(str(p)), ctypes.byref(h)) == -6      # dense input does not match the 0x0x0 input
+    # header whose weight count wraps size_t: cout * kh * kw * cin = 2^32 * 2^32; refused as malformed data, nothing dereferenced
+    p2 = tmp_path / "hostile.bin"
+    p2.write_bytes(b"EDNNQ7\0\0" + struct.pack("<II", 1, 1) + struct.pack("<9I", 1, 0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF, 8, 0, 0, 0) + bytes(64))
+    assert L.edison_model_load(os.fsencode(str(p2)), ctypes.byref(h)) == -4
+    p3 = tmp_path / "hostile2.bin"      # 65536^4 = 2^64 wraps to 0
+    p3.write_bytes(b"EDNNQ7\0\0" + struct.pack("<II", 1, 1) + struct.pack("<9I", 1, 65536, 65536, 65536, 65536, 8, 0, 0, 0) + bytes(64))
+    assert L.edison_model_load(os.fsencode(str(p3)), ctypes.byref(h)) == -4
