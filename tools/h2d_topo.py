@@ -28,6 +28,34 @@ def rate(devs, bufs_h, bufs_d, reps):
     return len(devs) * reps * bufs_h[devs[0]].numel() / dt / 1e9
 
 
+def wc_rate(dst, size, reps):
+    """device 0, one stream: cudaHostAlloc(default) vs cudaHostAlloc(cudaHostAllocWriteCombined) as the source of the same copy"""
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")
+    rt.cudaHostAlloc.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_size_t, ctypes.c_uint]
+    rt.cudaMemcpy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]
+    rt.cudaFreeHost.argtypes = [ctypes.c_void_p]
+    res = {}
+    torch.cuda.set_device(0)
+    for name, flag in (("pinned", 0), ("pinned_write_combined", 4)):
+        p = ctypes.c_void_p()
+        if rt.cudaHostAlloc(ctypes.byref(p), size, flag) != 0:
+            res[name] = None
+            continue
+        ctypes.memset(p, 1, size)
+        best = 0.0
+        for _ in range(3):
+            torch.cuda.synchronize(0)
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                rt.cudaMemcpy(ctypes.c_void_p(dst.data_ptr()), p, size, 1)
+            torch.cuda.synchronize(0)
+            best = max(best, reps * size / (time.perf_counter() - t0) / 1e9)
+        res[name] = round(best, 1)
+        rt.cudaFreeHost(p)
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="gpurun_out/h2d_topo.json")
@@ -49,6 +77,7 @@ def main():
     for s in sets:
         rate(s, bufs_h, bufs_d, 1)   # warm-up
         out["sets"][",".join(map(str, s))] = round(max(rate(s, bufs_h, bufs_d, a.reps) for _ in range(3)), 1)
+    out["write_combined"] = wc_rate(bufs_d[0], size, a.reps)
     try:
         out["topo"] = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=60).stdout
     except Exception as e:   # noqa: BLE001
