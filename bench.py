@@ -354,6 +354,33 @@ def run_ours(args, rank, world, local_rank):
             "clips_per_s": n4 / (cfg4_ms / 1e3), "fp32_tflops": n4 * 1569504 / (cfg4_ms / 1e3) / 1e12}
     del x4, lg4, sm4
 
+    # ---- generic NNoM executor: the upstream keyword_spotting example of the reference tree (63 x 12 x 1 input,
+    # 4 conv + dense, 35 classes, 2.1 M MAC per input) on 65,536 device-resident inputs; tensor-core nodes vs the one-thread-per-output path
+    generic = None
+    blob = os.path.join(ROOT, "tests", "golden", "nnom_kws_example.bin")
+    if rank == 0 and os.path.exists(blob):
+        ng = 65536
+        with ed.Model(blob) as gm:
+            xg = torch.randint(-128, 128, (ng, gm.in_size), dtype=torch.int8, device=dev)
+            lgg = torch.empty(ng, gm.n_out, dtype=torch.int8, device=dev)
+            smg = torch.empty(ng, gm.n_out, dtype=torch.int8, device=dev)
+            outs = {}
+            for name, naive, reps in (("tensor_core_nodes", False, 10), ("one_thread_per_output", True, 3)):
+                gm.set_naive(naive)
+                for _ in range(2):
+                    chk(L.edison_model_infer(gm._h, P(xg), ng, P(lgg), P(smg)))       # synchronous (device pointers: no copies)
+                t0 = time.perf_counter()
+                for _ in range(reps):
+                    chk(L.edison_model_infer(gm._h, P(xg), ng, P(lgg), P(smg)))
+                outs[name] = ((time.perf_counter() - t0) / reps, lgg.clone())
+        generic = {"workload": "generic executor: upstream NNoM keyword_spotting example (tests/golden/nnom_kws_example.bin), 65,536 inputs x 756 int8, device resident",
+                   "inputs_per_s": ng / outs["tensor_core_nodes"][0], "ms": outs["tensor_core_nodes"][0] * 1e3,
+                   "int8_tops": ng * 2 * 2098240 / outs["tensor_core_nodes"][0] / 1e12,
+                   "one_thread_per_output_ms": outs["one_thread_per_output"][0] * 1e3,
+                   "speedup_over_one_thread_per_output": outs["one_thread_per_output"][0] / outs["tensor_core_nodes"][0],
+                   "same_logits_both_paths": bool(torch.equal(outs["tensor_core_nodes"][1], outs["one_thread_per_output"][1]))}
+        del xg, lgg, smg, outs
+
     # ---- e2e: edison_kws_batch() on pinned HOST buffers, H2D + D2H inside the timed region
     ne = E2E_CLIPS
     h_pcm = torch.empty(ne * CLIP, dtype=torch.int16).pin_memory()
@@ -503,6 +530,8 @@ def run_ours(args, rank, world, local_rank):
                                 "note": "algorithmic ops; the kernel issues ~1.6x more (wrap-around pixels, Toeplitz conv1) and is bound by "
                                         "epilogue latency, not by the tensor pipe (DESIGN.md 4)"}
         line["cfg4_float_cnn"] = cfg4
+        if generic:
+            line["generic_executor"] = generic
         line["float_mfcc"] = dict(float_stats, workload="mfcc_utils.mfcc arithmetic on 65,536 x 1 s clips (15 frames each), 1 GPU")
         if world == 1 and not args.no_cpu:
             sys.path.insert(0, os.path.join(ROOT, "oracle"))

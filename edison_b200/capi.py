@@ -69,6 +69,7 @@ def lib():
         L.edison_model_free.restype = None
         L.edison_model_shape.argtypes = [vp] + [ctypes.POINTER(ci)] * 4
         L.edison_model_infer.argtypes = [vp, vp, sz, vp, vp]
+        L.edison_model_set_naive.argtypes = [vp, ci]
         L.edison_infer_f32_batch.argtypes = [vp, sz, vp, vp]
         L.edison_infer_f32_batch_dev.argtypes = [vp, sz, vp, vp, vp]
         for t in ("f32", "f64"):
@@ -226,6 +227,10 @@ class Model:
         sm = np.empty((x.shape[0], self.n_out), dtype=np.int8)
         check(lib().edison_model_infer(self._h, _p(x), x.shape[0], _p(lg), _p(sm)), "edison_model_infer")
         return lg, sm
+
+    def set_naive(self, naive):
+        """debug / measurement: True = every node on the one-thread-per-output kernels (no tensor-core nodes)"""
+        check(lib().edison_model_set_naive(self._h, 1 if naive else 0), "edison_model_set_naive")
 
     def close(self):
         if self._h:

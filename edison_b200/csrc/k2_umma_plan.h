@@ -47,8 +47,9 @@ constexpr int kNetIn = 403;
 // weight image (built once on the host, copied in with one bulk copy)
 constexpr uint32_t W1_CHUNK = 288 * 16;                  // one K-chunk of a conv1 B matrix: rows [x third][tile E/O][px][c] x 16 bytes
 constexpr uint32_t OFF_W1 = 0;                           // 3 chunk pairs j x 2 chunks
-constexpr uint32_t OFF_W2 = OFF_W1 + 6 * W1_CHUNK;       // 5 x [2][32][16]
-constexpr uint32_t OFF_W3 = OFF_W2 + 5 * 1024;           // 9 x [2][64][16]
+constexpr uint32_t OFF_W2 = OFF_W1 + 6 * W1_CHUNK;       // 13 blocks of [32][16]: Z k0w0 k0w1 k0w2 Z k1w0 k1w1 k1w2 Z k2w0 k2w1 k2w2 Z (k = kx, w = ky)
+constexpr uint32_t W2_BLOCK = 512;
+constexpr uint32_t OFF_W3 = OFF_W2 + 13 * W2_BLOCK;      // 9 x [2][64][16]
 constexpr uint32_t OFF_W4 = OFF_W3 + 9 * 2048;           // 18 x [2][32][16]
 constexpr uint32_t OFF_WD = OFF_W4 + 18 * 1024;          // 3 x [2][16][16]
 constexpr uint32_t OFF_PAR = OFF_WD + 3 * 512;           // int32: seed1[16] seed2[32] seed3[64] seed4[32] seedd[16] rs[5] hi[5]
@@ -63,11 +64,11 @@ constexpr uint32_t RAW_BYTES = NC * kNetIn + 16;
 constexpr uint32_t OFF_C1P = OFF_RAW + RAW_BYTES;        // pooled conv1: 12 rows x 9 px (+2 px read by zero-weight / dropped taps)
 constexpr uint32_t OFF_C2P = OFF_C1P + 110 * PX;         // pooled conv2: 2 planes x (5 x 7 px + 1)
 constexpr uint32_t PLANE2 = 36 * PX;
-constexpr uint32_t OFF_C3 = OFF_C2P + 2 * PLANE2;        // conv3: 4 planes x (3 x 5 px + 1)
+constexpr uint32_t OFF_C4 = OFF_C2P + 2 * PLANE2;        // conv4: 2 planes x 3 px; the dense tile's unused rows (pixels 3..5) read on into the
+constexpr uint32_t PLANE4 = 3 * PX;                      //   next plane / conv3's buffer: they only feed accumulator rows nobody reads
+constexpr uint32_t OFF_C3 = OFF_C4 + 2 * PLANE4;         // conv3: 4 planes x (3 x 5 px + 1)
 constexpr uint32_t PLANE3 = 16 * PX;
-constexpr uint32_t OFF_C4 = OFF_C3 + 4 * PLANE3;         // conv4: 2 planes x (3 px + 3 read by the dense tile's unused rows)
-constexpr uint32_t PLANE4 = 6 * PX;
-constexpr uint32_t OFF_BAR = OFF_C4 + 2 * PLANE4;        // mbarriers full[4] empty[4] raw wts (80 B), TMEM base (+80), class histogram (+96, 40 B)
+constexpr uint32_t OFF_BAR = OFF_C3 + 4 * PLANE3;        // mbarriers full[4] empty[4] raw wts (80 B), TMEM base (+80), class histogram (+96, 40 B)
 constexpr uint32_t SMEM_BYTES = OFF_BAR + 144;
 static_assert(IMAGE_BYTES % 16 == 0 && RAW_BYTES % 16 == 0 && OFF_BAR % 16 == 0, "16-byte granularity");
 static_assert(SMEM_BYTES <= 232448, "more than the 227 KB a CTA can have");
@@ -92,17 +93,24 @@ constexpr Unit kSched[kUnits] = {
 //   that batch's C2 rows (end of the previous iteration); C4' 4 after the last conv3 tile; DN' 4 after C4';
 //   an epilogue never overwrites what an older batch's MMAs still read: C2(r0) comes after conv3 tiles 0, 1 (the readers of c2p row
 //   0), C2(r1) after tile 3, C2(r2) after tile 4; the conv1 units of batch b + 1 come after every C2 of batch b.
-constexpr int kMmaPerIter = 9 * 3 + 5 * 20 + 5 * 9 + 18 + 3;   // 193 MMAs per iteration (checked against mma_count in the host emulation)
-constexpr int kPosTranspose = 15;   // the epilogue of this unit also lays out the NEXT batch's input (conv1 of this batch is done with c0)
-constexpr int kPosNextRaw = 19;     // same slot as 15: once it is free the raw buffer is too; the issuing thread starts the next bulk copy
+constexpr int kMmaPerIter = 9 * 3 + 5 * 12 + 5 * 9 + 18 + 3;   // 153 MMAs per iteration (checked against mma_count in the host emulation)
+// The team that drains the dense unit (one warp's work: lane = clip) also lays out the NEXT batch's input with its other three warps:
+// conv1 of this batch is done with c0 by then (all MMAs before the dense unit's have completed), and the slot's next user, four units
+// later, is the first conv1 unit of the next iteration -- the one unit that needs the new layout, so its slot wait is the dependency.
+// (At position 15, C2(r0), the extra ~2,500 cycles held a slot that C2(r3) was waiting for: profiles/r02g_k2_trace.txt.)
+constexpr int kPosTranspose = 17;
+constexpr int kPosNextRaw = 0;      // first unit of an iteration, same slot as 17 of the iteration before: the raw buffer has been consumed,
+                                    // the issuing thread starts the bulk copy of the batch after the next
+
+static_assert(kSched[kPosTranspose].kind == DN && kUnits - kPosTranspose + kPosNextRaw == kSlots, "transpose slot = first slot of the next iteration");
 
 struct MmaOp { uint32_t a_off, a_lbo, b_off, b_lbo, n, col, acc; };   // SBO = 128 for every operand; col relative to the slot
 
 // Closed forms instead of tables: the kernel's loops must stay small AND must not stream tables through the constant cache
 // (sixteen-plus specialised unit bodies were ~170 KB of SASS and every unit's code came from L2 once per iteration; 13 KB of
 // per-unit tables in constant memory missed that cache just as steadily: profiles/r02b_k2_trace.txt).
-K2_HD constexpr int mma_count(const Unit &u) { return u.kind == C1 ? 3 : u.kind == C2 ? 20 : u.kind == C3 ? 9 * u.b : u.kind == C4 ? 18 : 3; }
-K2_HD constexpr uint32_t mma_n(const Unit &u) { return u.kind == C1 ? 96u : u.kind == C3 ? 64u : u.kind == DN ? 16u : 32u; }
+K2_HD constexpr int mma_count(const Unit &u) { return u.kind == C1 ? 3 : u.kind == C2 ? 12 : u.kind == C3 ? 9 * u.b : u.kind == C4 ? 18 : 3; }
+K2_HD constexpr uint32_t mma_n(const Unit &u) { return u.kind == C1 ? 96u : (u.kind == C3 || u.kind == C2) ? 64u : u.kind == DN ? 16u : 32u; }
 
 // the m-th MMA of unit u, in issue order
 K2_HD constexpr MmaOp mma_op(const Unit &u, int m) {
@@ -114,14 +122,19 @@ K2_HD constexpr MmaOp mma_op(const Unit &u, int m) {
     return MmaOp{OFF_C0 + (uint32_t)(4 * u.a + m) * PX, C0_HALF, OFF_W1 + (uint32_t)m * 2 * W1_CHUNK + (uint32_t)u.b * 96 * 16, W1_CHUNK, 96, 0,
                  (uint32_t)(m > 0)};
   } else if (u.kind == C2) {
-    // pooled row r: conv rows y = 2r + p (p = 0, 1), x halves h: tile (p, h) at columns (2p + h) * 32, pixels x = 4h..4h+3;
-    // five MMAs per tile: taps (mm, 0) + (mm, 1) for mm = 0..2 (chunk 1 = next pixel), (0, 2) + (1, 2) (chunk 1 = next row),
-    // (2, 2) + zero weights
-    const int tile = m / 5, mm = m - 5 * tile, p = tile >> 1, h = tile & 1;
-    const uint32_t y = 2 * u.a + p, col = (uint32_t)tile * 32;
-    if (mm < 3) return MmaOp{OFF_C1P + ((y + mm) * 9 + 4 * h) * PX, PX, OFF_W2 + (uint32_t)mm * 1024, 512, 32, col, (uint32_t)(mm > 0)};
-    if (mm == 3) return MmaOp{OFF_C1P + (y * 9 + 4 * h + 2) * PX, 9 * PX, OFF_W2 + 3 * 1024, 512, 32, col, 1};
-    return MmaOp{OFF_C1P + ((y + 2) * 9 + 4 * h + 2) * PX, PX, OFF_W2 + 4 * 1024, 512, 32, col, 1};
+    // pooled row r, x half h (pixels x = 4h..4h+3): ONE accumulator tile of N = 64 holds both conv rows under the pooled row --
+    // columns 0..31 the odd row y = 2r + 1, columns 32..63 the even row y = 2r (like conv1's E / O tiles: same A rows, so the
+    // 2x1 max pool is a max between two registers of one lane).  A walks the four input rows 2r + i, i = 0..3; the B block
+    // pair for input row i is [w(ky = i - 1) | w(ky = i)] with zero blocks for ky = -1 and ky = 3, which the block order
+    // Z w0 w1 w2 Z provides as 1,024 contiguous bytes starting at block i.  Six MMAs per x half (conv2 used to be five N = 32
+    // MMAs per conv row and x half: 20 per unit; an MMA costs the same ~60 cycles for N = 32 and N = 64):
+    //   mm = 0..3: input row i = mm, taps kx = 0 (chunk 0) and kx = 1 (chunk 1 = next pixel);
+    //   mm = 4, 5: kx = 2 of input rows 2(mm - 4) (chunk 0) and 2(mm - 4) + 1 (chunk 1 = next row)
+    const int h = m / 6, mm = m - 6 * h;
+    const uint32_t y0 = 2 * u.a, col = (uint32_t)h * 64;
+    if (mm < 4) return MmaOp{OFF_C1P + ((y0 + mm) * 9 + 4 * h) * PX, PX, OFF_W2 + (uint32_t)mm * W2_BLOCK, 4 * W2_BLOCK, 64, col, (uint32_t)(mm > 0)};
+    const uint32_t i0 = 2 * (uint32_t)(mm - 4);
+    return MmaOp{OFF_C1P + ((y0 + i0) * 9 + 4 * h + 2) * PX, 9 * PX, OFF_W2 + (8 + i0) * W2_BLOCK, W2_BLOCK, 64, col, 1};
   } else if (u.kind == C3) {
     // tile tau: output positions q = 4 tau .. 4 tau + 3 on the 7-wide input grid (y = q / 7, x = q % 7; x >= 5 dropped)
     const int tl = m / 9, tap = m - 9 * tl, ky = tap / 3, kx = tap - 3 * ky;
@@ -268,11 +281,11 @@ template <class Ctx> K2_HD void epilogue_conv(Ctx &c, const Unit &u) {
     });
   } else if (u.kind == C2) {
     // pooled row u.a; job j: x half h = j >> 1, channel half j & 1; x = 4h + q (x = 7, i.e. q = 3 in the second half, is the
-    // wrap-around pixel); tile (p, h) at columns (2p + h) * 32
+    // wrap-around pixel); x half h at columns 64 h: odd conv row at +0, even conv row at +32
     const uint32_t out = OFF_C2P + (uint32_t)(u.a * 7 + c.q) * PX + lane16;
     job_stream<true>(c, c.q < 3 ? 4 : 2, c.par(PAR_RS + 1), c.par(PAR_HI + 1), [&](int j) {
       const uint32_t h = (uint32_t)j >> 1, half = (uint32_t)j & 1;
-      return JobParams{h * 32 + half * 16, (2 + h) * 32 + half * 16, (uint32_t)PAR_SEED2 + half * 16, out + half * PLANE2 + h * 4 * PX};
+      return JobParams{h * 64 + 32 + half * 16, h * 64 + half * 16, (uint32_t)PAR_SEED2 + half * 16, out + half * PLANE2 + h * 4 * PX};
     });
   } else if (u.kind == C3) {
     // one tile: position idx = 4 u.a + q on the 7-wide grid (x >= 5 and row 3 are wrap-around positions); four 16-channel planes
@@ -361,14 +374,12 @@ inline void build_image(uint8_t *img, const int8_t *const w[5], const int8_t *co
             for (int kx = 0; kx < 5; kx++)
               chunk[((x / 3) * 96 + p * 48 + (x % 3) * 16 + c) * 16 + x + kx] = (uint8_t)w[0][(c * 5 + ky) * 5 + kx];
       }
-  // conv2: matrix m = [chunk][n][16]; taps per chunk as in for_each_mma
-  const int tap2[5][2] = {{0, 1}, {3, 4}, {6, 7}, {2, 5}, {8, -1}};
-  for (int m = 0; m < 5; m++)
-    for (int h = 0; h < 2; h++) {
-      if (tap2[m][h] < 0) continue;
+  // conv2: block 4 kx + 1 + ky = [n][16] weights of tap (ky, kx); blocks 0, 4, 8, 12 stay zero (mma_op, C2)
+  for (int kx = 0; kx < 3; kx++)
+    for (int ky = 0; ky < 3; ky++)
       for (int n = 0; n < 32; n++)
-        for (int kk = 0; kk < 16; kk++) img[OFF_W2 + m * 1024 + h * 512 + n * 16 + kk] = (uint8_t)w[1][n * 144 + tap2[m][h] * 16 + kk];
-    }
+        for (int kk = 0; kk < 16; kk++)
+          img[OFF_W2 + (4 * kx + 1 + ky) * W2_BLOCK + n * 16 + kk] = (uint8_t)w[1][n * 144 + (ky * 3 + kx) * 16 + kk];
   for (int tap = 0; tap < 9; tap++)
     for (int h = 0; h < 2; h++)
       for (int n = 0; n < 64; n++)

@@ -76,6 +76,116 @@ __global__ void gen_conv_kernel(const int8_t *__restrict__ in, int8_t *__restric
   }
 }
 
+// ---- tensor-core path for conv / dense nodes whose input channel count is a multiple of 4 ------------------------------------
+// Implicit GEMM on mma.sync.m16n8k32.s8 (the per-node activations live in HBM here, so operands are register fragments, not
+// shared-memory descriptors: K2 is the tcgen05 path of the tuned model): M = output pixels of all inputs, N = output channels,
+// K = (ky, kx, c) in the reference's O,H,W,I weight order.  With C % 4 == 0 every A register (4 consecutive k) is 4 channels of
+// one tap = one aligned 32-bit load from the [n][H][W][C] activation buffer; taps outside the image contribute zero, which is
+// what the reference's tap skipping computes (nnom_local.c:425-483).  A warp owns 32 output pixels x up to 8 NT output
+// channels; the (tap -> byte offset) table of the node is built once per CTA in shared memory.  int32 accumulation is exact and
+// order independent, the epilogue is the reference's (bias << lshift) + round, >> rshift, SSAT8, ReLU: bit-exact.
+__device__ __forceinline__ void gen_mma_s8(int (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+constexpr int kGenMmaWarps = 8;
+
+template <int NT>
+__global__ void __launch_bounds__(kGenMmaWarps * 32) gen_conv_mma_kernel(const int8_t *__restrict__ in, int8_t *__restrict__ out,
+                                                                         const int8_t *__restrict__ w, const int8_t *__restrict__ b,
+                                                                         GenNode L, long long n_rows, int K, int bounds) {
+  extern __shared__ int2 s_tab[];   // per group of 4 k: x = byte offset from the pixel's window origin, y = (ky << 16) | kx, -1 past K
+  const int C = L.aC, O = L.C, HW = L.H * L.W;
+  const int nq = K >> 2, nq_pad = (nq + 7) & ~7;
+  for (int q = threadIdx.x; q < nq_pad; q += blockDim.x) {
+    int2 e = make_int2(0, -1);
+    if (q < nq) {
+      const int k = 4 * q, tap = k / C, c = k - tap * C, ky = tap / L.kw, kx = tap - ky * L.kw;
+      e = make_int2((ky * L.aW + kx) * C + c, (ky << 16) | kx);
+    }
+    s_tab[q] = e;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+  const long long n_tiles = (n_rows + 31) >> 5;
+  for (long long tile = (long long)blockIdx.x * kGenMmaWarps + warp; tile < n_tiles; tile += (long long)gridDim.x * kGenMmaWarps) {
+    // the four output pixels this thread feeds: rows 16 mt + 8 h + g of the tile
+    const int8_t *base[2][2];
+    int y0[2][2], x0[2][2];
+    long long row[2][2];
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const long long r = tile * 32 + mt * 16 + h * 8 + g;
+        row[mt][h] = r;
+        const long long rr = r < n_rows ? r : n_rows - 1;   // rows past the end recompute the last one and are not stored
+        const long long clip = rr / HW;
+        const int rem = (int)(rr - clip * HW), y = rem / L.W, x = rem - y * L.W;
+        y0[mt][h] = y * L.sh - L.ph;
+        x0[mt][h] = x * L.sw - L.pw;
+        base[mt][h] = in + clip * ((long long)L.aH * L.aW * C) + ((long long)y0[mt][h] * L.aW + x0[mt][h]) * C;
+      }
+    auto fetch = [&](int mt, int h, int2 e) -> uint32_t {
+      if (e.y < 0) return 0u;
+      if (bounds) {
+        const int yy = y0[mt][h] + (e.y >> 16), xx = x0[mt][h] + (e.y & 0xffff);
+        if (yy < 0 || yy >= L.aH || xx < 0 || xx >= L.aW) return 0u;
+      }
+      return __ldg(reinterpret_cast<const unsigned int *>(base[mt][h] + e.x));
+    };
+    for (int n0 = 0; n0 < O; n0 += 8 * NT) {
+      int acc[2][NT][4];
+#pragma unroll
+      for (int nt = 0; nt < NT; nt++) {
+        const int c0 = n0 + 8 * nt + 2 * t;
+        const int s0 = c0 < O ? (int)((unsigned)(int)b[c0] << L.lshift) + (1 << (L.rshift - 1)) : 0;
+        const int s1 = c0 + 1 < O ? (int)((unsigned)(int)b[c0 + 1] << L.lshift) + (1 << (L.rshift - 1)) : 0;
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) { acc[mt][nt][0] = s0; acc[mt][nt][1] = s1; acc[mt][nt][2] = s0; acc[mt][nt][3] = s1; }
+      }
+      for (int k0 = 0; k0 < K; k0 += 32) {
+        const int2 e0 = s_tab[(k0 >> 2) + t], e1 = s_tab[(k0 >> 2) + 4 + t];
+        uint32_t a[2][4];
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) {
+          a[mt][0] = fetch(mt, 0, e0); a[mt][1] = fetch(mt, 1, e0);
+          a[mt][2] = fetch(mt, 0, e1); a[mt][3] = fetch(mt, 1, e1);
+        }
+        const int klo = k0 + 4 * t, khi = klo + 16;
+#pragma unroll
+        for (int nt = 0; nt < NT; nt++) {
+          const int col = n0 + 8 * nt + g;
+          const int8_t *wr = w + (long long)col * K;
+          const uint32_t b0 = (col < O && klo < K) ? __ldg(reinterpret_cast<const unsigned int *>(wr + klo)) : 0u;
+          const uint32_t b1 = (col < O && khi < K) ? __ldg(reinterpret_cast<const unsigned int *>(wr + khi)) : 0u;
+          gen_mma_s8(acc[0][nt], a[0], b0, b1);
+          gen_mma_s8(acc[1][nt], a[1], b0, b1);
+        }
+      }
+#pragma unroll
+      for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          if (row[mt][h] >= n_rows) continue;
+          int8_t *dst = out + row[mt][h] * O;
+#pragma unroll
+          for (int nt = 0; nt < NT; nt++)
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+              const int col = n0 + 8 * nt + 2 * t + j;
+              if (col >= O) continue;
+              int v = g_ssat8(acc[mt][nt][2 * h + j] >> L.rshift);
+              if (L.relu && v < 0) v = 0;
+              dst[col] = (int8_t)v;
+            }
+        }
+    }
+  }
+}
+
 // dense: in [n][cin] (the flattened H,W,C output of the previous node), w [cout][cin]
 __global__ void gen_dense_kernel(const int8_t *__restrict__ in, int8_t *__restrict__ out, const int8_t *__restrict__ w,
                                  const int8_t *__restrict__ b, GenNode L, long long n) {
@@ -191,6 +301,7 @@ struct edison_model {
   long long arena_per_input; // bytes per input of all intermediate activations
   int8_t *d_arena, *d_in, *d_lg, *d_sm;
   size_t cap;                // inputs the scratch buffers hold
+  int naive;                 // debug: 1 = one thread per output element for every node (edison_model_set_naive)
 };
 
 namespace edison {
@@ -220,13 +331,38 @@ static int model_run(edison_model *m, const CtxView &c, const int8_t *d_in, size
     if (i == m->out_node) return d_logits;
     return m->d_arena + m->N[i].act_off * (long long)n;
   };
+  // tensor-core path: input channels (dense: the flattened input) a multiple of 4 and a 4-byte aligned input buffer
+  auto run_mma = [&](const GenNode &L0, const int8_t *src, int8_t *dst, bool dense) -> bool {
+    GenNode L = L0;
+    if (dense) { L.aC = L0.aH * L0.aW * L0.aC; L.aH = L.aW = 1; L.kh = L.kw = L.sh = L.sw = 1; L.ph = L.pw = 0; }
+    if (m->naive || (L.aC & 3) || (reinterpret_cast<uintptr_t>(src) & 3)) return false;
+    const int K = L.kh * L.kw * L.aC;
+    const size_t smem = (size_t)(((K >> 2) + 7) & ~7) * sizeof(int2);
+    if (smem > 48 * 1024) return false;
+    const long long n_rows = (long long)n * L.H * L.W, tiles = (n_rows + 31) / 32;
+    long long ctas = (tiles + kGenMmaWarps - 1) / kGenMmaWarps;
+    const long long cap = (long long)c.sm_count * 8;
+    if (ctas > cap) ctas = cap;
+    const int bounds = L.same || L.ph || L.pw;
+    const int8_t *w = m->d_w + L.w_off, *b = m->d_w + L.b_off;
+    if (L.C <= 16) gen_conv_mma_kernel<2><<<(unsigned)ctas, kGenMmaWarps * 32, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
+    else if (L.C <= 32) gen_conv_mma_kernel<4><<<(unsigned)ctas, kGenMmaWarps * 32, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
+    else gen_conv_mma_kernel<8><<<(unsigned)ctas, kGenMmaWarps * 32, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
+    return true;
+  };
   for (int i = 1; i < m->n_nodes; i++) {
     const GenNode &L = m->N[i];
     const long long total = (long long)n * L.H * L.W * L.C;
     int8_t *dst = act(i);
     switch (L.op) {
-      case G_CONV: gen_conv_kernel<<<blocks(total), threads, 0, st>>>(act(L.in[0]), dst, m->d_w + L.w_off, m->d_w + L.b_off, L, (long long)n); break;
-      case G_DENSE: gen_dense_kernel<<<blocks(total), threads, 0, st>>>(act(L.in[0]), dst, m->d_w + L.w_off, m->d_w + L.b_off, L, (long long)n); break;
+      case G_CONV:
+        if (!run_mma(L, act(L.in[0]), dst, false))
+          gen_conv_kernel<<<blocks(total), threads, 0, st>>>(act(L.in[0]), dst, m->d_w + L.w_off, m->d_w + L.b_off, L, (long long)n);
+        break;
+      case G_DENSE:
+        if (!run_mma(L, act(L.in[0]), dst, true))
+          gen_dense_kernel<<<blocks(total), threads, 0, st>>>(act(L.in[0]), dst, m->d_w + L.w_off, m->d_w + L.b_off, L, (long long)n);
+        break;
       case G_MAXPOOL:
       case G_GMAXPOOL: gen_maxpool_kernel<<<blocks(total), threads, 0, st>>>(act(L.in[0]), dst, L, (long long)n); break;
       case G_CONCAT: {
@@ -527,6 +663,15 @@ int edison_model_infer(edison_model *m, const int8_t *in, size_t n, int8_t *logi
   }
   ctx_unlock();
   return rc;
+}
+
+// debug / measurement: 1 = run every node on the one-thread-per-output kernels (the round-1 executor), 0 = tensor-core nodes where they apply
+int edison_model_set_naive(edison_model *m, int naive) {
+  if (!m) return ctx_fail(EDISON_E_ARG, "edison_model_set_naive: null model");
+  ctx_lock();
+  m->naive = naive ? 1 : 0;
+  ctx_unlock();
+  return EDISON_OK;
 }
 
 }  // extern "C"

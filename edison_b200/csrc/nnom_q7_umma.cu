@@ -8,12 +8,12 @@
 //     shared-memory descriptors (operands are never copied: a filter tap is a shifted start address), commits them to
 //     mbarrier full[slot]; it also starts the bulk copies (cp.async.bulk -> SASS UBLKCP) of the weight image and of each
 //     batch's 32 x 403 input bytes;
-//   * warps 0..15: wait on full[slot], read their lane quarter of the accumulators with tcgen05.ld (lane = clip), run the
+//   * warps 0..15, four teams of four (team t drains slot t): wait on full[slot], read their lane quarter of the accumulators with tcgen05.ld (lane = clip), run the
 //     integer epilogue of arm_convolve_HWC_q7_fast_nonsquare.c / nnom_local.c (bias seed, >> shift, SSAT8, ReLU, 2x1 max
 //     pool), store 16 channels as one 16-byte word in the next layer's operand layout, make the stores visible to the
 //     tensor core's asynchronous proxy, and release the slot (mbarrier empty[slot]);
-//   * the unit order interleaves the head of batch b with the tail of batch b - 1 so that no unit depends on the unit
-//     right before it: the only waits are the two-deep TMEM slot ring.
+//   * the unit order interleaves the head of batch b with the tail of batch b - 1 so that every unit's producers are
+//     at least four units older: the only waits are those of the four-slot TMEM ring (one team of four epilogue warps per slot).
 // There is no CPU path and no legacy mma.sync path behind this entry point.
 #include <stdio.h>
 #include <stdlib.h>
@@ -187,9 +187,10 @@ template <int POS, bool TRACE> struct IssueUnits {
     mbar_wait(bars + 32 + 8 * slot, par ^ 1);            // the team of this slot has drained its previous unit
     tc_fence_after();
     if (TRACE && trace && it == 1 && lane == 0) trace[4 * POS + 1] = clock64();
-    if (POS == kPosNextRaw && it + 2 < J.nbc && J.bulk(it + 2) && elect_one()) {   // raw was consumed by unit kPosTranspose's epilogue (same slot)
+    // raw (batch `it`'s bytes) was consumed by the epilogue of unit kPosTranspose of the previous iteration, whose slot this wait covered
+    if (POS == kPosNextRaw && it >= 1 && it + 1 < J.nbc && J.bulk(it + 1) && elect_one()) {
       mbar_expect_tx(bar_raw, NC * kNetIn);
-      bulk_g2s(sbase + OFF_RAW, J.net_in + J.batch(it + 2) * NC * kNetIn, NC * kNetIn, bar_raw);
+      bulk_g2s(sbase + OFF_RAW, J.net_in + J.batch(it + 1) * NC * kNetIn, NC * kNetIn, bar_raw);
     }
     if (U.lag ? it > 0 : it < J.nbc) IssueMmas<POS, 0>::go(tmem + slot * kSlotCols, sb4);
     umma_commit(bars + 8 * slot);
@@ -293,7 +294,7 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
           }
         }
         if (stamp && c.tracing) { trace[4 * kUnits] = c.t_ld; trace[4 * kUnits + 1] = clock64(); }
-        if (pos == kPosTranspose && it + 1 < J.nbc) transpose_in(smem, J, it + 1, bar_raw, (int)ttid);
+        if (pos == kPosTranspose && it + 1 < J.nbc && c.q > 0) transpose_in(smem, J, it + 1, bar_raw, (int)ttid - 32, 96);   // warp 0 of the team runs the dense epilogue
         fence_async_smem();   // this thread's shared-memory stores -> visible to the MMAs that will read them
         tc_fence_before();
         if (stamp && c.tracing) trace[4 * kUnits + 2] = clock64();

@@ -177,6 +177,9 @@ int edison_model_load(const char *blob_path, edison_model **out);
 void edison_model_free(edison_model *m);
 int edison_model_shape(const edison_model *m, int *in_h, int *in_w, int *in_c, int *n_out);
 int edison_model_infer(edison_model *m, const int8_t *in, size_t n, int8_t *logits, int8_t *softmax);
+/* debug / measurement: naive != 0 runs every node on the one-thread-per-output kernels instead of the tensor-core
+ * (mma.sync int8) conv / dense nodes used when a node's input channels are a multiple of 4; results are identical */
+int edison_model_set_naive(edison_model *m, int naive);
 
 /* ---- section 3: device-resident variants (all pointers are device pointers; stream is a
  *      cudaStream_t passed as void*, NULL = the library's own non-blocking stream; asynchronous.

@@ -178,6 +178,9 @@ def test_gpu_graph_vs_reference_runtime(edison, key):
         with edison.Model(blob_path(key)) as m:
             assert (m.in_shape, m.n_out) == MODELS[key]
             lg, sm = m.infer(g[key + "_x"])
+            m.set_naive(True)
+            lg_n, sm_n = m.infer(g[key + "_x"])
+            assert np.array_equal(lg, lg_n) and np.array_equal(sm, sm_n)
     finally:
         edison.set_softmax_mode(edison.SOFTMAX_CMSIS_SIMD)
     assert np.array_equal(lg, g[key + "_logits"])
@@ -200,11 +203,14 @@ def test_gpu_random_graphs_vs_oracle(edison, oracle, tmp_path, case):
             with edison.Model(blob) as m:
                 lg, sm = m.infer(x)
                 lg1, sm1 = m.infer(x[:1])                # a different batch size re-bases every arena offset
+                m.set_naive(True)                        # every node on the one-thread-per-output kernels: same bits
+                lg_n, sm_n = m.infer(x)
         finally:
             edison.set_softmax_mode(edison.SOFTMAX_CMSIS_SIMD)
         assert np.array_equal(lg, want_lg), "logits, mode %d" % mode
         assert np.array_equal(sm, want_sm), "softmax, mode %d" % mode
         assert np.array_equal(lg1, want_lg[:1]) and np.array_equal(sm1, want_sm[:1])
+        assert np.array_equal(lg_n, want_lg) and np.array_equal(sm_n, want_sm)
     assert np.unique(want_lg).size > 8
 
 

@@ -9,8 +9,8 @@ import torch
 import edison_b200 as ed
 
 KIND = ["C1(t0,x0)", "C3(0)'", "C1(t0,x1)", "C3(1)'", "C1(t0,x2)", "C3(2)'", "C1(t1,x0)", "C3(3)'", "C1(t1,x1)", "C3(4)'", "C1(t1,x2)", "C1(t2,x0)",
-        "C1(t2,x1)", "C4'", "C1(t2,x2)", "C2(r0)+T", "C2(r1)", "DN'", "C2(r2)", "C2(r3)", "C2(r4)"]   # ' = previous batch
-FINE = 15
+        "C1(t2,x1)", "C4'", "C1(t2,x2)", "C2(r0)", "C2(r1)", "DN'+T", "C2(r2)", "C2(r3)", "C2(r4)"]   # ' = previous batch
+FINE = 17
 NU = len(KIND)
 
 def main():
