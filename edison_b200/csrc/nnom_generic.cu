@@ -92,17 +92,21 @@ __device__ __forceinline__ void gen_mma_s8(int (&d)[4], const uint32_t (&a)[4], 
 
 constexpr int kGenMmaWarps = 8;
 
-template <int NT>
+// BYTES (input channels not a multiple of 4, e.g. the single-channel first layer of every model here): the table has one entry per
+// k and a register is assembled from four byte loads, each with its own tap test; weights likewise.  Still ~25x fewer loads per
+// output than one thread per output element.
+template <int NT, bool BYTES>
 __global__ void __launch_bounds__(kGenMmaWarps * 32) gen_conv_mma_kernel(const int8_t *__restrict__ in, int8_t *__restrict__ out,
                                                                          const int8_t *__restrict__ w, const int8_t *__restrict__ b,
                                                                          GenNode L, long long n_rows, int K, int bounds) {
   extern __shared__ int2 s_tab[];   // per group of 4 k: x = byte offset from the pixel's window origin, y = (ky << 16) | kx, -1 past K
   const int C = L.aC, O = L.C, HW = L.H * L.W;
-  const int nq = K >> 2, nq_pad = (nq + 7) & ~7;
+  const int step = BYTES ? 1 : 4;                                   // k per table entry
+  const int nq = BYTES ? K : K >> 2, nq_pad = BYTES ? (K + 31) & ~31 : (nq + 7) & ~7;
   for (int q = threadIdx.x; q < nq_pad; q += blockDim.x) {
     int2 e = make_int2(0, -1);
     if (q < nq) {
-      const int k = 4 * q, tap = k / C, c = k - tap * C, ky = tap / L.kw, kx = tap - ky * L.kw;
+      const int k = step * q, tap = k / C, c = k - tap * C, ky = tap / L.kw, kx = tap - ky * L.kw;
       e = make_int2((ky * L.aW + kx) * C + c, (ky << 16) | kx);
     }
     s_tab[q] = e;
@@ -136,6 +140,27 @@ __global__ void __launch_bounds__(kGenMmaWarps * 32) gen_conv_mma_kernel(const i
       }
       return __ldg(reinterpret_cast<const unsigned int *>(base[mt][h] + e.x));
     };
+    auto fetch_bytes = [&](int mt, int h, int k) -> uint32_t {      // k..k+3, one table entry and one byte load each
+      uint32_t v = 0;
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int2 e = s_tab[k + j];
+        if (e.y < 0) continue;
+        if (bounds) {
+          const int yy = y0[mt][h] + (e.y >> 16), xx = x0[mt][h] + (e.y & 0xffff);
+          if (yy < 0 || yy >= L.aH || xx < 0 || xx >= L.aW) continue;
+        }
+        v |= (uint32_t)(uint8_t)__ldg(base[mt][h] + e.x) << (8 * j);
+      }
+      return v;
+    };
+    auto weight_bytes = [&](const int8_t *wr, int k) -> uint32_t {
+      uint32_t v = 0;
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (k + j < K) v |= (uint32_t)(uint8_t)__ldg(wr + k + j) << (8 * j);
+      return v;
+    };
     for (int n0 = 0; n0 < O; n0 += 8 * NT) {
       int acc[2][NT][4];
 #pragma unroll
@@ -147,20 +172,34 @@ __global__ void __launch_bounds__(kGenMmaWarps * 32) gen_conv_mma_kernel(const i
         for (int mt = 0; mt < 2; mt++) { acc[mt][nt][0] = s0; acc[mt][nt][1] = s1; acc[mt][nt][2] = s0; acc[mt][nt][3] = s1; }
       }
       for (int k0 = 0; k0 < K; k0 += 32) {
-        const int2 e0 = s_tab[(k0 >> 2) + t], e1 = s_tab[(k0 >> 2) + 4 + t];
-        uint32_t a[2][4];
-#pragma unroll
-        for (int mt = 0; mt < 2; mt++) {
-          a[mt][0] = fetch(mt, 0, e0); a[mt][1] = fetch(mt, 1, e0);
-          a[mt][2] = fetch(mt, 0, e1); a[mt][3] = fetch(mt, 1, e1);
-        }
         const int klo = k0 + 4 * t, khi = klo + 16;
+        uint32_t a[2][4];
+        if (BYTES) {
+#pragma unroll
+          for (int mt = 0; mt < 2; mt++) {
+            a[mt][0] = fetch_bytes(mt, 0, klo); a[mt][1] = fetch_bytes(mt, 1, klo);
+            a[mt][2] = fetch_bytes(mt, 0, khi); a[mt][3] = fetch_bytes(mt, 1, khi);
+          }
+        } else {
+          const int2 e0 = s_tab[(k0 >> 2) + t], e1 = s_tab[(k0 >> 2) + 4 + t];
+#pragma unroll
+          for (int mt = 0; mt < 2; mt++) {
+            a[mt][0] = fetch(mt, 0, e0); a[mt][1] = fetch(mt, 1, e0);
+            a[mt][2] = fetch(mt, 0, e1); a[mt][3] = fetch(mt, 1, e1);
+          }
+        }
 #pragma unroll
         for (int nt = 0; nt < NT; nt++) {
           const int col = n0 + 8 * nt + g;
           const int8_t *wr = w + (long long)col * K;
-          const uint32_t b0 = (col < O && klo < K) ? __ldg(reinterpret_cast<const unsigned int *>(wr + klo)) : 0u;
-          const uint32_t b1 = (col < O && khi < K) ? __ldg(reinterpret_cast<const unsigned int *>(wr + khi)) : 0u;
+          uint32_t b0, b1;
+          if (BYTES) {
+            b0 = col < O ? weight_bytes(wr, klo) : 0u;
+            b1 = col < O ? weight_bytes(wr, khi) : 0u;
+          } else {
+            b0 = (col < O && klo < K) ? __ldg(reinterpret_cast<const unsigned int *>(wr + klo)) : 0u;
+            b1 = (col < O && khi < K) ? __ldg(reinterpret_cast<const unsigned int *>(wr + khi)) : 0u;
+          }
           gen_mma_s8(acc[0][nt], a[0], b0, b1);
           gen_mma_s8(acc[1][nt], a[1], b0, b1);
         }
@@ -331,13 +370,14 @@ static int model_run(edison_model *m, const CtxView &c, const int8_t *d_in, size
     if (i == m->out_node) return d_logits;
     return m->d_arena + m->N[i].act_off * (long long)n;
   };
-  // tensor-core path: input channels (dense: the flattened input) a multiple of 4 and a 4-byte aligned input buffer
+  // tensor-core path; word loads when the input channels (dense: the flattened input) are a multiple of 4 and the buffer is 4-byte aligned
   auto run_mma = [&](const GenNode &L0, const int8_t *src, int8_t *dst, bool dense) -> bool {
     GenNode L = L0;
     if (dense) { L.aC = L0.aH * L0.aW * L0.aC; L.aH = L.aW = 1; L.kh = L.kw = L.sh = L.sw = 1; L.ph = L.pw = 0; }
-    if (m->naive || (L.aC & 3) || (reinterpret_cast<uintptr_t>(src) & 3)) return false;
+    if (m->naive) return false;
     const int K = L.kh * L.kw * L.aC;
-    const size_t smem = (size_t)(((K >> 2) + 7) & ~7) * sizeof(int2);
+    const bool bytes = (L.aC & 3) || (reinterpret_cast<uintptr_t>(src) & 3);
+    const size_t smem = (size_t)(bytes ? (K + 31) & ~31 : ((K >> 2) + 7) & ~7) * sizeof(int2);
     if (smem > 48 * 1024) return false;
     const long long n_rows = (long long)n * L.H * L.W, tiles = (n_rows + 31) / 32;
     long long ctas = (tiles + kGenMmaWarps - 1) / kGenMmaWarps;
@@ -345,9 +385,16 @@ static int model_run(edison_model *m, const CtxView &c, const int8_t *d_in, size
     if (ctas > cap) ctas = cap;
     const int bounds = L.same || L.ph || L.pw;
     const int8_t *w = m->d_w + L.w_off, *b = m->d_w + L.b_off;
-    if (L.C <= 16) gen_conv_mma_kernel<2><<<(unsigned)ctas, kGenMmaWarps * 32, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
-    else if (L.C <= 32) gen_conv_mma_kernel<4><<<(unsigned)ctas, kGenMmaWarps * 32, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
-    else gen_conv_mma_kernel<8><<<(unsigned)ctas, kGenMmaWarps * 32, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
+    const unsigned grid = (unsigned)ctas, thr = kGenMmaWarps * 32;
+    if (bytes) {
+      if (L.C <= 16) gen_conv_mma_kernel<2, true><<<grid, thr, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
+      else if (L.C <= 32) gen_conv_mma_kernel<4, true><<<grid, thr, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
+      else gen_conv_mma_kernel<8, true><<<grid, thr, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
+    } else {
+      if (L.C <= 16) gen_conv_mma_kernel<2, false><<<grid, thr, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
+      else if (L.C <= 32) gen_conv_mma_kernel<4, false><<<grid, thr, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
+      else gen_conv_mma_kernel<8, false><<<grid, thr, smem, st>>>(src, dst, w, b, L, n_rows, K, bounds);
+    }
     return true;
   };
   for (int i = 1; i < m->n_nodes; i++) {
