@@ -29,8 +29,8 @@
 
 namespace edison {
 
-constexpr int kXchStride = 72;                 // complex units per radix-8 row: 64 + 8 keeps both transposes conflict-free
-constexpr int kXchLen = 8 * kXchStride;        // 576 >= 513
+constexpr int kXchStride = 34;                 // complex units per radix-16 output row: 32 + 2 keeps the transposing read conflict-free
+constexpr int kXchLen = 16 * kXchStride;       // 544 >= 512
 constexpr int kMagLen = 520;
 constexpr int kMelWMax = 1280;
 
@@ -41,9 +41,8 @@ template <> struct RealTraits<double> { static constexpr int kWarps = 12; };
 
 template <typename R>
 struct alignas(16) FloatTables {
-  Cx<R> tw1[7][2][32];         // W512^{(l + 32h) r}, r = 1..7      (pass 1)
-  Cx<R> tw2[7][8];             // W64^{m0 r'}, r' = 1..7            (pass 2)
-  Cx<R> tws[8][32];            // W1024^{l + 32 j}                  (real split)
+  Cx<R> twa[4][16];            // W256^{b p}, p = 1, 2, 4, 8; b = lane >> 1   (after pass A)
+  Cx<R> tws[32];               // W1024^{l}                                  (last radix-2 stage + real split)
   R dct_t[32][32];             // [n][k] = scale * 2 cos(pi k (2n+1) / 64)
   R mel_w[kMelWMax];           // non-zero weights filter by filter, times the spectrum scale of the mode (and the 1/2
                                // the split leaves out)
@@ -156,6 +155,33 @@ __device__ __forceinline__ void radix8(Cx<R> (&v)[8]) {
   }
 }
 
+// 16-point DFT, decimation in frequency into two radix-8 halves, natural order out: v[r] = sum_n v[n] W16^{n r}
+template <typename R>
+__device__ __forceinline__ void radix16(Cx<R> (&v)[16]) {
+  const R s = (R)0.70710678118654752440, c1 = (R)0.92387953251128675613, s1 = (R)0.38268343236508977173;
+  Cx<R> a[8], b[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) { a[i] = cadd(v[i], v[i + 8]); b[i] = csub(v[i], v[i + 8]); }
+  b[1] = cmul(b[1], Cx<R>{c1, -s1});                                // * W16^1
+  b[2] = Cx<R>{(b[2].x + b[2].y) * s, (b[2].y - b[2].x) * s};       // * W16^2 = W8^1
+  b[3] = cmul(b[3], Cx<R>{s1, -c1});                                // * W16^3
+  b[4] = mul_mj(b[4]);                                              // * W16^4 = -j
+  b[5] = cmul(b[5], Cx<R>{-s1, -c1});                               // * W16^5
+  b[6] = Cx<R>{(b[6].y - b[6].x) * s, -(b[6].x + b[6].y) * s};      // * W16^6 = W8^3
+  b[7] = cmul(b[7], Cx<R>{-c1, -s1});                               // * W16^7
+  radix8(a);
+  radix8(b);
+#pragma unroll
+  for (int r = 0; r < 8; r++) { v[2 * r] = a[r]; v[2 * r + 1] = b[r]; }
+}
+
+// two adjacent complex values: one 128-bit shared-memory access for float
+__device__ __forceinline__ void load_pair(const Cx<float> *p, Cx<float> &a, Cx<float> &b) {
+  const float4 v = *reinterpret_cast<const float4 *>(p);
+  a = Cx<float>{v.x, v.y}; b = Cx<float>{v.z, v.w};
+}
+__device__ __forceinline__ void load_pair(const Cx<double> *p, Cx<double> &a, Cx<double> &b) { a = p[0]; b = p[1]; }
+
 // (lo, hi) int16 pair -> two reals without the conversion pipe.
 //   float : 0x4B000000 | (x ^ 0x8000)  is 2^23 + x + 2^15
 //   double: 0x43300000:(x ^ 0x8000)    is 2^52 + x + 2^15
@@ -245,81 +271,73 @@ __global__ void __launch_bounds__(RealTraits<R>::kWarps * 32, 1) mfcc_float_kern
     }
     if (f + stride < n_frames) load_frame_words<ALIGNED>(frame_base(f + stride), lane, frame_len, pw);   // lands during the FFT
 
-    // ---- pass 1: over n2 (stride 64); lane holds m = lane + 32h, n2 = 0..7 in v[2 n2 + h]
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-      C t[8];
-#pragma unroll
-      for (int i = 0; i < 8; i++) t[i] = v[2 * i + h];
-      radix8(t);
-      W.xch[lane + 32 * h] = t[0];
-      // the kernel is bound by shared-memory wavefronts, not by the FMA pipe: W^1, W^2, W^4 are read, the other four
-      // twiddles are products of those (two roundings more at most)
-      C tw[8];
-      tw[1] = T.tw1[0][h][lane]; tw[2] = T.tw1[1][h][lane]; tw[4] = T.tw1[3][h][lane];
+    // The 512-point complex FFT of z[n] = x[2n] + j x[2n+1] as 16 x 16 x 2 (n = 32 a + 2 b + c, k = k0 + 16 k1 + 256 k2): two radix-16
+    // passes in registers with ONE shared-memory exchange between them and one after; the last radix-2 stage is folded into the
+    // real-input split, which reads pairs anyway (tools/proto/fft_16x16x2_flow.py checks this index flow against numpy).  The kernel
+    // is bound by shared-memory wavefronts: 8 x 8 x 8 needed three exchanges (228 wavefronts per frame for FFT + split; now 154).
+    // ---- pass A: over a (stride 32); lane m = 2 b + c holds z[32 a + m] in v[a]
+    radix16(v);
+    {
+      // twiddle W256^{b k0}, b = lane >> 1: W^1, W^2, W^4, W^8 are read (lane pairs share an entry), the other eleven are products of those
+      const int bq = lane >> 1;
+      C tw[16];
+      tw[1] = T.twa[0][bq]; tw[2] = T.twa[1][bq]; tw[4] = T.twa[2][bq]; tw[8] = T.twa[3][bq];
       tw[3] = cmul(tw[1], tw[2]); tw[5] = cmul(tw[4], tw[1]); tw[6] = cmul(tw[4], tw[2]); tw[7] = cmul(tw[4], tw[3]);
+      W.xch[lane] = v[0];
 #pragma unroll
-      for (int r = 1; r < 8; r++) W.xch[kXchStride * r + lane + 32 * h] = cmul(t[r], tw[r]);
+      for (int k0 = 1; k0 < 8; k0++) W.xch[kXchStride * k0 + lane] = cmul(v[k0], tw[k0]);
+      W.xch[kXchStride * 8 + lane] = cmul(v[8], tw[8]);
+#pragma unroll
+      for (int k0 = 9; k0 < 16; k0++) W.xch[kXchStride * k0 + lane] = cmul(v[k0], cmul(tw[8], tw[k0 - 8]));
     }
     __syncwarp();
-    // ---- pass 2: over m1; this lane takes m0 = lane & 7 and r = (lane >> 3) + 4h
-    const int lo3 = lane & 7, hi2 = lane >> 3;
+    // ---- pass B: over b; this lane takes k0 = lane >> 1 and c = lane & 1 (row stride 34: the 16 lanes of a wavefront hit 16 bank pairs)
+    {
+      const C *row = W.xch + kXchStride * (lane >> 1) + (lane & 1);
 #pragma unroll
-    for (int h = 0; h < 2; h++)
-#pragma unroll
-      for (int i = 0; i < 8; i++) v[8 * h + i] = W.xch[kXchStride * (hi2 + 4 * h) + 8 * i + lo3];
-    __syncwarp();
-    C tw2[8];
-    tw2[1] = T.tw2[0][lo3]; tw2[2] = T.tw2[1][lo3]; tw2[4] = T.tw2[3][lo3];
-    tw2[3] = cmul(tw2[1], tw2[2]); tw2[5] = cmul(tw2[4], tw2[1]); tw2[6] = cmul(tw2[4], tw2[2]); tw2[7] = cmul(tw2[4], tw2[3]);
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-      C t[8];
-#pragma unroll
-      for (int i = 0; i < 8; i++) t[i] = v[8 * h + i];
-      radix8(t);
-      const int r = hi2 + 4 * h;
-      const int col = 8 * r + (lo3 ^ r);
-      W.xch[col] = t[0];
-#pragma unroll
-      for (int rp = 1; rp < 8; rp++) W.xch[kXchStride * rp + col] = cmul(t[rp], tw2[rp]);
+      for (int b = 0; b < 16; b++) v[b] = row[2 * b];
     }
     __syncwarp();
-    // ---- pass 3: over m0; this lane takes r = lane & 7 and r' = (lane >> 3) + 4h; outputs k = 64 q + lane + 32 h
+    radix16(v);
+    // Y2[k0, k1; c] at element 2 (k0 + 16 k1) + c = lane + 32 k1: the pair (c = 0, c = 1) of one k is one 128-bit read below
 #pragma unroll
-    for (int h = 0; h < 2; h++)
-#pragma unroll
-      for (int i = 0; i < 8; i++) v[8 * h + i] = W.xch[kXchStride * (hi2 + 4 * h) + 8 * lo3 + (i ^ lo3)];
+    for (int k1 = 0; k1 < 16; k1++) W.xch[lane + 32 * k1] = v[k1];
     __syncwarp();
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-      C t[8];
-#pragma unroll
-      for (int i = 0; i < 8; i++) t[i] = v[8 * h + i];
-      radix8(t);
-#pragma unroll
-      for (int q = 0; q < 8; q++) W.xch[64 * q + lane + 32 * h] = t[q];
-      if (h == 0 && lane == 0) W.xch[512] = t[0];      // Z[512] = Z[0] for the k = 0 pair
-    }
-    __syncwarp();
-    // ---- real-input split on pairs (k, 512 - k), k = lane + 32 j; magnitudes are 2|X| (the 1/2 lives in mel_w)
-    const C ws0 = T.tws[0][lane];
-#pragma unroll
-    for (int j = 0; j < 8; j++) {
-      const int k = lane + 32 * j;
-      const C a = W.xch[k], bc = W.xch[512 - k];
-      // W1024^{lane + 32 j} = W1024^{lane} * W32^{j}: one read per frame, the eight W32 powers are constants
-      const C w = j ? cmul(ws0, C{(R)kW32[j][0], (R)kW32[j][1]}) : ws0;
-      const R er = a.x + bc.x, ei = a.y - bc.y;        // A + conj(Z[512-k])
-      const R dr = a.x - bc.x, di = a.y + bc.y;        // A - conj(Z[512-k])
+    // ---- last stage + real-input split.  For k = lane + 32 j < 128: (P, Q) = Y2[k; 0..1], Z[k] = P + W512^k Q, Z[k + 256] = P - W512^k Q;
+    //      the same for k' = 256 - k gives Z[256 - k] and Z[512 - k]; then the split on the pairs (k, 512 - k) and (256 - k, 256 + k).
+    //      Magnitudes are 2|X| (the 1/2 lives in mel_w).  W1024^k = W1024^lane * W32^j, W512^k is its square, W512^{256-k} = -conj(W512^k),
+    //      W1024^{256-k} = -j conj(W1024^k): one table read per frame.
+    auto split_pair = [&](C a, C bc, C w, int ka, int kb) {      // a = Z[ka], bc = Z[kb] with kb = 512 - ka, w = W1024^ka
+      const R er = a.x + bc.x, ei = a.y - bc.y;        // A + conj(B)
+      const R dr = a.x - bc.x, di = a.y + bc.y;        // A - conj(B)
       const R tr = w.x * di + w.y * dr, ti = w.y * di - w.x * dr;   // W^k * (-j D)
       const R x1r = er + tr, x1i = ei + ti, x2r = er - tr, x2i = ei - ti;
-      W.mag[k] = mag_from_power(x1r * x1r + x1i * x1i);
-      W.mag[512 - k] = mag_from_power(x2r * x2r + x2i * x2i);
+      W.mag[ka] = mag_from_power(x1r * x1r + x1i * x1i);
+      W.mag[kb] = mag_from_power(x2r * x2r + x2i * x2i);
+    };
+    const C ws0 = T.tws[lane];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int k = lane + 32 * j, kp = 256 - k;       // lane 0, j = 0 computes rubbish here (kp = 256) and repairs it below
+      const C w = j ? cmul(ws0, C{(R)kW32[j][0], (R)kW32[j][1]}) : ws0;
+      const C w2 = cmul(w, w);
+      C p, q, pp, qp;
+      load_pair(W.xch + 2 * k, p, q);
+      load_pair(W.xch + 2 * kp, pp, qp);
+      const C t = cmul(w2, q), tp = cmul(C{-w2.x, w2.y}, qp);
+      const C zk = cadd(p, t), zk256 = csub(p, t), zkp = cadd(pp, tp), z512k = csub(pp, tp);
+      split_pair(zk, z512k, w, k, 512 - k);
+      split_pair(zkp, zk256, C{-w.y, -w.x}, kp, 256 + k);
     }
     if (lane == 0) {
-      const C c = W.xch[256];
-      W.mag[256] = (R)2 * mag_from_power(c.x * c.x + c.y * c.y);
+      C p, q;
+      load_pair(W.xch, p, q);                          // k = 0: Z[0] = P + Q pairs with itself (Z[512] = Z[0]); Z[256] = P - Q
+      const C z0 = cadd(p, q), z256 = csub(p, q);
+      split_pair(z0, z0, C{(R)1, (R)0}, 0, 512);
+      W.mag[256] = (R)2 * mag_from_power(z256.x * z256.x + z256.y * z256.y);
+      load_pair(W.xch + 256, p, q);                    // k = 128: W512^128 = -j, W1024^128 = exp(-j pi / 4)
+      const C t = mul_mj(q);
+      split_pair(cadd(p, t), csub(p, t), C{(R)0.70710678118654752440, (R)-0.70710678118654752440}, 128, 384);
     }
     __syncwarp();
     // ---- mel: 4 lanes per filter, 8 filters per round.  Each lane takes aligned chunks of 4 bins (128-bit reads of the
@@ -436,22 +454,15 @@ template <typename R>
 static int fill_tables(FloatTables<R> &T, int mode) {
   memset(&T, 0, sizeof T);
   const double tau = 6.283185307179586476925286766559;
-  for (int r = 1; r < 8; r++)
-    for (int h = 0; h < 2; h++)
-      for (int l = 0; l < 32; l++) {
-        const double a = -tau * (double)(((l + 32 * h) * r) % 512) / 512.0;
-        T.tw1[r - 1][h][l] = Cx<R>{(R)cos(a), (R)sin(a)};
-      }
-  for (int r = 1; r < 8; r++)
-    for (int m0 = 0; m0 < 8; m0++) {
-      const double a = -tau * (double)((m0 * r) % 64) / 64.0;
-      T.tw2[r - 1][m0] = Cx<R>{(R)cos(a), (R)sin(a)};
+  for (int pi = 0; pi < 4; pi++)
+    for (int b = 0; b < 16; b++) {
+      const double a = -tau * (double)((b << pi) % 256) / 256.0;
+      T.twa[pi][b] = Cx<R>{(R)cos(a), (R)sin(a)};
     }
-  for (int j = 0; j < 8; j++)
-    for (int l = 0; l < 32; l++) {
-      const double a = -tau * (double)(l + 32 * j) / 1024.0;
-      T.tws[j][l] = Cx<R>{(R)cos(a), (R)sin(a)};
-    }
+  for (int l = 0; l < 32; l++) {
+    const double a = -tau * (double)l / 1024.0;
+    T.tws[l] = Cx<R>{(R)cos(a), (R)sin(a)};
+  }
   const int n_bins = mode == EDISON_MFCC_F32_HOST ? 512 : 513;
   const double spec_scale = mode == EDISON_MFCC_F32_HOST ? 1.0 : 1.0 / 1024.0 / sqrt(2.0);
   const double dct_scale = mode == EDISON_MFCC_F32_HOST ? 1.0 / sqrt(64.0) : 1.0 / 64.0;
