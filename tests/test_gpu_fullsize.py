@@ -73,10 +73,18 @@ def test_config2_983040_frames_bit_exact(edison, oracle):
     assert torch.equal(ni.to(torch.int16), mf2[:, :13].clamp(-128, 127))            # mfccToNetInput, app.c:684-693
 
 
-def test_config4_262144_float_clips_vs_pool(edison, oracle):
-    """float CNN at config #4's size: every result equals the result of the same input computed in a small batch"""
+def test_config4_262144_float_clips_vs_restatement(edison, oracle):
+    """float CNN at config #4's size: every one of the 262,144 results is compared with the fp64 restatement (oracle/cube_float.py) of
+    the same input, within the tolerance of tests/test_cube_float.py (softmax max-abs 1e-4, logits 1e-3 relative) -- the inputs are a
+    seeded gather of a pool whose restatement outputs cost 160 CPU evaluations; and the large launch equals a small-batch launch of
+    the same inputs bit for bit (per-clip arithmetic order does not depend on the batch)"""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(common.ROOT, "oracle"))
+    import cube_float as cf
     n, pool = 262144, 160
     x = oracle.mfcc(common.synth_frames(pool * 31, seed=505))[:, :13].astype(np.float32).reshape(pool, 403)
+    want_lg, want_sm = cf.forward(cf.load(os.path.join(common.ROOT, "edison_b200", "data", "kws_cube_f32.bin")), x)
     lg_small, sm_small = edison.infer_f32_batch(x)
     dev = torch.device("cuda")
     idx = torch.randint(0, pool, (n,), generator=torch.Generator().manual_seed(3))
@@ -87,5 +95,8 @@ def test_config4_262144_float_clips_vs_pool(edison, oracle):
     torch.cuda.synchronize()
     edison.capi.check(L.edison_infer_f32_batch_dev(P(xin), n, P(lg), P(sm), None))
     edison.capi.check(L.edison_sync(None))
-    assert np.array_equal(lg.cpu().numpy(), lg_small[idx.numpy()])      # same kernel, same per-clip arithmetic order: identical bits
-    assert np.array_equal(sm.cpu().numpy(), sm_small[idx.numpy()])
+    lg, sm, ix = lg.cpu().numpy(), sm.cpu().numpy(), idx.numpy()
+    assert np.abs(sm - want_sm[ix]).max() <= 1e-4
+    assert np.abs(lg - want_lg[ix]).max() <= 1e-3 * max(1.0, np.abs(want_lg).max())
+    assert np.array_equal(lg, lg_small[ix])      # same kernel, same per-clip arithmetic order: identical bits
+    assert np.array_equal(sm, sm_small[ix])
