@@ -141,6 +141,7 @@ int edison_streams_open(size_t n_streams, edison_streams **out) {
   if (e == cudaSuccess) e = cudaMemset(s->d_window, 0, n_streams * EDISON_NET_IN);   // netInput is zero-initialised static storage
   if (e == cudaSuccess) e = cudaMemset(s->d_filt, 0, n_streams * EDISON_N_CLASSES * sizeof(float));  // app.c:300
   if (e == cudaSuccess) e = cudaMemset(s->d_softmax, 0, n_streams * EDISON_N_CLASSES);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();   // the memsets ran on the legacy stream; the hops run on non-blocking streams that do not wait for it
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->compute, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->copy, cudaStreamNonBlocking);
   for (int i = 0; i < 2 && e == cudaSuccess; i++) {
@@ -184,6 +185,7 @@ int edison_streams_set_incremental(edison_streams *s, int on) {
     const size_t bytes = nnom_incr_state_bytes((long long)s->n);
     cudaError_t e = cudaMalloc(&s->d_incr, bytes);
     if (e == cudaSuccess) e = cudaMemset(s->d_incr, 0, bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) return ctx_fail(EDISON_E_NOMEM, "edison_streams_set_incremental: %s", cudaGetErrorString(e));
     nnom_incr_state_bind(&s->incr, s->d_incr, (long long)s->n);
   }
