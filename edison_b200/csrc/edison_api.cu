@@ -15,6 +15,7 @@
 #include <string>
 
 #include "edison_internal.h"
+#include <nvtx3/nvToolsExt.h>
 #include "../../include/edison_b200.h"
 
 namespace edison {
@@ -199,6 +200,9 @@ static int do_init(const edison_cfg *cfg) {
 
 int ctx_device(void) { return g.ready ? g.device : -1; }
 
+TraceRange::TraceRange(const char *label) { nvtxRangePushA(label); }
+TraceRange::~TraceRange() { nvtxRangePop(); }
+
 // 0 = null, 1 = host (pageable or pinned), 2 = device / managed
 static int ptr_kind(const void *p) {
   if (!p) return 0;
@@ -235,6 +239,7 @@ static int mfcc_dev(const int16_t *d_pcm, size_t n_clips, size_t fpc, size_t str
   MfccLaunch L;
   L.pcm = d_pcm; L.n_clips = (long long)n_clips; L.frames_per_clip = (int)fpc; L.clip_stride = (long long)stride;
   L.mfcc = d_mfcc; L.net_in = d_net_in; L.net_in_stride = EDISON_N_COEFF; L.tables = g.d_tables;
+  TraceRange r("audioCalcMFCCs");   // audioprocessing.c:123
   CU(launch_mfcc_q15(L, g.sm_count, st));
   return EDISON_OK;
 }
@@ -244,6 +249,7 @@ static int infer_dev(const int8_t *d_in, size_t n, int8_t *d_logits, int8_t *d_s
   if (!d_in || (!d_logits && !d_softmax && !d_counts)) return fail(EDISON_E_ARG, "null pointer");
   K2Launch k{};
   k.net_in = d_in; k.n = (long long)n; k.logits = d_logits; k.softmax = d_softmax; k.softmax_mode = g.softmax_mode; k.class_counts = d_counts;
+  TraceRange r("inference");        // app.c:207
   CU(launch_nnom_q7(g.d_model, k, g.sm_count, st));
   return EDISON_OK;
 }
@@ -280,6 +286,7 @@ static int kws_host_chunks(const int16_t *pcm, size_t n_clips, size_t fpc, size_
     if ((net_in || want_net) && (rc = ensure(&s.net_in, &s.net_in_cap, nf * EDISON_N_COEFF))) return rc;
     if (logits && (rc = ensure(&s.logits, &s.logits_cap, nc * EDISON_N_CLASSES))) return rc;
     if (softmax && (rc = ensure(&s.softmax, &s.softmax_cap, nc * EDISON_N_CLASSES))) return rc;
+    TraceRange chunk_range("appHifMfccAndInference");   // app.c:177; its events: "receive and MFCC" :199, "inference" :207
     CU(cudaMemcpyAsync(s.pcm, pcm + c0 * stride, in_samples * 2, cudaMemcpyHostToDevice, s.stream));
     int8_t *d_net = (net_in || want_net) ? (int8_t *)s.net_in : nullptr;
     if ((rc = mfcc_dev((const int16_t *)s.pcm, nc, fpc, stride, mfcc ? (int16_t *)s.mfcc : nullptr, d_net, s.stream))) return rc;

@@ -63,6 +63,17 @@ cudaError_t launch_debug_mag_sweep(uint32_t lo, uint32_t hi, const uint32_t *d_e
                                    cudaStream_t stream);
 
 void count_launch(void);
+
+// NVTX ranges named after the reference's cycle-profiler labels (prfStart / prfEvent: firmware/src/audioprocessing.c:123-207,
+// firmware/src/app.c:177-207), so that a timeline tool shows the same stage names a firmware trace does.  Header-only NVTX v3:
+// a no-op unless a profiler injects itself.  The ranges cover the host-side enqueue of the corresponding work (the stages inside
+// audioCalcMFCCs -- "fft", "cmpl_mag_q15", "matrix mult", "dct2_q15" -- are one fused kernel here).
+struct TraceRange {
+  explicit TraceRange(const char *label);
+  ~TraceRange();
+  TraceRange(const TraceRange &) = delete;
+  TraceRange &operator=(const TraceRange &) = delete;
+};
 void mfcc_float_release(void);   // frees the lazily built tables of K3 (mfcc_float.cu); caller holds the ctx lock
 void cube_release(void);         // frees the float model of K4 (cube_f32_kernel.cu)
 
