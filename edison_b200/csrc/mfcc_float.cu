@@ -32,7 +32,7 @@ namespace edison {
 constexpr int kXchStride = 34;                 // complex units per radix-16 output row: 32 + 2 keeps the transposing read conflict-free
 constexpr int kXchLen = 16 * kXchStride;       // 544 >= 512
 constexpr int kMagLen = 520;
-constexpr int kMelWMax = 1280;
+constexpr int kMelWMax = 2304;                 // non-zero weights + chunk padding + the bank alignment of fill_tables
 
 template <typename R> struct alignas(2 * sizeof(R)) Cx { R x, y; };   // one 64- / 128-bit shared-memory access
 template <typename R> struct RealTraits;
@@ -493,6 +493,13 @@ static int fill_tables(FloatTables<R> &T, int mode) {
     if (start < 0) start = 0;
     const int a_start = start & ~3;                                  // chunks of 4 bins, 16-byte aligned in mag[]
     const int a_count = ((start + count - a_start) + 3) & ~3;
+    if (sizeof(R) == 4) {
+      // fp32: the two filters that share a quarter-warp in the mel loop (m even, m odd: lanes 8p..8p+3 and 8p+4..8p+7 of one 128-bit
+      // load wavefront) each read 64 contiguous bytes of weights per step; starting them 64 bytes apart modulo 128 makes those reads
+      // conflict-free whatever the filters' lengths (the magnitudes' alignment is fixed by the filterbank and keeps its conflicts)
+      const int want = (m & 1) ? 16 : 0;
+      off += ((want - off) % 32 + 32) % 32;
+    }
     if (off + a_count > kMelWMax || a_start + a_count > kMagLen) return -1;
     T.mel_start[m] = a_start; T.mel_count[m] = a_count; T.mel_off[m] = off;
     if (a_count > T.mel_count_max) T.mel_count_max = a_count;
