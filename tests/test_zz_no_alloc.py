@@ -90,3 +90,27 @@ def test_noalloc_rejects_oversize_and_bad_arguments(edison):
     assert L.edison_kws_batch_noalloc_dev(P(pcm), 0, CLIP, None, None, None) == 0      # nothing to do
     edison.capi.check(L.edison_sync(None))
     assert (out == 99).all()
+
+
+def test_noalloc_call_can_be_captured_into_a_cuda_graph(edison):
+    """what the entry point is for: under stream capture (where cudaMalloc is illegal) the call records its two kernels; replays on new
+    inputs give the existing entry point's bytes"""
+    dev = torch.device("cuda")
+    L = edison.lib()
+    n = 1000
+    pcm = _clips(n, 48, 931, dev)
+    lg = torch.full((n, 10), 99, dtype=torch.int8, device=dev)
+    sm = torch.full((n, 10), 99, dtype=torch.int8, device=dev)
+    edison.capi.check(L.edison_kws_batch_noalloc_dev(P(pcm), 1, CLIP, P(lg), None, None))     # set-up call before the capture
+    edison.capi.check(L.edison_sync(None))
+    graph, side = torch.cuda.CUDAGraph(), torch.cuda.Stream()
+    with torch.cuda.graph(graph, stream=side):
+        edison.capi.check(L.edison_kws_batch_noalloc_dev(P(pcm), n, CLIP, P(lg), P(sm), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    for seed in (931, 932):                       # the first replay on the captured inputs, the second on new contents of the same buffer
+        pcm.copy_(_clips(n, 48, seed, dev))
+        want_lg, want_sm = _existing(edison, pcm, n)
+        lg.fill_(99); sm.fill_(99)
+        torch.cuda.synchronize()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(lg, want_lg) and torch.equal(sm, want_sm), seed
