@@ -286,7 +286,7 @@ class Streams:
         self.n = int(n)
         self._h = ctypes.c_void_p()
         check(lib().edison_streams_open(self.n, ctypes.byref(self._h)), "edison_streams_open")
-        check(lib().edison_streams_set_incremental(self._h, int(bool(incremental))), "edison_streams_set_incremental")
+        check(lib().edison_streams_set_incremental(self._h, int(incremental)), "edison_streams_set_incremental")
 
     def close(self):
         if self._h:

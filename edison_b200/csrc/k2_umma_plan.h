@@ -104,6 +104,42 @@ constexpr int kPosNextRaw = 0;      // first unit of an iteration, same slot as 
 
 static_assert(kSched[kPosTranspose].kind == DN && kUnits - kPosTranspose + kPosNextRaw == kSlots, "transpose slot = first slot of the next iteration");
 
+// ---- incremental sliding-window mode (streaming) ------------------------------------------------------
+// A window that starts one input row later is a new window for the pooled layers (the 2x1 pools are anchored at the window
+// start), but one that starts FOUR rows later is the old one moved up by exactly one pooled conv2 row and one conv3 row:
+//     c2p_h[row 3] = c2p_{h-4}[row 4],  c2p_h[row 2] = c2p_{h-8}[row 4],   c3_h[row 1] = c3_{h-4}[row 2],  c3_h[row 0] = c3_{h-8}[row 2]
+// (h = hop number).  So a hop only has to compute the BOTTOM row of every layer -- conv1 rows 16..23 (units C1(2, x)), pooled conv2
+// row 4 (C2(4)), conv3 row 2 (tiles 3 and 4), then conv4 and the dense layer -- if the rows it computed 4 and 8 hops ago are
+// at hand.  They are kept in HBM per batch of 32 streams in the shared-memory layout, in four phase sets (h mod 4) of three slots
+// used in rotation (use k of a set writes slot k % 3 and reads the rows of uses k - 1 and k - 2: a hop never reads a slot it writes).
+// The kernel is the same: the units that a hop does not need are switched off by a mask (a subset of a hazard-free schedule is
+// hazard free), the epilogues of C2(4) and of the conv3 tiles also store their 16-byte results to the cache, and the team of the
+// dense unit -- which runs once every MMA that read the previous batch's cached rows has completed -- starts the bulk copies of the next
+// rows (12 contiguous pieces, 34 KB) onto an mbarrier that the issuing thread waits on before the first unit that reads them, ten units later.  60 MMAs per batch
+// instead of 153; bit-identical to the full window (integer convolutions are position-local).
+constexpr uint32_t CACHE_C3_ROW = 5 * PX, CACHE_C2_ROW = 7 * PX;                       // one plane of one cached row
+constexpr uint32_t CACHE_C3_SLOT = 4 * CACHE_C3_ROW, CACHE_C2_SLOT = 2 * CACHE_C2_ROW; // all planes of a row
+constexpr uint32_t CACHE_C2_BASE = 4 * 3 * CACHE_C3_SLOT;                              // conv3 part first: [set 4][slot 3][plane 4][5 px]
+constexpr uint32_t CACHE_BATCH_BYTES = CACHE_C2_BASE + 4 * 3 * CACHE_C2_SLOT;          // then conv2: [set 4][slot 3][plane 2][7 px]
+constexpr uint32_t kNoCache = 0xffffffffu;
+constexpr uint32_t CACHE_LOAD_BYTES = 2 * (CACHE_C3_SLOT + CACHE_C2_SLOT);   // the two older rows of both layers: 12 bulk copies per batch
+constexpr int kPosCacheWait = 7;        // first unit that reads cached rows (conv3 tile 3): the issuing thread waits for the bulk copies here
+constexpr uint32_t BAR_CACHE = 136;     // mbarrier of those copies, in the barrier block behind the class histogram
+// units a hop of the incremental mode does not run: C1(0, x), C1(1, x), C2(0..3), conv3 tiles 0..2
+constexpr uint32_t incremental_skip_mask() {
+  uint32_t m = 0;
+  for (int p = 0; p < kUnits; p++) {
+    const Unit u = kSched[p];
+    if ((u.kind == C1 && u.a < 2) || (u.kind == C2 && u.a < 4) || (u.kind == C3 && u.a < 3)) m |= 1u << p;
+  }
+  return m;
+}
+constexpr uint32_t kIncrSkipMask = incremental_skip_mask();
+K2_HD uint32_t cache_c3_off(int set, int slot) { return (uint32_t)(set * 3 + slot) * CACHE_C3_SLOT; }
+K2_HD uint32_t cache_c2_off(int set, int slot) { return CACHE_C2_BASE + (uint32_t)(set * 3 + slot) * CACHE_C2_SLOT; }
+
+static_assert(kSched[kPosCacheWait].kind == C3 && kSched[kPosCacheWait].a == 3 && kPosCacheWait < 13, "cache wait sits at the first reader of cached rows");
+
 struct MmaOp { uint32_t a_off, a_lbo, b_off, b_lbo, n, col, acc; };   // SBO = 128 for every operand; col relative to the slot
 
 // Closed forms instead of tables: the kernel's loops must stay small AND must not stream tables through the constant cache
@@ -233,13 +269,14 @@ K2_HD void softmax_q7(const int8_t *in, int8_t *out, int mode) {
 
 // What an epilogue needs from its executor (CUDA kernel or host emulation):
 //   c.ld16(col, v)   : this thread's lane of TMEM columns col..col+15 of the unit's slot;  c.ld_wait() before using v
-//   c.st16(off, Vec16) : 16-byte shared-memory store;  c.par(i) / c.par4(i): int32 parameter(s) i (same for all lanes)
+//   c.st16(off, Vec16) : 16-byte shared-memory store;  c.st16_cache(off, Vec16): 16-byte store into this batch's row cache (incremental mode:
+//   c.cache_w_c2 / c.cache_w_c3 = offsets of the slots being written, kNoCache otherwise);  c.par(i) / c.par4(i): int32 parameter(s) i (same for all lanes)
 //   c.lane (= clip), c.q (lane quarter = pixel within an M = 128 tile);  dense only: c.clip0 (first clip of the batch),
 //   c.nclips, c.logits, c.softmax (global, may be null), c.softmax_mode, c.count(cls) (class histogram hook),
 //   c.filt (null or the streaming filter state) with c.post(clip, softmax)
 // One warp per lane quarter drains a whole unit: lean loops (a job = 16 accumulator columns -> one 16-byte store is ~75
 // instructions; evaluating a generic job descriptor per job tripled that and the epilogue is latency bound).
-struct JobParams { uint32_t col_e, col_o, seed, out; };
+struct JobParams { uint32_t col_e, col_o, seed, out, gout; };   // gout: byte offset in this batch's row cache, or kNoCache
 
 // n jobs back to back, software pipelined: the tcgen05.ld of job j + 1 is in flight while job j is quantised and stored (the
 // epilogue is bound by latency -- ~250 cycles of TMEM load against ~100 of arithmetic per job -- not by issue slots)
@@ -266,8 +303,9 @@ template <bool POOL, class Ctx, class P> K2_HD void job_stream(Ctx &c, int n, in
     int v[16];
 #pragma unroll
     for (int i = 0; i < 16; i++) v[i] = q7_relu(m[i], seed[i], hi, rs);
-    c.st16(cur.out, Vec16{pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7]), pack4(v[8], v[9], v[10], v[11]),
-                          pack4(v[12], v[13], v[14], v[15])});
+    const Vec16 r{pack4(v[0], v[1], v[2], v[3]), pack4(v[4], v[5], v[6], v[7]), pack4(v[8], v[9], v[10], v[11]), pack4(v[12], v[13], v[14], v[15])};
+    c.st16(cur.out, r);
+    if (cur.gout != kNoCache) c.st16_cache(cur.gout, r);
   }
 }
 
@@ -277,28 +315,34 @@ template <class Ctx> K2_HD void epilogue_conv(Ctx &c, const Unit &u) {
     // lane quarter q is pooled row 4t + q; the unit holds the three pixels of x third u.b: tile E at columns 16 px, tile O at 48 + 16 px
     const uint32_t out = OFF_C1P + (uint32_t)((4 * u.a + c.q) * 9 + 3 * u.b) * PX + lane16;
     job_stream<true>(c, 3, c.par(PAR_RS + 0), c.par(PAR_HI + 0), [&](int j) {
-      return JobParams{(uint32_t)j * 16, 48 + (uint32_t)j * 16, (uint32_t)PAR_SEED1, out + (uint32_t)j * PX};
+      return JobParams{(uint32_t)j * 16, 48 + (uint32_t)j * 16, (uint32_t)PAR_SEED1, out + (uint32_t)j * PX, kNoCache};
     });
   } else if (u.kind == C2) {
     // pooled row u.a; job j: x half h = j >> 1, channel half j & 1; x = 4h + q (x = 7, i.e. q = 3 in the second half, is the
     // wrap-around pixel); x half h at columns 64 h: odd conv row at +0, even conv row at +32
     const uint32_t out = OFF_C2P + (uint32_t)(u.a * 7 + c.q) * PX + lane16;
+    // incremental mode: pooled row 4 also goes to the row cache, [plane][x][clip][16]
+    const uint32_t gbase = (c.cache_w_c2 != kNoCache && u.a == 4) ? c.cache_w_c2 + (uint32_t)c.q * PX + lane16 : kNoCache;
     job_stream<true>(c, c.q < 3 ? 4 : 2, c.par(PAR_RS + 1), c.par(PAR_HI + 1), [&](int j) {
       const uint32_t h = (uint32_t)j >> 1, half = (uint32_t)j & 1;
-      return JobParams{h * 64 + 32 + half * 16, h * 64 + half * 16, (uint32_t)PAR_SEED2 + half * 16, out + half * PLANE2 + h * 4 * PX};
+      return JobParams{h * 64 + 32 + half * 16, h * 64 + half * 16, (uint32_t)PAR_SEED2 + half * 16, out + half * PLANE2 + h * 4 * PX,
+                       gbase == kNoCache ? kNoCache : gbase + half * CACHE_C2_ROW + h * 4 * PX};
     });
   } else if (u.kind == C3) {
     // one tile: position idx = 4 u.a + q on the 7-wide grid (x >= 5 and row 3 are wrap-around positions); four 16-channel planes
     const int idx = 4 * u.a + c.q, y = idx / 7, x = idx - 7 * y;
     const uint32_t out = OFF_C3 + (uint32_t)(y * 5 + x) * PX + lane16;
+    // incremental mode: row 2 also goes to the row cache, [plane][x][clip][16]
+    const uint32_t gbase = (c.cache_w_c3 != kNoCache && y == 2) ? c.cache_w_c3 + (uint32_t)x * PX + lane16 : kNoCache;
     job_stream<false>(c, (x < 5 && y < 3) ? 4 : 0, c.par(PAR_RS + 2), c.par(PAR_HI + 2), [&](int j) {
-      return JobParams{(uint32_t)j * 16, 0, (uint32_t)PAR_SEED3 + (uint32_t)j * 16, out + (uint32_t)j * PLANE3};
+      return JobParams{(uint32_t)j * 16, 0, (uint32_t)PAR_SEED3 + (uint32_t)j * 16, out + (uint32_t)j * PLANE3,
+                       gbase == kNoCache ? kNoCache : gbase + (uint32_t)j * CACHE_C3_ROW};
     });
   } else if (u.kind == C4) {
     // x = q (3 is the wrap-around pixel); two 16-channel planes
     const uint32_t out = OFF_C4 + (uint32_t)c.q * PX + lane16;
     job_stream<false>(c, c.q < 3 ? 2 : 0, c.par(PAR_RS + 3), c.par(PAR_HI + 3), [&](int j) {
-      return JobParams{(uint32_t)j * 16, 0, (uint32_t)PAR_SEED4 + (uint32_t)j * 16, out + (uint32_t)j * PLANE4};
+      return JobParams{(uint32_t)j * 16, 0, (uint32_t)PAR_SEED4 + (uint32_t)j * 16, out + (uint32_t)j * PLANE4, kNoCache};
     });
   }
 }

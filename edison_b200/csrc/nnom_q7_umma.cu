@@ -80,6 +80,8 @@ struct DevCtx {
   int *hist;        // shared-memory class histogram
   float *filt;      // streaming post-processing (null: none)
   int32_t *detect;
+  uint8_t *cache_batch;               // incremental mode: this unit's batch in the row cache
+  uint32_t cache_w_c2, cache_w_c3;    //   offsets of the slots this hop writes (kNoCache: no caching)
   long long t_ld;   // TRACE builds: clock64() when the last tcgen05.ld had landed
   bool tracing;
   __device__ __forceinline__ void ld16(uint32_t col, uint32_t (&v)[16]) {
@@ -93,6 +95,7 @@ struct DevCtx {
     if (tracing) t_ld = clock64();
   }
   __device__ __forceinline__ void st16(uint32_t off, Vec16 v) { *reinterpret_cast<uint4 *>(smem + off) = make_uint4(v.x, v.y, v.z, v.w); }
+  __device__ __forceinline__ void st16_cache(uint32_t off, Vec16 v) { *reinterpret_cast<uint4 *>(cache_batch + off) = make_uint4(v.x, v.y, v.z, v.w); }
   __device__ __forceinline__ int par(int i) const { return reinterpret_cast<const int *>(smem + OFF_PAR)[i]; }
   __device__ __forceinline__ Int4 par4(int i) const {
     const int4 v = *reinterpret_cast<const int4 *>(smem + OFF_PAR + 4 * i);
@@ -123,6 +126,8 @@ struct Job {
   int row0;             // ring offset of the input rows (0 for plain batches)
   int nbc;              // batches of this CTA: blockIdx.x + k * gridDim.x, k < nbc
   bool aligned;         // net_in is 16-byte aligned: full batches come in by bulk copy
+  uint32_t skip;        // schedule positions that are switched off (incremental mode)
+  bool cached;          // incremental mode: cached rows arrive by bulk copy
   __device__ __forceinline__ long long batch(int k) const { return (long long)blockIdx.x + (long long)k * gridDim.x; }
   __device__ __forceinline__ bool bulk(int k) const { return aligned && (batch(k) + 1) * NC <= n; }
 };
@@ -159,6 +164,24 @@ __device__ __forceinline__ void transpose_in(uint8_t *smem, const Job &J, int k,
   }
 }
 
+// incremental mode: rows 0, 1 of conv3 (4 planes x 5 px) and rows 2, 3 of pooled conv2 (2 planes x 7 px) of one batch, from the row cache
+// into their places in the activation buffers: 12 bulk copies onto one mbarrier (issued by one thread)
+__device__ __forceinline__ void start_cached_rows(uint32_t sbase, const uint8_t *cb, int set, int older, int newer, uint32_t bar) {
+  mbar_expect_tx(bar, CACHE_LOAD_BYTES);
+#pragma unroll
+  for (int row = 0; row < 2; row++) {   // row 0 = the older one
+    const int slot = row ? newer : older;
+#pragma unroll
+    for (int plane = 0; plane < 4; plane++)
+      bulk_g2s(sbase + OFF_C3 + (uint32_t)plane * PLANE3 + (uint32_t)(row * 5) * PX, cb + cache_c3_off(set, slot) + (uint32_t)plane * CACHE_C3_ROW,
+               CACHE_C3_ROW, bar);
+#pragma unroll
+    for (int plane = 0; plane < 2; plane++)
+      bulk_g2s(sbase + OFF_C2P + (uint32_t)plane * PLANE2 + (uint32_t)((2 + row) * 7) * PX, cb + cache_c2_off(set, slot) + (uint32_t)plane * CACHE_C2_ROW,
+               CACHE_C2_ROW, bar);
+  }
+}
+
 __constant__ Unit c_sched[kUnits];   // k2::kSched for the epilogue loop, uploaded once by nnom_umma_configure (304 bytes: stays cached)
 
 __device__ __forceinline__ uint64_t desc_from_lo(uint32_t lo) { return (uint64_t)lo | ((uint64_t)(8u | (1u << 14)) << 32); }
@@ -192,7 +215,8 @@ template <int POS, bool TRACE> struct IssueUnits {
       mbar_expect_tx(bar_raw, NC * kNetIn);
       bulk_g2s(sbase + OFF_RAW, J.net_in + J.batch(it + 1) * NC * kNetIn, NC * kNetIn, bar_raw);
     }
-    if (U.lag ? it > 0 : it < J.nbc) IssueMmas<POS, 0>::go(tmem + slot * kSlotCols, sb4);
+    if (POS == kPosCacheWait && J.cached && it > 0) mbar_wait(bars + BAR_CACHE, (uint32_t)(it - 1) & 1u);   // the cached rows of this tail batch have landed
+    if (!((J.skip >> POS) & 1u) && (U.lag ? it > 0 : it < J.nbc)) IssueMmas<POS, 0>::go(tmem + slot * kSlotCols, sb4);
     umma_commit(bars + 8 * slot);
     gpos++;
     if constexpr (POS + 1 < kUnits) IssueUnits<POS + 1, TRACE>::go(J, bars, bar_raw, sbase, sb4, tmem, it, gpos, lane, trace);
@@ -221,6 +245,8 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
   J.image = image; J.net_in = net_in; J.n = n; J.nb = (n + NC - 1) / NC; J.row0 = K.row0;
   J.nbc = (long long)blockIdx.x < J.nb ? (int)((J.nb - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
   J.aligned = (reinterpret_cast<uintptr_t>(net_in) & 15) == 0;
+  J.skip = K.skip_mask;
+  J.cached = K.cache != nullptr;
 
   if (warp == kEpiWarps) {
     if (lane == 0) {
@@ -228,7 +254,7 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
         mbar_init(bars + 8 * s, 1);
         mbar_init(bars + 32 + 8 * s, 128);                      // one team of four warps per slot
       }
-      mbar_init(bar_raw, 1); mbar_init(bar_wts, 1);
+      mbar_init(bar_raw, 1); mbar_init(bar_wts, 1); mbar_init(bars + BAR_CACHE, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       mbar_expect_tx(bar_wts, IMAGE_BYTES);
       bulk_g2s(sbase, image, IMAGE_BYTES, bar_wts);
@@ -268,6 +294,9 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
       c.smem = smem; c.lane = lane; c.q = warp & 3; c.g = 0;
       c.clip0 = 0; c.nclips = 0; c.logits = logits; c.softmax = softmax; c.softmax_mode = softmax_mode; c.hist = hist;
       c.t_ld = 0; c.tracing = false; c.filt = K.filt; c.detect = K.detect;
+      c.cache_batch = nullptr;
+      c.cache_w_c2 = K.cache ? cache_c2_off(K.cache_set, K.cache_write) : kNoCache;
+      c.cache_w_c3 = K.cache ? cache_c3_off(K.cache_set, K.cache_write) : kNoCache;
       const uint32_t team = warp >> 2, ttid = tid & 127;
       const uint32_t tmem_q = tmem + ((uint32_t)(c.q * 32) << 16) + team * kSlotCols;
       const uint32_t bar_full = bars + 8 * team, bar_empty = bars + 32 + 8 * team;
@@ -282,7 +311,8 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
         const bool stamp = TRACE && trace && it == 1 && ttid == 0;
         if (stamp) trace[4 * pos + 2] = clock64();
         if (TRACE) c.tracing = stamp && pos == kPosTranspose;  // fine stamps of one unit: [4 kUnits] last ld landed, [+1] stored, [+2] fenced
-        if (U.lag ? it > 0 : it < J.nbc) {
+        if (!((J.skip >> pos) & 1u) && (U.lag ? it > 0 : it < J.nbc)) {
+          if (K.cache) c.cache_batch = K.cache + (size_t)J.batch(it - U.lag) * CACHE_BATCH_BYTES;
           if (U.kind == DN) {
             if (c.q == 0) {
               c.clip0 = J.batch(it - 1) * NC;
@@ -295,6 +325,8 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
         }
         if (stamp && c.tracing) { trace[4 * kUnits] = c.t_ld; trace[4 * kUnits + 1] = clock64(); }
         if (pos == kPosTranspose && it + 1 < J.nbc && c.q > 0) transpose_in(smem, J, it + 1, bar_raw, (int)ttid - 32, 96);   // warp 0 of the team runs the dense epilogue
+        if (pos == kPosTranspose && K.cache && it < J.nbc && ttid == 32)   // incremental mode: the cached rows of the batch whose tail runs next iteration
+          start_cached_rows(sbase, K.cache + (size_t)J.batch(it) * CACHE_BATCH_BYTES, K.cache_set, K.cache_older, K.cache_newer, bars + BAR_CACHE);
         fence_async_smem();   // this thread's shared-memory stores -> visible to the MMAs that will read them
         tc_fence_before();
         if (stamp && c.tracing) trace[4 * kUnits + 2] = clock64();
@@ -337,6 +369,9 @@ int nnom_umma_upload(const int8_t *const w[5], const int8_t *const b[5], const i
   *out_image = d;
   return EDISON_OK;
 }
+
+size_t nnom_umma_cache_bytes(long long n) { return (size_t)((n + NC - 1) / NC) * CACHE_BATCH_BYTES; }
+uint32_t nnom_umma_incr_skip_mask(void) { return kIncrSkipMask; }
 
 cudaError_t launch_nnom_q7_umma(const uint8_t *image, const K2Launch &k, int sm_count, cudaStream_t stream) {
   if (k.n <= 0) return cudaSuccess;

@@ -35,6 +35,8 @@ struct edison_streams {
   int8_t *d_incr;      // ring state of the incremental net (nnom_q7_kernel.cu), 7,392 B per stream
   edison::NnomIncrState incr;
   int incremental;     // 0 (default): the whole window through K2 every hop, as the firmware does; 1: one new row per layer and hop
+                       // (mma.sync kernel with HBM rings); 2: the tcgen05 K2 on the bottom rows only, older rows from its row cache
+  uint8_t *d_cache;    // mode 2: row cache of nnom_q7_umma.cu (k2_umma_plan.h), 6.5 KB per stream
   // host ingest pipeline
   int16_t *d_pcm[2];         // [n][1024] staging
   unsigned char *h_out[2];   // pinned: softmax [n][10] | filt [n][10] float | detect [n] int32
@@ -90,7 +92,16 @@ static int push_dev(edison_streams *s, const CtxView &c, const int16_t *d_pcm, i
   s->hops++;
   // the firmware fills the window (31 frames), waits for one more frame, then starts inferring (app.c:311-318)
   const bool infer = s->hops > EDISON_N_FRAMES;
-  if (s->incremental) {   // runs from the first hop on: it is what fills the rings
+  if (s->incremental == 2) {   // runs from the first hop on: it is what fills the row cache
+    const unsigned long long h = s->hops;
+    const int use = (int)((h >> 2) % 3);
+    K2Launch k{};
+    k.net_in = s->d_window; k.n = (long long)n; k.softmax_mode = c.softmax_mode; k.row0 = s->row0;
+    k.cache = s->d_cache; k.cache_set = (int)(h & 3); k.cache_write = use; k.cache_newer = (use + 2) % 3; k.cache_older = (use + 1) % 3;
+    k.skip_mask = nnom_umma_incr_skip_mask();
+    if (infer) { k.softmax = s->d_softmax; k.filt = s->d_filt; k.detect = s->d_detect; }
+    CUS(launch_nnom_q7(c.model, k, c.sm_count, st));
+  } else if (s->incremental) {   // runs from the first hop on: it is what fills the rings
     CUS(launch_nnom_q7_incremental(c.model, s->d_window, s->row0, s->incr, (long long)n, (long long)s->hops - 1, nullptr,
                                    infer ? s->d_softmax : nullptr, c.softmax_mode, c.sm_count, st));
     if (infer) {
@@ -161,7 +172,7 @@ void edison_streams_close(edison_streams *s) {
   DeviceScope device_scope_;
   if (!s) return;
   cudaDeviceSynchronize();
-  void *bufs[] = {s->d_window, s->d_softmax, s->d_filt, s->d_detect, s->d_pcm[0], s->d_pcm[1], s->d_incr};
+  void *bufs[] = {s->d_window, s->d_softmax, s->d_filt, s->d_detect, s->d_pcm[0], s->d_pcm[1], s->d_incr, s->d_cache};
   for (void *b : bufs)
     if (b) cudaFree(b);
   for (int i = 0; i < 2; i++) {
@@ -181,7 +192,14 @@ int edison_streams_set_incremental(edison_streams *s, int on) {
   DeviceScope device_scope_;
   if (!s) return ctx_fail(EDISON_E_ARG, "edison_streams_set_incremental: null handle");
   if (s->hops) return ctx_fail(EDISON_E_ARG, "edison_streams_set_incremental: only before the first hop (the rings fill from hop 1)");
-  if (on && !s->d_incr) {
+  if (on == 2 && !s->d_cache) {
+    const size_t bytes = nnom_umma_cache_bytes((long long)s->n);
+    cudaError_t e = cudaMalloc(&s->d_cache, bytes);
+    if (e == cudaSuccess) e = cudaMemset(s->d_cache, 0, bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return ctx_fail(EDISON_E_NOMEM, "edison_streams_set_incremental: %s", cudaGetErrorString(e));
+  }
+  if (on == 1 && !s->d_incr) {
     const size_t bytes = nnom_incr_state_bytes((long long)s->n);
     cudaError_t e = cudaMalloc(&s->d_incr, bytes);
     if (e == cudaSuccess) e = cudaMemset(s->d_incr, 0, bytes);
@@ -189,7 +207,7 @@ int edison_streams_set_incremental(edison_streams *s, int on) {
     if (e != cudaSuccess) return ctx_fail(EDISON_E_NOMEM, "edison_streams_set_incremental: %s", cudaGetErrorString(e));
     nnom_incr_state_bind(&s->incr, s->d_incr, (long long)s->n);
   }
-  s->incremental = on ? 1 : 0;
+  s->incremental = on == 2 ? 2 : (on ? 1 : 0);
   return EDISON_OK;
 }
 
