@@ -273,7 +273,7 @@ K2_HD void softmax_q7(const int8_t *in, int8_t *out, int mode) {
 //   c.cache_w_c2 / c.cache_w_c3 = offsets of the slots being written, kNoCache otherwise);  c.par(i) / c.par4(i): int32 parameter(s) i (same for all lanes)
 //   c.lane (= clip), c.q (lane quarter = pixel within an M = 128 tile);  dense only: c.clip0 (first clip of the batch),
 //   c.nclips, c.logits, c.softmax (global, may be null), c.softmax_mode, c.count(cls) (class histogram hook),
-//   c.filt (null or the streaming filter state) with c.post(clip, softmax)
+//   c.filt (null or the streaming filter state) with c.prefetch(clip) (start loading the state) and c.post(clip, softmax)
 // One warp per lane quarter drains a whole unit: lean loops (a job = 16 accumulator columns -> one 16-byte store is ~75
 // instructions; evaluating a generic job descriptor per job tripled that and the epilogue is latency bound).
 struct JobParams { uint32_t col_e, col_o, seed, out, gout; };   // gout: byte offset in this batch's row cache, or kNoCache
@@ -352,6 +352,7 @@ template <class Ctx> K2_HD void run_dense(Ctx &c) {
   const int rs = c.par(PAR_RS + 4);
   uint32_t e[16];
   c.ld16(0, e);
+  if (c.filt && c.lane < c.nclips) c.prefetch(c.clip0 + c.lane);   // streaming: the filter state travels while the accumulators do
   c.ld_wait();
   if (c.lane < c.nclips) {
     int8_t lg[10];

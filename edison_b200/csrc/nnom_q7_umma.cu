@@ -103,7 +103,14 @@ struct DevCtx {
   }
   __device__ __forceinline__ void count(int cls) { atomicAdd(&hist[cls], 1); }
   // app.c:336-350: netOutFilt = 0.9 netOutFilt + (1.0 - 0.9) netOutFloat, evaluated in double (the literals are doubles, the
-  // firmware has no -fsingle-precision-constant) and stored as float; arm_max_f32 (first maximum); spotted when > 0.5
+  // firmware has no -fsingle-precision-constant) and stored as float; arm_max_f32 (first maximum); spotted when > 0.5.
+  // The ten state loads are issued by prefetch() before the dense unit's accumulators are read: inside the loop each sat behind the
+  // previous value's store, ten global-memory latencies in a row, and in the incremental mode the dense unit's team is the critical path.
+  float pf[10];
+  __device__ __forceinline__ void prefetch(long long clip) {
+#pragma unroll
+    for (int i = 0; i < 10; i++) pf[i] = filt[clip * 10 + i];
+  }
   __device__ __forceinline__ void post(long long clip, const int8_t *sm) {
     const double alpha = 0.9, beta = 1.0 - 0.9;
     float best = 0.f;
@@ -111,7 +118,7 @@ struct DevCtx {
 #pragma unroll
     for (int i = 0; i < 10; i++) {
       const double o = (double)(float)sm[i];
-      const float f = (float)__dadd_rn(__dmul_rn(alpha, (double)filt[clip * 10 + i]), __dmul_rn(beta, o));
+      const float f = (float)__dadd_rn(__dmul_rn(alpha, (double)pf[i]), __dmul_rn(beta, o));
       filt[clip * 10 + i] = f;
       if (i == 0 || f > best) { best = f; idx = i; }
     }
@@ -128,6 +135,7 @@ struct Job {
   bool aligned;         // net_in is 16-byte aligned: full batches come in by bulk copy
   uint32_t skip;        // schedule positions that are switched off (incremental mode)
   bool cached;          // incremental mode: cached rows arrive by bulk copy
+  int row_begin;        // first input row the active conv1 units read (16 in the incremental mode: only C1(2, x) runs)
   __device__ __forceinline__ long long batch(int k) const { return (long long)blockIdx.x + (long long)k * gridDim.x; }
   __device__ __forceinline__ bool bulk(int k) const { return aligned && (batch(k) + 1) * NC <= n; }
 };
@@ -140,7 +148,7 @@ __device__ __forceinline__ void transpose_in(uint8_t *smem, const Job &J, int k,
   if (bulk) mbar_wait(raw_bar, (uint32_t)k & 1u);
   const int clip = tid & 31;
 #pragma unroll 1
-  for (int row = tid >> 5; row < kInRowsUsed; row += nthreads >> 5) {
+  for (int row = J.row_begin + (tid >> 5); row < kInRowsUsed; row += nthreads >> 5) {
     {
       const uint32_t a = raw_offset(clip, row, J.row0);
       uint32_t w[4];
@@ -247,6 +255,7 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
   J.aligned = (reinterpret_cast<uintptr_t>(net_in) & 15) == 0;
   J.skip = K.skip_mask;
   J.cached = K.cache != nullptr;
+  J.row_begin = ((K.skip_mask & kIncrSkipMask) == kIncrSkipMask) ? 16 : 0;
 
   if (warp == kEpiWarps) {
     if (lane == 0) {

@@ -37,6 +37,7 @@ struct edison_streams {
   int incremental;     // 0 (default): the whole window through K2 every hop, as the firmware does; 1: one new row per layer and hop
                        // (mma.sync kernel with HBM rings); 2: the tcgen05 K2 on the bottom rows only, older rows from its row cache
   uint8_t *d_cache;    // mode 2: row cache of nnom_q7_umma.cu (k2_umma_plan.h), 6.5 KB per stream
+  long long *d_trace;  // debug: K2's per-unit clock stamps of the next hops (edison_streams_debug_trace)
   // host ingest pipeline
   int16_t *d_pcm[2];         // [n][1024] staging
   unsigned char *h_out[2];   // pinned: softmax [n][10] | filt [n][10] float | detect [n] int32
@@ -100,6 +101,7 @@ static int push_dev(edison_streams *s, const CtxView &c, const int16_t *d_pcm, i
     k.cache = s->d_cache; k.cache_set = (int)(h & 3); k.cache_write = use; k.cache_newer = (use + 2) % 3; k.cache_older = (use + 1) % 3;
     k.skip_mask = nnom_umma_incr_skip_mask();
     if (infer) { k.softmax = s->d_softmax; k.filt = s->d_filt; k.detect = s->d_detect; }
+    k.trace = s->d_trace;
     CUS(launch_nnom_q7(c.model, k, c.sm_count, st));
   } else if (s->incremental) {   // runs from the first hop on: it is what fills the rings
     CUS(launch_nnom_q7_incremental(c.model, s->d_window, s->row0, s->incr, (long long)n, (long long)s->hops - 1, nullptr,
@@ -111,7 +113,7 @@ static int push_dev(edison_streams *s, const CtxView &c, const int16_t *d_pcm, i
   } else if (infer) {
     K2Launch k{};
     k.net_in = s->d_window; k.n = (long long)n; k.softmax = s->d_softmax; k.softmax_mode = c.softmax_mode; k.row0 = s->row0;
-    k.filt = s->d_filt; k.detect = s->d_detect;
+    k.filt = s->d_filt; k.detect = s->d_detect; k.trace = s->d_trace;
     CUS(launch_nnom_q7(c.model, k, c.sm_count, st));
   }
   if (!infer) {
@@ -187,6 +189,13 @@ void edison_streams_close(edison_streams *s) {
 }
 
 unsigned long long edison_streams_hops(const edison_streams *s) { return s ? s->hops : 0; }
+
+// debug: K2 of the following hops runs its tracing instantiation and writes block 0's per-unit clock stamps to d_trace (128 int64, device); null: off
+int edison_streams_debug_trace(edison_streams *s, long long *d_trace) {
+  if (!s) return ctx_fail(EDISON_E_ARG, "edison_streams_debug_trace: null handle");
+  s->d_trace = d_trace;
+  return EDISON_OK;
+}
 
 int edison_streams_set_incremental(edison_streams *s, int on) {
   DeviceScope device_scope_;

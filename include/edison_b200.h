@@ -256,6 +256,8 @@ int edison_debug_mag_sweep(uint32_t lo, uint32_t hi, unsigned long long *mismatc
                            unsigned long long *checksum);
 /* K2 with clock64() stamps per schedule unit of block 0's second batch (d_trace: 96 int64 on the device; tools/k2_trace.py) */
 int edison_debug_k2_trace_dev(const int8_t *d_net_in, size_t n, int8_t *d_logits, int8_t *d_softmax, long long *d_trace, void *stream);
+/* the same stamps from K2 inside the streaming hops that follow (any mode); NULL switches it off */
+int edison_streams_debug_trace(edison_streams *s, long long *d_trace);
 
 #ifdef __cplusplus
 }

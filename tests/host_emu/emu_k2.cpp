@@ -58,6 +58,7 @@ struct Ctx {
   float *filt = nullptr;
   uint32_t cache_w_c2 = kNoCache, cache_w_c3 = kNoCache;
   void st16_cache(uint32_t, Vec16) {}
+  void prefetch(long long) {}
   void post(long long, const int8_t *) {}
   void ld16(uint32_t col, uint32_t (&v)[16]) {
     for (int j = 0; j < 16; j++) v[j] = (uint32_t)e->tmem[(q * 32 + lane) * 512 + slot * kSlotCols + col + j];
