@@ -44,13 +44,11 @@ struct K2Launch {
   int32_t *detect;          //   filt[n][10] moving average (in / out), detect[n] = spotted class or -1
   long long *trace;         // debug: clock64() stamps of block 0 (edison_debug_k2_trace_dev)
   // incremental sliding-window mode (k2_umma_plan.h): the row cache [batches][CACHE_BATCH_BYTES], the phase set of this hop and the
-  // slots holding the rows of the set's two previous uses / taking this use's rows; units in skip_mask are not run
+  // slots holding the rows of the set's two previous uses / taking this use's rows; non-null selects the incremental kernel
   uint8_t *cache;
   int cache_set, cache_older, cache_newer, cache_write;
-  uint32_t skip_mask;
 };
 size_t nnom_umma_cache_bytes(long long n);   // bytes of the row cache for n streams
-uint32_t nnom_umma_incr_skip_mask(void);     // schedule positions the incremental mode switches off
 cudaError_t launch_nnom_q7(const NnomModel *model, const K2Launch &k, int sm_count, cudaStream_t stream);
 cudaError_t nnom_umma_configure(void);
 int nnom_umma_upload(const int8_t *const w[5], const int8_t *const b[5], const int rs[5], const int ls[5], uint8_t **out_image);

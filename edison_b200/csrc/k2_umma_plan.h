@@ -69,7 +69,7 @@ constexpr uint32_t PLANE4 = 3 * PX;                      //   next plane / conv3
 constexpr uint32_t OFF_C3 = OFF_C4 + 2 * PLANE4;         // conv3: 4 planes x (3 x 5 px + 1)
 constexpr uint32_t PLANE3 = 16 * PX;
 constexpr uint32_t OFF_BAR = OFF_C3 + 4 * PLANE3;        // mbarriers full[4] empty[4] raw wts (80 B), TMEM base (+80), class histogram (+96, 40 B)
-constexpr uint32_t SMEM_BYTES = OFF_BAR + 144;
+constexpr uint32_t SMEM_BYTES = OFF_BAR + 160;
 static_assert(IMAGE_BYTES % 16 == 0 && RAW_BYTES % 16 == 0 && OFF_BAR % 16 == 0, "16-byte granularity");
 static_assert(SMEM_BYTES <= 232448, "more than the 227 KB a CTA can have");
 
@@ -112,34 +112,33 @@ static_assert(kSched[kPosTranspose].kind == DN && kUnits - kPosTranspose + kPosN
 // row 4 (C2(4)), conv3 row 2 (tiles 3 and 4), then conv4 and the dense layer -- if the rows it computed 4 and 8 hops ago are
 // at hand.  They are kept in HBM per batch of 32 streams in the shared-memory layout, in four phase sets (h mod 4) of three slots
 // used in rotation (use k of a set writes slot k % 3 and reads the rows of uses k - 1 and k - 2: a hop never reads a slot it writes).
-// The kernel is the same: the units that a hop does not need are switched off by a mask (a subset of a hazard-free schedule is
-// hazard free), the epilogues of C2(4) and of the conv3 tiles also store their 16-byte results to the cache, and the team of the
-// dense unit -- which runs once every MMA that read the previous batch's cached rows has completed -- starts the bulk copies of the next
-// rows (12 contiguous pieces, 34 KB) onto an mbarrier that the issuing thread waits on before the first unit that reads them, ten units later.  60 MMAs per batch
-// instead of 153; bit-identical to the full window (integer convolutions are position-local).
+// The machinery is the same (nnom_q7_umma_incr_kernel, schedule kSchedI below): the epilogues of C2(4) and of the conv3 tiles also store their
+// 16-byte results to the cache, and the team of the unit that follows the last reader of a layer's cached rows starts the bulk copies of the next
+// batch's rows (contiguous pieces, 34 KB per batch) onto an mbarrier that the issuing thread waits on before the first unit that reads them.
+// 60 MMAs per batch instead of 153; bit-identical to the full window (integer convolutions are position-local).
 constexpr uint32_t CACHE_C3_ROW = 5 * PX, CACHE_C2_ROW = 7 * PX;                       // one plane of one cached row
 constexpr uint32_t CACHE_C3_SLOT = 4 * CACHE_C3_ROW, CACHE_C2_SLOT = 2 * CACHE_C2_ROW; // all planes of a row
 constexpr uint32_t CACHE_C2_BASE = 4 * 3 * CACHE_C3_SLOT;                              // conv3 part first: [set 4][slot 3][plane 4][5 px]
 constexpr uint32_t CACHE_BATCH_BYTES = CACHE_C2_BASE + 4 * 3 * CACHE_C2_SLOT;          // then conv2: [set 4][slot 3][plane 2][7 px]
 constexpr uint32_t kNoCache = 0xffffffffu;
-constexpr uint32_t CACHE_LOAD_BYTES = 2 * (CACHE_C3_SLOT + CACHE_C2_SLOT);   // the two older rows of both layers: 12 bulk copies per batch
-constexpr int kPosCacheWait = 7;        // first unit that reads cached rows (conv3 tile 3): the issuing thread waits for the bulk copies here
-constexpr uint32_t BAR_CACHE = 136;     // mbarrier of those copies, in the barrier block behind the class histogram
-// units a hop of the incremental mode does not run: C1(0, x), C1(1, x), C2(0..3), conv3 tiles 0..2
-constexpr uint32_t incremental_skip_mask() {
-  uint32_t m = 0;
-  for (int p = 0; p < kUnits; p++) {
-    const Unit u = kSched[p];
-    if ((u.kind == C1 && u.a < 2) || (u.kind == C2 && u.a < 4) || (u.kind == C3 && u.a < 3)) m |= 1u << p;
-  }
-  return m;
-}
-constexpr uint32_t kIncrSkipMask = incremental_skip_mask();
+constexpr uint32_t BAR_CACHE = 136;     // mbarrier of conv3's cached-row copies, in the barrier block behind the class histogram
 K2_HD uint32_t cache_c3_off(int set, int slot) { return (uint32_t)(set * 3 + slot) * CACHE_C3_SLOT; }
 K2_HD uint32_t cache_c2_off(int set, int slot) { return CACHE_C2_BASE + (uint32_t)(set * 3 + slot) * CACHE_C2_SLOT; }
 
-static_assert(kSched[kPosCacheWait].kind == C3 && kSched[kPosCacheWait].a == 3 && kPosCacheWait < 13, "cache wait sits at the first reader of cached rows");
-
+// The incremental mode's own schedule (nnom_q7_umma_incr_kernel): the eight units a hop needs, one pipeline stage per iteration -- in
+// iteration i, conv1 works on batch i, conv2 on batch i - 1, conv3 on i - 2, conv4 on i - 3, dense on i - 4 -- and within an iteration
+// the deepest stage first.  Every consumer then sits 5..7 units after its producer (previous iteration), and every writer of a
+// buffer is issued after the readers of the buffer's previous content (same iteration, earlier position), which is all the slot
+// ring needs (see the argument above).  8 units on 4 slots: a position always uses slot pos & 3, in phase pos >> 2.
+constexpr int kUnitsI = 8, kMaxLagI = 4;
+constexpr Unit kSchedI[kUnitsI] = {{DN, 0, 0, 4}, {C4, 0, 0, 3}, {C3, 3, 1, 2}, {C3, 4, 1, 2}, {C2, 4, 0, 1}, {C1, 2, 0, 0}, {C1, 2, 1, 0}, {C1, 2, 2, 0}};
+constexpr int kPosI_Dense = 0;    // its team lays out batch i's input rows (conv1 of batch i - 1 is done with c0; conv1 of batch i is 5 units away)
+constexpr int kPosI_Conv4 = 1;    // the issuing thread waits for conv3's cached rows 0, 1 of its batch here
+constexpr int kPosI_Conv3 = 2;    // ... and for conv2's cached rows 2, 3 here; this unit's team starts the copy of conv3's rows for ITS batch
+constexpr int kPosI_Conv2 = 4;    // this unit's team starts the copy of conv2's rows for its batch; the issuing thread starts the next raw copy here
+constexpr uint32_t CACHE_C3_LOAD = 2 * CACHE_C3_SLOT, CACHE_C2_LOAD = 2 * CACHE_C2_SLOT;
+constexpr uint32_t BAR_CACHE2 = 144;    // second cache mbarrier (conv2 rows); BAR_CACHE takes conv3's
+constexpr int kIncrFirstRow = 16;       // conv1 rows 16..23 read input rows 16..27
 struct MmaOp { uint32_t a_off, a_lbo, b_off, b_lbo, n, col, acc; };   // SBO = 128 for every operand; col relative to the slot
 
 // Closed forms instead of tables: the kernel's loops must stay small AND must not stream tables through the constant cache

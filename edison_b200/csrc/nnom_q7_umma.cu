@@ -133,9 +133,7 @@ struct Job {
   int row0;             // ring offset of the input rows (0 for plain batches)
   int nbc;              // batches of this CTA: blockIdx.x + k * gridDim.x, k < nbc
   bool aligned;         // net_in is 16-byte aligned: full batches come in by bulk copy
-  uint32_t skip;        // schedule positions that are switched off (incremental mode)
-  bool cached;          // incremental mode: cached rows arrive by bulk copy
-  int row_begin;        // first input row the active conv1 units read (16 in the incremental mode: only C1(2, x) runs)
+  int row_begin;        // first input row the conv1 units of this kernel read (kIncrFirstRow in the incremental kernel: only C1(2, x) runs)
   __device__ __forceinline__ long long batch(int k) const { return (long long)blockIdx.x + (long long)k * gridDim.x; }
   __device__ __forceinline__ bool bulk(int k) const { return aligned && (batch(k) + 1) * NC <= n; }
 };
@@ -172,25 +170,29 @@ __device__ __forceinline__ void transpose_in(uint8_t *smem, const Job &J, int k,
   }
 }
 
-// incremental mode: rows 0, 1 of conv3 (4 planes x 5 px) and rows 2, 3 of pooled conv2 (2 planes x 7 px) of one batch, from the row cache
-// into their places in the activation buffers: 12 bulk copies onto one mbarrier (issued by one thread)
-__device__ __forceinline__ void start_cached_rows(uint32_t sbase, const uint8_t *cb, int set, int older, int newer, uint32_t bar) {
-  mbar_expect_tx(bar, CACHE_LOAD_BYTES);
+// incremental kernel: the two older rows of a layer for one batch, from the row cache into their places in the activation buffers, as
+// bulk copies onto one mbarrier (issued by one thread).  conv3: rows 0, 1 (4 planes x 5 px); pooled conv2: rows 2, 3 (2 planes x 7 px)
+__device__ __forceinline__ void start_cached_c3(uint32_t sbase, const uint8_t *cb, int set, int older, int newer, uint32_t bar) {
+  mbar_expect_tx(bar, CACHE_C3_LOAD);
 #pragma unroll
-  for (int row = 0; row < 2; row++) {   // row 0 = the older one
-    const int slot = row ? newer : older;
+  for (int row = 0; row < 2; row++)
 #pragma unroll
     for (int plane = 0; plane < 4; plane++)
-      bulk_g2s(sbase + OFF_C3 + (uint32_t)plane * PLANE3 + (uint32_t)(row * 5) * PX, cb + cache_c3_off(set, slot) + (uint32_t)plane * CACHE_C3_ROW,
-               CACHE_C3_ROW, bar);
+      bulk_g2s(sbase + OFF_C3 + (uint32_t)plane * PLANE3 + (uint32_t)(row * 5) * PX,
+               cb + cache_c3_off(set, row ? newer : older) + (uint32_t)plane * CACHE_C3_ROW, CACHE_C3_ROW, bar);
+}
+__device__ __forceinline__ void start_cached_c2(uint32_t sbase, const uint8_t *cb, int set, int older, int newer, uint32_t bar) {
+  mbar_expect_tx(bar, CACHE_C2_LOAD);
+#pragma unroll
+  for (int row = 0; row < 2; row++)
 #pragma unroll
     for (int plane = 0; plane < 2; plane++)
-      bulk_g2s(sbase + OFF_C2P + (uint32_t)plane * PLANE2 + (uint32_t)((2 + row) * 7) * PX, cb + cache_c2_off(set, slot) + (uint32_t)plane * CACHE_C2_ROW,
-               CACHE_C2_ROW, bar);
-  }
+      bulk_g2s(sbase + OFF_C2P + (uint32_t)plane * PLANE2 + (uint32_t)((2 + row) * 7) * PX,
+               cb + cache_c2_off(set, row ? newer : older) + (uint32_t)plane * CACHE_C2_ROW, CACHE_C2_ROW, bar);
 }
 
-__constant__ Unit c_sched[kUnits];   // k2::kSched for the epilogue loop, uploaded once by nnom_umma_configure (304 bytes: stays cached)
+__constant__ Unit c_sched[kUnits];
+__constant__ Unit c_sched_i[kUnitsI];   // k2::kSchedI, the incremental kernel's   // k2::kSched for the epilogue loop, uploaded once by nnom_umma_configure (304 bytes: stays cached)
 
 __device__ __forceinline__ uint64_t desc_from_lo(uint32_t lo) { return (uint64_t)lo | ((uint64_t)(8u | (1u << 14)) << 32); }
 
@@ -223,8 +225,7 @@ template <int POS, bool TRACE> struct IssueUnits {
       mbar_expect_tx(bar_raw, NC * kNetIn);
       bulk_g2s(sbase + OFF_RAW, J.net_in + J.batch(it + 1) * NC * kNetIn, NC * kNetIn, bar_raw);
     }
-    if (POS == kPosCacheWait && J.cached && it > 0) mbar_wait(bars + BAR_CACHE, (uint32_t)(it - 1) & 1u);   // the cached rows of this tail batch have landed
-    if (!((J.skip >> POS) & 1u) && (U.lag ? it > 0 : it < J.nbc)) IssueMmas<POS, 0>::go(tmem + slot * kSlotCols, sb4);
+    if (U.lag ? it > 0 : it < J.nbc) IssueMmas<POS, 0>::go(tmem + slot * kSlotCols, sb4);
     umma_commit(bars + 8 * slot);
     gpos++;
     if constexpr (POS + 1 < kUnits) IssueUnits<POS + 1, TRACE>::go(J, bars, bar_raw, sbase, sb4, tmem, it, gpos, lane, trace);
@@ -253,9 +254,7 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
   J.image = image; J.net_in = net_in; J.n = n; J.nb = (n + NC - 1) / NC; J.row0 = K.row0;
   J.nbc = (long long)blockIdx.x < J.nb ? (int)((J.nb - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
   J.aligned = (reinterpret_cast<uintptr_t>(net_in) & 15) == 0;
-  J.skip = K.skip_mask;
-  J.cached = K.cache != nullptr;
-  J.row_begin = ((K.skip_mask & kIncrSkipMask) == kIncrSkipMask) ? 16 : 0;
+  J.row_begin = 0;
 
   if (warp == kEpiWarps) {
     if (lane == 0) {
@@ -263,7 +262,7 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
         mbar_init(bars + 8 * s, 1);
         mbar_init(bars + 32 + 8 * s, 128);                      // one team of four warps per slot
       }
-      mbar_init(bar_raw, 1); mbar_init(bar_wts, 1); mbar_init(bars + BAR_CACHE, 1);
+      mbar_init(bar_raw, 1); mbar_init(bar_wts, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       mbar_expect_tx(bar_wts, IMAGE_BYTES);
       bulk_g2s(sbase, image, IMAGE_BYTES, bar_wts);
@@ -303,9 +302,7 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
       c.smem = smem; c.lane = lane; c.q = warp & 3; c.g = 0;
       c.clip0 = 0; c.nclips = 0; c.logits = logits; c.softmax = softmax; c.softmax_mode = softmax_mode; c.hist = hist;
       c.t_ld = 0; c.tracing = false; c.filt = K.filt; c.detect = K.detect;
-      c.cache_batch = nullptr;
-      c.cache_w_c2 = K.cache ? cache_c2_off(K.cache_set, K.cache_write) : kNoCache;
-      c.cache_w_c3 = K.cache ? cache_c3_off(K.cache_set, K.cache_write) : kNoCache;
+      c.cache_batch = nullptr; c.cache_w_c2 = kNoCache; c.cache_w_c3 = kNoCache;
       const uint32_t team = warp >> 2, ttid = tid & 127;
       const uint32_t tmem_q = tmem + ((uint32_t)(c.q * 32) << 16) + team * kSlotCols;
       const uint32_t bar_full = bars + 8 * team, bar_empty = bars + 32 + 8 * team;
@@ -320,8 +317,7 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
         const bool stamp = TRACE && trace && it == 1 && ttid == 0;
         if (stamp) trace[4 * pos + 2] = clock64();
         if (TRACE) c.tracing = stamp && pos == kPosTranspose;  // fine stamps of one unit: [4 kUnits] last ld landed, [+1] stored, [+2] fenced
-        if (!((J.skip >> pos) & 1u) && (U.lag ? it > 0 : it < J.nbc)) {
-          if (K.cache) c.cache_batch = K.cache + (size_t)J.batch(it - U.lag) * CACHE_BATCH_BYTES;
+        if (U.lag ? it > 0 : it < J.nbc) {
           if (U.kind == DN) {
             if (c.q == 0) {
               c.clip0 = J.batch(it - 1) * NC;
@@ -334,8 +330,6 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
         }
         if (stamp && c.tracing) { trace[4 * kUnits] = c.t_ld; trace[4 * kUnits + 1] = clock64(); }
         if (pos == kPosTranspose && it + 1 < J.nbc && c.q > 0) transpose_in(smem, J, it + 1, bar_raw, (int)ttid - 32, 96);   // warp 0 of the team runs the dense epilogue
-        if (pos == kPosTranspose && K.cache && it < J.nbc && ttid == 32)   // incremental mode: the cached rows of the batch whose tail runs next iteration
-          start_cached_rows(sbase, K.cache + (size_t)J.batch(it) * CACHE_BATCH_BYTES, K.cache_set, K.cache_older, K.cache_newer, bars + BAR_CACHE);
         fence_async_smem();   // this thread's shared-memory stores -> visible to the MMAs that will read them
         tc_fence_before();
         if (stamp && c.tracing) trace[4 * kUnits + 2] = clock64();
@@ -351,11 +345,161 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
   if (class_counts && tid < 10 && hist[tid]) atomicAdd(&class_counts[tid], hist[tid]);
 }
 
+// ---- incremental kernel (streaming, k2_umma_plan.h "incremental sliding-window mode") -------------------------------------------
+// Same machinery as above on the eight-unit schedule kSchedI: one pipeline stage per iteration, five batches in flight.
+template <int POS, int M> struct IssueMmasI {
+  static __device__ __forceinline__ void go(uint32_t tm, uint32_t sb4) {
+    constexpr Unit U = kSchedI[POS];
+    if constexpr (M < mma_count(U)) {
+      constexpr MmaOp op = mma_op(U, M);
+      mma_i8(tm + op.col, desc_from_lo(desc_lo(op.a_off, op.a_lbo) + sb4), desc_from_lo(desc_lo(op.b_off, op.b_lbo) + sb4), idesc_i8(op.n), op.acc);
+      IssueMmasI<POS, M + 1>::go(tm, sb4);
+    }
+  }
+};
+
+template <int POS, bool TRACE> struct IssueUnitsI {
+  static __device__ __forceinline__ void go(const Job &J, uint32_t bars, uint32_t bar_raw, uint32_t sbase, uint32_t sb4, uint32_t tmem, int it, int lane,
+                                            long long *trace) {
+    constexpr Unit U = kSchedI[POS];
+    constexpr uint32_t slot = POS & 3, par = POS >> 2;     // 8 units on 4 slots: fixed per position
+    const int b = it - U.lag;                               // this unit's batch (of this CTA)
+    const bool active = b >= 0 && b < J.nbc;
+    if (TRACE && trace && it == 5 && lane == 0) trace[4 * POS + 0] = clock64();
+    mbar_wait(bars + 32 + 8 * slot, par ^ 1);
+    tc_fence_after();
+    if (TRACE && trace && it == 5 && lane == 0) trace[4 * POS + 1] = clock64();
+    // the raw buffer (batch `it`) was consumed by the dense unit's team at position 0, whose slot this wait covered
+    if (POS == kPosI_Conv2 && it >= 1 && it + 1 < J.nbc && J.bulk(it + 1) && elect_one()) {
+      mbar_expect_tx(bar_raw, NC * kNetIn);
+      bulk_g2s(sbase + OFF_RAW, J.net_in + J.batch(it + 1) * NC * kNetIn, NC * kNetIn, bar_raw);
+    }
+    if (POS == kPosI_Conv4 && active) mbar_wait(bars + BAR_CACHE, (uint32_t)b & 1u);    // conv3's cached rows of this batch have landed
+    if (POS == kPosI_Conv3 && active) mbar_wait(bars + BAR_CACHE2, (uint32_t)b & 1u);   // conv2's cached rows of this batch have landed
+    if (active) IssueMmasI<POS, 0>::go(tmem + slot * kSlotCols, sb4);
+    umma_commit(bars + 8 * slot);
+    if constexpr (POS + 1 < kUnitsI) IssueUnitsI<POS + 1, TRACE>::go(J, bars, bar_raw, sbase, sb4, tmem, it, lane, trace);
+  }
+};
+
+template <bool TRACE>
+__global__ void __launch_bounds__(kThreads, 1)
+nnom_q7_umma_incr_kernel(const uint8_t *image, const K2Launch K) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int8_t *net_in = K.net_in;
+  const long long n = K.n;
+  long long *trace = (TRACE && blockIdx.x == 0) ? K.trace : nullptr;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t sbase = smem_u32(smem), bars = sbase + OFF_BAR;
+  const uint32_t bar_raw = bars + 64, bar_wts = bars + 72;
+  volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(smem + OFF_BAR + 80);
+  int *hist = reinterpret_cast<int *>(smem + OFF_BAR + 96);
+  Job J;
+  J.image = image; J.net_in = net_in; J.n = n; J.nb = (n + NC - 1) / NC; J.row0 = K.row0;
+  J.nbc = (long long)blockIdx.x < J.nb ? (int)((J.nb - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+  J.aligned = (reinterpret_cast<uintptr_t>(net_in) & 15) == 0;
+  J.row_begin = kIncrFirstRow;
+
+  if (warp == kEpiWarps) {
+    if (lane == 0) {
+      for (int s = 0; s < kSlots; s++) {
+        mbar_init(bars + 8 * s, 1);
+        mbar_init(bars + 32 + 8 * s, 128);
+      }
+      mbar_init(bar_raw, 1); mbar_init(bar_wts, 1); mbar_init(bars + BAR_CACHE, 1); mbar_init(bars + BAR_CACHE2, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      mbar_expect_tx(bar_wts, IMAGE_BYTES);
+      bulk_g2s(sbase, image, IMAGE_BYTES, bar_wts);
+      if (J.nbc > 0 && J.bulk(0)) {
+        mbar_expect_tx(bar_raw, NC * kNetIn);
+        bulk_g2s(sbase + OFF_RAW, net_in + J.batch(0) * NC * kNetIn, NC * kNetIn, bar_raw);
+      }
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(bars + 80), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (tid < 10) hist[tid] = 0;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  mbar_wait(bar_wts, 0);
+  if (warp < kEpiWarps && J.nbc > 0) transpose_in(smem, J, 0, bar_raw, tid, kEpiWarps * 32);
+  fence_async_smem();
+  __syncthreads();
+
+  if (J.nbc > 0) {
+    const int n_it = J.nbc + kMaxLagI;
+    if (warp == kEpiWarps) {
+      if (J.nbc > 1 && J.bulk(1) && elect_one()) {
+        mbar_expect_tx(bar_raw, NC * kNetIn);
+        bulk_g2s(sbase + OFF_RAW, net_in + J.batch(1) * NC * kNetIn, NC * kNetIn, bar_raw);
+      }
+      const uint32_t sb4 = sbase >> 4;
+#pragma unroll 1
+      for (int it = 0; it < n_it; it++) IssueUnitsI<0, TRACE>::go(J, bars, bar_raw, sbase, sb4, tmem, it, lane, trace);
+    } else {
+      DevCtx c;
+      c.smem = smem; c.lane = lane; c.q = warp & 3; c.g = 0;
+      c.clip0 = 0; c.nclips = 0; c.logits = K.logits; c.softmax = K.softmax; c.softmax_mode = K.softmax_mode; c.hist = hist;
+      c.t_ld = 0; c.tracing = false; c.filt = K.filt; c.detect = K.detect;
+      c.cache_batch = nullptr;
+      c.cache_w_c2 = cache_c2_off(K.cache_set, K.cache_write);
+      c.cache_w_c3 = cache_c3_off(K.cache_set, K.cache_write);
+      const uint32_t team = warp >> 2, ttid = tid & 127;
+      c.taddr = tmem + ((uint32_t)(c.q * 32) << 16) + team * kSlotCols;
+      const uint32_t bar_full = bars + 8 * team, bar_empty = bars + 32 + 8 * team;
+      const uint32_t total = (uint32_t)n_it * kUnitsI;
+#pragma unroll 1
+      for (uint32_t u = team; u < total; u += kSlots) {
+        const int it = (int)(u / kUnitsI), pos = (int)(u - (uint32_t)it * kUnitsI);
+        const Unit U = c_sched_i[pos];
+        const int b = it - U.lag;
+        const bool active = b >= 0 && b < J.nbc;
+        mbar_wait(bar_full, (u >> 2) & 1);
+        tc_fence_after();
+        const bool stamp = TRACE && trace && it == 5 && ttid == 0;
+        if (stamp) trace[4 * pos + 2] = clock64();
+        if (active) {
+          c.cache_batch = K.cache + (size_t)J.batch(b) * CACHE_BATCH_BYTES;
+          if (U.kind == DN) {
+            if (c.q == 0) {
+              c.clip0 = J.batch(b) * NC;
+              c.nclips = (int)min((long long)NC, J.n - c.clip0);
+              run_dense(c);
+            }
+          } else {
+            epilogue_conv(c, U);
+          }
+          // every MMA issued before this unit has completed, the readers of the previous batch's cached rows among them: fetch this batch's
+          if (pos == kPosI_Conv3 && ttid == 32) start_cached_c3(sbase, c.cache_batch, K.cache_set, K.cache_older, K.cache_newer, bars + BAR_CACHE);
+          if (pos == kPosI_Conv2 && ttid == 32) start_cached_c2(sbase, c.cache_batch, K.cache_set, K.cache_older, K.cache_newer, bars + BAR_CACHE2);
+        }
+        // the dense unit's team lays out batch `it`'s input rows (batch 0 was laid out before the loop): conv1 of batch it - 1 is done with c0
+        if (pos == kPosI_Dense && it >= 1 && it < J.nbc && c.q > 0) transpose_in(smem, J, it, bar_raw, (int)ttid - 32, 96);
+        fence_async_smem();
+        tc_fence_before();
+        mbar_arrive(bar_empty);
+        if (stamp) trace[4 * pos + 3] = clock64();
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kEpiWarps)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(512) : "memory");
+  if (K.class_counts && tid < 10 && hist[tid]) atomicAdd(&K.class_counts[tid], hist[tid]);
+}
+
 }  // namespace
 
 // ---- host side -----------------------------------------------------------------------------------------------------------
 cudaError_t nnom_umma_configure(void) {
   cudaError_t e = cudaMemcpyToSymbol(c_sched, kSched, sizeof(kSched));
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_sched_i, kSchedI, sizeof(kSchedI));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(nnom_q7_umma_incr_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(nnom_q7_umma_incr_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(nnom_q7_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
   if (e != cudaSuccess) return e;
@@ -380,13 +524,16 @@ int nnom_umma_upload(const int8_t *const w[5], const int8_t *const b[5], const i
 }
 
 size_t nnom_umma_cache_bytes(long long n) { return (size_t)((n + NC - 1) / NC) * CACHE_BATCH_BYTES; }
-uint32_t nnom_umma_incr_skip_mask(void) { return kIncrSkipMask; }
+
 
 cudaError_t launch_nnom_q7_umma(const uint8_t *image, const K2Launch &k, int sm_count, cudaStream_t stream) {
   if (k.n <= 0) return cudaSuccess;
   const long long nb = (k.n + NC - 1) / NC;
   const unsigned ctas = (unsigned)(nb < (long long)sm_count ? nb : (long long)sm_count);
-  if (k.trace) nnom_q7_umma_kernel<true><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, k);
+  if (k.cache) {   // incremental sliding-window mode
+    if (k.trace) nnom_q7_umma_incr_kernel<true><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, k);
+    else nnom_q7_umma_incr_kernel<false><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, k);
+  } else if (k.trace) nnom_q7_umma_kernel<true><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, k);
   else nnom_q7_umma_kernel<false><<<ctas, kThreads, SMEM_BYTES, stream>>>(image, k);
   count_launch();
   return cudaGetLastError();

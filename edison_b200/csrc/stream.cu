@@ -99,7 +99,6 @@ static int push_dev(edison_streams *s, const CtxView &c, const int16_t *d_pcm, i
     K2Launch k{};
     k.net_in = s->d_window; k.n = (long long)n; k.softmax_mode = c.softmax_mode; k.row0 = s->row0;
     k.cache = s->d_cache; k.cache_set = (int)(h & 3); k.cache_write = use; k.cache_newer = (use + 2) % 3; k.cache_older = (use + 1) % 3;
-    k.skip_mask = nnom_umma_incr_skip_mask();
     if (infer) { k.softmax = s->d_softmax; k.filt = s->d_filt; k.detect = s->d_detect; }
     k.trace = s->d_trace;
     CUS(launch_nnom_q7(c.model, k, c.sm_count, st));
