@@ -129,13 +129,21 @@ K2_HD uint32_t cache_c2_off(int set, int slot) { return CACHE_C2_BASE + (uint32_
 // iteration i, conv1 works on batch i, conv2 on batch i - 1, conv3 on i - 2, conv4 on i - 3, dense on i - 4 -- and within an iteration
 // the deepest stage first.  Every consumer then sits 5..7 units after its producer (previous iteration), and every writer of a
 // buffer is issued after the readers of the buffer's previous content (same iteration, earlier position), which is all the slot
-// ring needs (see the argument above).  8 units on 4 slots: a position always uses slot pos & 3, in phase pos >> 2.
+// ring needs (see the argument above).  Slots are assigned so that the two long epilogues (dense + input layout, conv2 + its cache traffic) do not
+// share one: slot_i below, two uses per slot and iteration, and every producer's slot is re-used (hence waited for) between the producer and its
+// consumers.  The next batch's input rows are laid out by the two idle warps of conv3 tile 3's team (its positions 12, 13 are wrap-around pixels),
+// whose slot's next user is the first conv1 unit.
 constexpr int kUnitsI = 8, kMaxLagI = 4;
 constexpr Unit kSchedI[kUnitsI] = {{DN, 0, 0, 4}, {C4, 0, 0, 3}, {C3, 3, 1, 2}, {C3, 4, 1, 2}, {C2, 4, 0, 1}, {C1, 2, 0, 0}, {C1, 2, 1, 0}, {C1, 2, 2, 0}};
-constexpr int kPosI_Dense = 0;    // its team lays out batch i's input rows (conv1 of batch i - 1 is done with c0; conv1 of batch i is 5 units away)
+constexpr int kPosI_Dense = 0;
 constexpr int kPosI_Conv4 = 1;    // the issuing thread waits for conv3's cached rows 0, 1 of its batch here
-constexpr int kPosI_Conv3 = 2;    // ... and for conv2's cached rows 2, 3 here; this unit's team starts the copy of conv3's rows for ITS batch
-constexpr int kPosI_Conv2 = 4;    // this unit's team starts the copy of conv2's rows for its batch; the issuing thread starts the next raw copy here
+constexpr int kPosI_Conv3 = 2;    // ... and for conv2's cached rows 2, 3 here; this unit's team starts the copy of conv3's rows for ITS batch and lays out batch i's input
+constexpr int kPosI_Conv2 = 4;    // this unit's team starts the copy of conv2's rows for its batch
+constexpr int kPosI_Conv1 = 5;    // first conv1 unit (same slot as conv3 tile 3): the issuing thread starts the next raw copy here
+// TMEM slot of each position: {0, 1, 2, 3, 1, 2, 3, 0}; positions 0..3 are a slot's first use of an iteration, 4..7 its second
+K2_HD constexpr int slot_i(int pos) { return pos < 4 ? pos : (pos == 7 ? 0 : pos - 3); }
+// the two positions each slot's team drains, in order: {0, 7}, {1, 4}, {2, 5}, {3, 6}
+K2_HD constexpr int team_pos_i(int team, int second) { return second ? (team == 0 ? 7 : team + 3) : team; }
 constexpr uint32_t CACHE_C3_LOAD = 2 * CACHE_C3_SLOT, CACHE_C2_LOAD = 2 * CACHE_C2_SLOT;
 constexpr uint32_t BAR_CACHE2 = 144;    // second cache mbarrier (conv2 rows); BAR_CACHE takes conv3's
 constexpr int kIncrFirstRow = 16;       // conv1 rows 16..23 read input rows 16..27
@@ -230,30 +238,38 @@ K2_HD int usat(int v, int bits) { return v < 0 ? 0 : (v > (1 << bits) - 1 ? (1 <
 
 // arm_softmax_q7 (reference branch arm_softmax_q7.c:217-254, SIMD branch :83-215) and local_softmax_q7 (nnom_local.c:948-1003)
 // mode: EDISON_SOFTMAX_* (0 CMSIS reference, 1 CMSIS SIMD with 8-bit wrapping subtractions, 2 NNoM local)
+// (every loop is unrolled: in and out are register arrays in the kernel -- as rolled loops they lived in local memory, on the one warp
+// whose latency the dense unit's slot waits for)
 K2_HD void softmax_q7(const int8_t *in, int8_t *out, int mode) {
   constexpr int n = 10;
   if (mode == 2) {
     int base = -257;
+#pragma unroll
     for (int i = 0; i < n; i++) base = imax(base, (int)in[i]);
     base -= 8;
     int sum = 0;
+#pragma unroll
     for (int i = 0; i < n; i++)
       if (in[i] > base) sum += 1 << usat(in[i] - base, 5);
     const int ob = 0x100000 / sum;
+#pragma unroll
     for (int i = 0; i < n; i++) out[i] = in[i] > base ? (int8_t)ssat8(ob >> usat(13 + base - in[i], 5)) : (int8_t)0;
     return;
   }
   int base = -128;
+#pragma unroll
   for (int i = 0; i < n; i++) base = imax(base, (int)in[i]);
   base -= 8;
   const int nv = mode == 1 ? (n & ~3) : 0;   // handled 4 at a time with 8-bit wrap
   int sum = 0;
+#pragma unroll
   for (int i = 0; i < n; i++) {
     int d = in[i] - base;
     if (i < nv) d = (int)(int8_t)(d & 0xff);   // __SSUB8 wraps (:127)
     sum += 1 << usat(d, 3);
   }
   const int ob = (1 << 20) / sum;
+#pragma unroll
   for (int i = 0; i < n; i++) {
     int d;
     if (i < nv) {

@@ -362,15 +362,15 @@ template <int POS, bool TRACE> struct IssueUnitsI {
   static __device__ __forceinline__ void go(const Job &J, uint32_t bars, uint32_t bar_raw, uint32_t sbase, uint32_t sb4, uint32_t tmem, int it, int lane,
                                             long long *trace) {
     constexpr Unit U = kSchedI[POS];
-    constexpr uint32_t slot = POS & 3, par = POS >> 2;     // 8 units on 4 slots: fixed per position
+    constexpr uint32_t slot = slot_i(POS), par = POS >> 2;   // 8 units on 4 slots, two uses per slot and iteration: fixed per position
     const int b = it - U.lag;                               // this unit's batch (of this CTA)
     const bool active = b >= 0 && b < J.nbc;
     if (TRACE && trace && it == 5 && lane == 0) trace[4 * POS + 0] = clock64();
     mbar_wait(bars + 32 + 8 * slot, par ^ 1);
     tc_fence_after();
     if (TRACE && trace && it == 5 && lane == 0) trace[4 * POS + 1] = clock64();
-    // the raw buffer (batch `it`) was consumed by the dense unit's team at position 0, whose slot this wait covered
-    if (POS == kPosI_Conv2 && it >= 1 && it + 1 < J.nbc && J.bulk(it + 1) && elect_one()) {
+    // the team of conv3 tile 3 (this slot's previous user) has laid out this batch's input rows: the raw buffer (batch `it`) has been consumed
+    if (POS == kPosI_Conv1 && it >= 1 && it + 1 < J.nbc && J.bulk(it + 1) && elect_one()) {
       mbar_expect_tx(bar_raw, NC * kNetIn);
       bulk_g2s(sbase + OFF_RAW, J.net_in + J.batch(it + 1) * NC * kNetIn, NC * kNetIn, bar_raw);
     }
@@ -451,16 +451,18 @@ nnom_q7_umma_incr_kernel(const uint8_t *image, const K2Launch K) {
       c.taddr = tmem + ((uint32_t)(c.q * 32) << 16) + team * kSlotCols;
       const uint32_t bar_full = bars + 8 * team, bar_empty = bars + 32 + 8 * team;
       const uint32_t total = (uint32_t)n_it * kUnitsI;
+      (void)total;
 #pragma unroll 1
-      for (uint32_t u = team; u < total; u += kSlots) {
-        const int it = (int)(u / kUnitsI), pos = (int)(u - (uint32_t)it * kUnitsI);
+      for (uint32_t j = 0; j < 2u * (uint32_t)n_it; j++) {     // the j-th use of this team's slot
+        const int it = (int)(j >> 1), pos = team_pos_i((int)team, (int)(j & 1));
         const Unit U = c_sched_i[pos];
         const int b = it - U.lag;
         const bool active = b >= 0 && b < J.nbc;
-        mbar_wait(bar_full, (u >> 2) & 1);
+        mbar_wait(bar_full, j & 1);
         tc_fence_after();
         const bool stamp = TRACE && trace && it == 5 && ttid == 0;
         if (stamp) trace[4 * pos + 2] = clock64();
+        if (TRACE) c.tracing = stamp && pos == kPosI_Dense;      // fine stamps of the dense unit: [4 kUnitsI] accumulators in registers, [+1] run_dense done
         if (active) {
           c.cache_batch = K.cache + (size_t)J.batch(b) * CACHE_BATCH_BYTES;
           if (U.kind == DN) {
@@ -472,12 +474,14 @@ nnom_q7_umma_incr_kernel(const uint8_t *image, const K2Launch K) {
           } else {
             epilogue_conv(c, U);
           }
+          if (stamp && c.tracing) { trace[4 * kUnitsI] = c.t_ld; trace[4 * kUnitsI + 1] = clock64(); }
           // every MMA issued before this unit has completed, the readers of the previous batch's cached rows among them: fetch this batch's
           if (pos == kPosI_Conv3 && ttid == 32) start_cached_c3(sbase, c.cache_batch, K.cache_set, K.cache_older, K.cache_newer, bars + BAR_CACHE);
           if (pos == kPosI_Conv2 && ttid == 32) start_cached_c2(sbase, c.cache_batch, K.cache_set, K.cache_older, K.cache_newer, bars + BAR_CACHE2);
         }
-        // the dense unit's team lays out batch `it`'s input rows (batch 0 was laid out before the loop): conv1 of batch it - 1 is done with c0
-        if (pos == kPosI_Dense && it >= 1 && it < J.nbc && c.q > 0) transpose_in(smem, J, it, bar_raw, (int)ttid - 32, 96);
+        // the two warps of conv3 tile 3's team whose positions are wrap-around pixels (no jobs) lay out batch `it`'s input rows (batch 0 was laid
+        // out before the loop): conv1 of batch it - 1 is done with c0, and the first conv1 unit of this iteration is the slot's next user
+        if (pos == kPosI_Conv3 && it >= 1 && it < J.nbc && c.q < 2) transpose_in(smem, J, it, bar_raw, (int)ttid, 64);
         fence_async_smem();
         tc_fence_before();
         mbar_arrive(bar_empty);

@@ -23,14 +23,21 @@ def main():
         chk(L.edison_streams_debug_trace(ss.handle, ctypes.c_void_p(tr.data_ptr())))
         hop(40); hop(41)
         torch.cuda.synchronize()
-    t = tr.cpu().numpy()[:4 * NU].reshape(NU, 4)
+    if mode == 2:   # the incremental kernel's eight-unit schedule; each ' = one batch back
+        kind, nu = ["DN''''", "C4'''", "C3(3)''", "C3(4)''", "C2(r4)'", "C1(t2,x0)", "C1(t2,x1)", "C1(t2,x2)"], 8
+    else:
+        kind, nu = KIND, NU
+    t = tr.cpu().numpy()[:4 * nu].reshape(nu, 4)
     t0 = t[:, 0].min()
     print("streaming mode %d, %d streams" % (mode, ns))
     print("%-12s %8s %8s %8s %8s | %7s %7s %7s" % ("unit", "wait", "issue", "ready", "released", "slotwait", "mma", "epilogue"))
-    for p in range(NU):
+    for p in range(nu):
         w, i, r, e = (t[p] - t0).tolist()
-        print("%-12s %8d %8d %8d %8d | %7d %7d %7d" % (KIND[p], w, i, r, e, i - w, r - i, e - r))
+        print("%-12s %8d %8d %8d %8d | %7d %7d %7d" % (kind[p], w, i, r, e, i - w, r - i, e - r))
     print("one iteration: last release - first wait = %d cycles" % (t[:, 3].max() - t0))
+    if mode == 2:
+        f = tr.cpu().numpy()[4 * nu:4 * nu + 2] - t0
+        print("dense unit, thread 0: ready %d -> accumulators in registers +%d -> logits / softmax / filter done +%d -> released +%d" % (t[0, 2] - t0, f[0] - (t[0, 2] - t0), f[1] - f[0], (t[0, 3] - t0) - f[1]))
 
 if __name__ == "__main__":
     main()
