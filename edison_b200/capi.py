@@ -282,7 +282,7 @@ class Streams:
     push_hop(pcm[n,1024]) -> (softmax int8 [n,10], filt float32 [n,10], detect int32 [n]); detect is the class index when
     the filtered maximum exceeds 0.5, -1 when it does not, -2 while the 31-row window is still filling."""
 
-    def __init__(self, n, incremental=False):
+    def __init__(self, n, incremental=True):
         self.n = int(n)
         self._h = ctypes.c_void_p()
         check(lib().edison_streams_open(self.n, ctypes.byref(self._h)), "edison_streams_open")

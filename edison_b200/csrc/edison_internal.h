@@ -27,7 +27,7 @@ cudaError_t launch_mfcc_q15(const MfccLaunch &p, int sm_count, cudaStream_t stre
 cudaError_t mfcc_q15_configure(void);   // opt-in to large dynamic shared memory (once)
 
 // ---- int8 net -----------------------------------------------------------------------------------
-struct NnomModel;   // device-side packed weights, defined in nnom_q7_kernel.cu
+struct NnomModel;   // opaque handle: the device pointer of K2's weight image (nnom_q7_kernel.cu)
 int nnom_load(const char *blob_path, NnomModel **out_dev_model, int *in_scale, int *in_min, int *in_max,
               char *err, size_t errlen);
 void nnom_free(NnomModel *m);
@@ -53,14 +53,6 @@ cudaError_t launch_nnom_q7(const NnomModel *model, const K2Launch &k, int sm_cou
 cudaError_t nnom_umma_configure(void);
 int nnom_umma_upload(const int8_t *const w[5], const int8_t *const b[5], const int rs[5], const int ls[5], uint8_t **out_image);
 cudaError_t launch_nnom_q7_umma(const uint8_t *image, const K2Launch &k, int sm_count, cudaStream_t stream);
-
-// incremental sliding-window inference (one new row per layer and hop); state rings live in one device allocation
-struct NnomIncrState { int8_t *c1, *p1, *c2, *p2, *c3; };
-size_t nnom_incr_state_bytes(long long n_streams);
-void nnom_incr_state_bind(NnomIncrState *st, int8_t *base, long long n_streams);
-cudaError_t launch_nnom_q7_incremental(const NnomModel *model, const int8_t *window, int row0, const NnomIncrState &st, long long n,
-                                       long long newest_row, int8_t *logits, int8_t *softmax, int softmax_mode, int sm_count,
-                                       cudaStream_t stream);
 
 // ---- debug kernels --------------------------------------------------------------------------------
 cudaError_t launch_debug_sqrt(const int32_t *d_in, size_t n, int32_t *d_out, cudaStream_t stream);

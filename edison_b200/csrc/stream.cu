@@ -12,7 +12,8 @@
 //      (moving average in double, first-maximum argmax, 0.5 threshold; app.c:336-350) fused into its dense epilogue.
 // (Round 1 issued four launches per hop -- K1, push, K2, post -- and a 1,024-stream hop was launch-latency bound.)
 // While the window fills (hops 1..31, like the firmware: app.c:311-318) a hop is K1 plus a tiny fill of detect[] = -2.
-// The opt-in incremental mode keeps its own kernel (nnom_q7_kernel.cu) plus the separate post kernel.
+// Incremental mode (edison_streams_set_incremental): K2's incremental kernel instead -- only the bottom row of every layer is computed per hop, the
+// older rows come from a row cache in HBM (k2_umma_plan.h); it runs from the first hop on (that is what fills the cache), same two launches, same bytes.
 //
 // Host callers: edison_streams_submit_hop / edison_streams_collect_hop pipeline hops through two staging slots -- the H2D copy of
 // hop h + 1 runs on a copy stream while hop h computes, results come back through pinned staging -- and edison_streams_push_hop is
@@ -32,11 +33,9 @@ struct edison_streams {
   int8_t *d_softmax;   // [n][10]
   float *d_filt;       // [n][10]
   int32_t *d_detect;   // [n]
-  int8_t *d_incr;      // ring state of the incremental net (nnom_q7_kernel.cu), 7,392 B per stream
-  edison::NnomIncrState incr;
-  int incremental;     // 0 (default): the whole window through K2 every hop, as the firmware does; 1: one new row per layer and hop
-                       // (mma.sync kernel with HBM rings); 2: the tcgen05 K2 on the bottom rows only, older rows from its row cache
-  uint8_t *d_cache;    // mode 2: row cache of nnom_q7_umma.cu (k2_umma_plan.h), 6.5 KB per stream
+  int incremental;     // 1 (default): only the bottom row of every layer per hop, older rows from the row cache (nnom_q7_umma_incr_kernel;
+                       // bit-identical, faster, 6.5 KB of HBM per stream); 0: the whole window through K2 every hop, as the firmware does
+  uint8_t *d_cache;    // incremental mode: row cache of nnom_q7_umma.cu (k2_umma_plan.h)
   long long *d_trace;  // debug: K2's per-unit clock stamps of the next hops (edison_streams_debug_trace)
   // host ingest pipeline
   int16_t *d_pcm[2];         // [n][1024] staging
@@ -46,22 +45,6 @@ struct edison_streams {
 };
 
 namespace edison {
-
-// app.c:336-350 for the incremental mode (the full-window mode has this fused into K2's dense epilogue, nnom_q7_umma.cu)
-__global__ void stream_post_kernel(const int8_t *softmax, float *filt, int32_t *detect, size_t n) {
-  const size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= n) return;
-  const double alpha = 0.9, beta = 1.0 - 0.9;
-  float best = 0.f;
-  int idx = 0;
-  for (int i = 0; i < EDISON_N_CLASSES; i++) {
-    const double o = (double)(float)softmax[s * EDISON_N_CLASSES + i];
-    const float f = (float)__dadd_rn(__dmul_rn(alpha, (double)filt[s * EDISON_N_CLASSES + i]), __dmul_rn(beta, o));
-    filt[s * EDISON_N_CLASSES + i] = f;
-    if (i == 0 || f > best) { best = f; idx = i; }
-  }
-  if (detect) detect[s] = best > 0.5f ? idx : -1;
-}
 
 __global__ void stream_fill_kernel(int32_t *detect, size_t n, int32_t v) {
   const size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -93,7 +76,7 @@ static int push_dev(edison_streams *s, const CtxView &c, const int16_t *d_pcm, i
   s->hops++;
   // the firmware fills the window (31 frames), waits for one more frame, then starts inferring (app.c:311-318)
   const bool infer = s->hops > EDISON_N_FRAMES;
-  if (s->incremental == 2) {   // runs from the first hop on: it is what fills the row cache
+  if (s->incremental) {   // runs from the first hop on: it is what fills the row cache
     const unsigned long long h = s->hops;
     const int use = (int)((h >> 2) % 3);
     K2Launch k{};
@@ -102,13 +85,6 @@ static int push_dev(edison_streams *s, const CtxView &c, const int16_t *d_pcm, i
     if (infer) { k.softmax = s->d_softmax; k.filt = s->d_filt; k.detect = s->d_detect; }
     k.trace = s->d_trace;
     CUS(launch_nnom_q7(c.model, k, c.sm_count, st));
-  } else if (s->incremental) {   // runs from the first hop on: it is what fills the rings
-    CUS(launch_nnom_q7_incremental(c.model, s->d_window, s->row0, s->incr, (long long)n, (long long)s->hops - 1, nullptr,
-                                   infer ? s->d_softmax : nullptr, c.softmax_mode, c.sm_count, st));
-    if (infer) {
-      stream_post_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s->d_softmax, s->d_filt, s->d_detect, n);
-      count_launch();
-    }
   } else if (infer) {
     K2Launch k{};
     k.net_in = s->d_window; k.n = (long long)n; k.softmax = s->d_softmax; k.softmax_mode = c.softmax_mode; k.row0 = s->row0;
@@ -153,6 +129,9 @@ int edison_streams_open(size_t n_streams, edison_streams **out) {
   if (e == cudaSuccess) e = cudaMemset(s->d_window, 0, n_streams * EDISON_NET_IN);   // netInput is zero-initialised static storage
   if (e == cudaSuccess) e = cudaMemset(s->d_filt, 0, n_streams * EDISON_N_CLASSES * sizeof(float));  // app.c:300
   if (e == cudaSuccess) e = cudaMemset(s->d_softmax, 0, n_streams * EDISON_N_CLASSES);
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_cache, nnom_umma_cache_bytes((long long)n_streams));   // incremental mode is the default
+  if (e == cudaSuccess) e = cudaMemset(s->d_cache, 0, nnom_umma_cache_bytes((long long)n_streams));
+  s->incremental = 1;
   if (e == cudaSuccess) e = cudaDeviceSynchronize();   // the memsets ran on the legacy stream; the hops run on non-blocking streams that do not wait for it
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->compute, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->copy, cudaStreamNonBlocking);
@@ -173,7 +152,7 @@ void edison_streams_close(edison_streams *s) {
   DeviceScope device_scope_;
   if (!s) return;
   cudaDeviceSynchronize();
-  void *bufs[] = {s->d_window, s->d_softmax, s->d_filt, s->d_detect, s->d_pcm[0], s->d_pcm[1], s->d_incr, s->d_cache};
+  void *bufs[] = {s->d_window, s->d_softmax, s->d_filt, s->d_detect, s->d_pcm[0], s->d_pcm[1], s->d_cache};
   for (void *b : bufs)
     if (b) cudaFree(b);
   for (int i = 0; i < 2; i++) {
@@ -199,23 +178,16 @@ int edison_streams_debug_trace(edison_streams *s, long long *d_trace) {
 int edison_streams_set_incremental(edison_streams *s, int on) {
   DeviceScope device_scope_;
   if (!s) return ctx_fail(EDISON_E_ARG, "edison_streams_set_incremental: null handle");
-  if (s->hops) return ctx_fail(EDISON_E_ARG, "edison_streams_set_incremental: only before the first hop (the rings fill from hop 1)");
-  if (on == 2 && !s->d_cache) {
+  if (s->hops) return ctx_fail(EDISON_E_ARG, "edison_streams_set_incremental: only before the first hop (the row cache fills from hop 1)");
+  if (on && !s->d_cache) {
     const size_t bytes = nnom_umma_cache_bytes((long long)s->n);
     cudaError_t e = cudaMalloc(&s->d_cache, bytes);
     if (e == cudaSuccess) e = cudaMemset(s->d_cache, 0, bytes);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) return ctx_fail(EDISON_E_NOMEM, "edison_streams_set_incremental: %s", cudaGetErrorString(e));
   }
-  if (on == 1 && !s->d_incr) {
-    const size_t bytes = nnom_incr_state_bytes((long long)s->n);
-    cudaError_t e = cudaMalloc(&s->d_incr, bytes);
-    if (e == cudaSuccess) e = cudaMemset(s->d_incr, 0, bytes);
-    if (e == cudaSuccess) e = cudaDeviceSynchronize();
-    if (e != cudaSuccess) return ctx_fail(EDISON_E_NOMEM, "edison_streams_set_incremental: %s", cudaGetErrorString(e));
-    nnom_incr_state_bind(&s->incr, s->d_incr, (long long)s->n);
-  }
-  s->incremental = on == 2 ? 2 : (on ? 1 : 0);
+  if (!on && s->d_cache) { cudaFree(s->d_cache); s->d_cache = nullptr; }
+  s->incremental = on ? 1 : 0;
   return EDISON_OK;
 }
 

@@ -126,7 +126,7 @@ def test_float_kernels_guards(edison, dev):
     assert np.array_equal(res[0][0], res[1][0]) and np.array_equal(res[0][1], res[1][1])
 
 
-@pytest.mark.parametrize("incremental", [0, 1, 2])
+@pytest.mark.parametrize("incremental", [0, 1])
 def test_stream_hop_guards(edison, dev, incremental):
     L, chk = edison.capi.lib(), edison.capi.check
     n = 37

@@ -31,7 +31,7 @@ def simulate(oracle, pcm_hops, mode=1):
     return out
 
 
-@pytest.mark.parametrize("incremental", [2, 1, 0])
+@pytest.mark.parametrize("incremental", [1, 0])
 @pytest.mark.parametrize("n", [1, 37])
 def test_streams_vs_firmware_loop(edison, oracle, n, incremental):
     hops = 58          # > 31 + 12 + 12: every ring of the incremental net wraps at least twice after inference starts
@@ -52,21 +52,19 @@ def test_streams_vs_firmware_loop(edison, oracle, n, incremental):
 
 
 def test_incremental_modes_equal_the_full_window_over_many_batches(edison):
-    """5,017 streams = 157 batches of 32 on 148 CTAs (some CTAs carry two batches, the last batch is ragged): the incremental modes
-    must give the full-window path's bytes at every hop (the full-window path is checked against the firmware loop above)"""
+    """5,017 streams = 157 batches of 32 on 148 CTAs (some CTAs carry two batches, the last batch is ragged): the incremental
+    mode must give the full-window path's bytes at every hop (the full-window path is checked against the firmware loop above)"""
     n, hops = 5017, 52
     rng = np.random.default_rng(9)
     base = synth_frames(64 * 8, seed=9).reshape(8, 64, 1024)
-    with edison.Streams(n, 0) as full, edison.Streams(n, 2) as inc2, edison.Streams(n, 1) as inc1:
+    with edison.Streams(n, 0) as full, edison.Streams(n, 1) as inc:
         for h in range(hops):
             pcm = base[h % 8][rng.integers(0, 64, n)]
-            a = full.push_hop(pcm)
-            for other, name in ((inc2, "tcgen05 row cache"), (inc1, "mma.sync rings")):
-                b = other.push_hop(pcm)
-                assert np.array_equal(a[2], b[2]), "detect, hop %d, %s" % (h, name)
-                if h + 1 > 31:
-                    assert np.array_equal(a[0], b[0]), "softmax, hop %d, %s" % (h, name)
-                assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), "filter bits, hop %d, %s" % (h, name)
+            a, b = full.push_hop(pcm), inc.push_hop(pcm)
+            assert np.array_equal(a[2], b[2]), "detect, hop %d" % h
+            if h + 1 > 31:
+                assert np.array_equal(a[0], b[0]), "softmax, hop %d" % h
+            assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), "filter bits, hop %d" % h
 
 
 def test_streams_detects_when_softmax_saturates(edison, oracle):

@@ -1,5 +1,5 @@
 #!/usr/bin/env python3
-"""Device-resident hop time of the streaming modes (0 = full window, 2 = tcgen05 K2 on the bottom rows + row cache, 1 = mma.sync rings) for a few stream
+"""Device-resident hop time of the streaming modes (0 = full window, 1 = incremental: the bottom row of every layer + row cache) for a few stream
 counts: p50 / p99 over 300 hops, CUDA events on the launching stream.  usage: stream_modes_time.py [n ...]"""
 import ctypes, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -12,7 +12,7 @@ st = torch.cuda.Stream(); torch.cuda.set_stream(st)
 sp = ctypes.c_void_p(st.cuda_stream)
 for ns in [int(a) for a in sys.argv[1:]] or [1024, 16384, 100000]:
     pcm = (torch.randn(4 * ns * 1024, device="cuda") * 3000).to(torch.int16)
-    for mode in (0, 2, 1):
+    for mode in (0, 1):
         with ed.Streams(ns, mode) as ss:
             hop = lambda h: chk(L.edison_streams_push_hop_dev(ss.handle, ctypes.c_void_p(pcm[(h % 4) * ns * 1024:].data_ptr()), None, None, None, sp))
             for h in range(40):
