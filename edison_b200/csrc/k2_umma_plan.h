@@ -287,7 +287,7 @@ K2_HD void softmax_q7(const int8_t *in, int8_t *out, int mode) {
 //   c.st16(off, Vec16) : 16-byte shared-memory store;  c.st16_cache(off, Vec16): 16-byte store into this batch's row cache (incremental mode:
 //   c.cache_w_c2 / c.cache_w_c3 = offsets of the slots being written, kNoCache otherwise);  c.par(i) / c.par4(i): int32 parameter(s) i (same for all lanes)
 //   c.lane (= clip), c.q (lane quarter = pixel within an M = 128 tile);  dense only: c.clip0 (first clip of the batch),
-//   c.nclips, c.logits, c.softmax (global, may be null), c.softmax_mode, c.count(cls) (class histogram hook),
+//   c.nclips, c.logits, c.softmax (global, may be null), c.softmax_mode, c.counting + c.count(cls) (class histogram hook),
 //   c.filt (null or the streaming filter state) with c.prefetch(clip) (start loading the state) and c.post(clip, softmax)
 // One warp per lane quarter drains a whole unit: lean loops (a job = 16 accumulator columns -> one 16-byte store is ~75
 // instructions; evaluating a generic job descriptor per job tripled that and the epilogue is latency bound).
@@ -371,8 +371,10 @@ template <class Ctx> K2_HD void run_dense(Ctx &c) {
   c.ld_wait();
   if (c.lane < c.nclips) {
     int8_t lg[10];
+    int seed[16];
+    load16(c, PAR_SEEDD, seed);
 #pragma unroll
-    for (int i = 0; i < 10; i++) lg[i] = (int8_t)ssat8(((int)e[i] + c.par(PAR_SEEDD + i)) >> rs);
+    for (int i = 0; i < 10; i++) lg[i] = (int8_t)ssat8(((int)e[i] + seed[i]) >> rs);
     const long long clip = c.clip0 + c.lane;
     if (c.logits)
 #pragma unroll
@@ -385,11 +387,13 @@ template <class Ctx> K2_HD void run_dense(Ctx &c) {
         for (int i = 0; i < 10; i++) c.softmax[clip * 10 + i] = sm[i];
       if (c.filt) c.post(clip, sm);   // streaming: moving average, argmax, threshold (app.c:336-350)
     }
-    int best = 0;   // first maximum of the logits: the class the firmware's arm_max would report on them
+    if (c.counting) {   // class histogram (edison_kws_counts_dev): first maximum of the logits, the class the firmware's arm_max would report on them
+      int best = 0, bestv = lg[0];   // (the value is tracked beside the index: lg[best] would be a run-time index into a register array)
 #pragma unroll
-    for (int i = 1; i < 10; i++)
-      if (lg[i] > lg[best]) best = i;
-    c.count(best);
+      for (int i = 1; i < 10; i++)
+        if (lg[i] > bestv) { bestv = lg[i]; best = i; }
+      c.count(best);
+    }
   }
 }
 

@@ -78,6 +78,7 @@ struct DevCtx {
   int8_t *logits, *softmax;
   int softmax_mode;
   int *hist;        // shared-memory class histogram
+  bool counting;    // the caller asked for the class histogram
   float *filt;      // streaming post-processing (null: none)
   int32_t *detect;
   uint8_t *cache_batch;               // incremental mode: this unit's batch in the row cache
@@ -145,7 +146,7 @@ __device__ __forceinline__ void transpose_in(uint8_t *smem, const Job &J, int k,
   const bool bulk = J.bulk(k);
   if (bulk) mbar_wait(raw_bar, (uint32_t)k & 1u);
   const int clip = tid & 31;
-#pragma unroll 1
+#pragma unroll 3
   for (int row = J.row_begin + (tid >> 5); row < kInRowsUsed; row += nthreads >> 5) {
     {
       const uint32_t a = raw_offset(clip, row, J.row0);
@@ -301,7 +302,7 @@ nnom_q7_umma_kernel(const uint8_t *image, const K2Launch K) {
       DevCtx c;
       c.smem = smem; c.lane = lane; c.q = warp & 3; c.g = 0;
       c.clip0 = 0; c.nclips = 0; c.logits = logits; c.softmax = softmax; c.softmax_mode = softmax_mode; c.hist = hist;
-      c.t_ld = 0; c.tracing = false; c.filt = K.filt; c.detect = K.detect;
+      c.t_ld = 0; c.tracing = false; c.filt = K.filt; c.detect = K.detect; c.counting = K.class_counts != nullptr;
       c.cache_batch = nullptr; c.cache_w_c2 = kNoCache; c.cache_w_c3 = kNoCache;
       const uint32_t team = warp >> 2, ttid = tid & 127;
       const uint32_t tmem_q = tmem + ((uint32_t)(c.q * 32) << 16) + team * kSlotCols;
@@ -443,7 +444,7 @@ nnom_q7_umma_incr_kernel(const uint8_t *image, const K2Launch K) {
       DevCtx c;
       c.smem = smem; c.lane = lane; c.q = warp & 3; c.g = 0;
       c.clip0 = 0; c.nclips = 0; c.logits = K.logits; c.softmax = K.softmax; c.softmax_mode = K.softmax_mode; c.hist = hist;
-      c.t_ld = 0; c.tracing = false; c.filt = K.filt; c.detect = K.detect;
+      c.t_ld = 0; c.tracing = false; c.filt = K.filt; c.detect = K.detect; c.counting = K.class_counts != nullptr;
       c.cache_batch = nullptr;
       c.cache_w_c2 = cache_c2_off(K.cache_set, K.cache_write);
       c.cache_w_c3 = cache_c3_off(K.cache_set, K.cache_write);

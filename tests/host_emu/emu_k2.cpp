@@ -56,6 +56,7 @@ struct Ctx {
   int softmax_mode;
   long long *hist;
   float *filt = nullptr;
+  bool counting = true;
   uint32_t cache_w_c2 = kNoCache, cache_w_c3 = kNoCache;
   void st16_cache(uint32_t, Vec16) {}
   void prefetch(long long) {}
