@@ -67,6 +67,30 @@ def test_incremental_modes_equal_the_full_window_over_many_batches(edison):
             assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), "filter bits, hop %d" % h
 
 
+def test_incremental_mode_over_many_cache_rotations(edison):
+    """the row cache rotates with period 12 hops (four phase sets x three slots): 150 hops on a ragged stream count, every hop compared
+    with the full-window mode, through the pipelined submit / collect calls on one side and push_hop on the other"""
+    n, hops = 97, 150
+    rng = np.random.default_rng(21)
+    base = synth_frames(48 * 6, seed=21).reshape(6, 48, 1024)
+    with edison.Streams(n, 0) as full, edison.Streams(n, 1) as inc:
+        pending, alive = None, []
+        for h in range(hops):
+            pcm = np.ascontiguousarray(base[h % 6][rng.integers(0, 48, n)])
+            want = full.push_hop(pcm)
+            alive = alive[-1:] + [inc.submit_hop(pcm)]      # a submitted hop's samples stay alive until it is collected
+            if pending is not None:
+                got = inc.collect_hop()
+                for k in (0, 1, 2):
+                    a, b = pending[k], got[k]
+                    if k == 0 and h <= 31:
+                        continue
+                    assert np.array_equal(a.view(np.uint32) if a.dtype == np.float32 else a, b.view(np.uint32) if b.dtype == np.float32 else b), (h - 1, k)
+            pending = want
+        got = inc.collect_hop()
+        assert np.array_equal(pending[2], got[2]) and np.array_equal(pending[0], got[0])
+
+
 def test_streams_detects_when_softmax_saturates(edison, oracle):
     """Feed the same loud frame for many hops: the filter converges to the softmax output, so some class crosses 0.5
     exactly when the simulation says so (exercises the detect >= 0 branch)."""
