@@ -58,7 +58,8 @@ struct Ctx {
   float *filt = nullptr;
   bool counting = true;
   uint32_t cache_w_c2 = kNoCache, cache_w_c3 = kNoCache;
-  void st16_cache(uint32_t, Vec16) {}
+  uint8_t *cache_batch = nullptr;      // incremental mode: this unit's batch in the row cache
+  void st16_cache(uint32_t off, Vec16 v) { memcpy(cache_batch + off, &v, 16); }
   void prefetch(long long) {}
   void post(long long, const int8_t *) {}
   void ld16(uint32_t col, uint32_t (&v)[16]) {
@@ -71,12 +72,12 @@ struct Ctx {
   void count(int cls) { if (hist) hist[cls]++; }
 };
 
-void transpose_in(Emu &E, const int8_t *net_in, long long n, long long batch) {
+void transpose_in(Emu &E, const int8_t *net_in, long long n, long long batch, int row_begin = 0) {
   const long long clip0 = batch * NC;
   const int nclips = (int)((n - clip0) < NC ? (n - clip0) : NC);
   memset(&E.smem[OFF_RAW], 0x77, RAW_BYTES);
   memcpy(&E.smem[OFF_RAW], net_in + clip0 * kNetIn, (size_t)nclips * kNetIn);
-  for (int row = 0; row < kInRowsUsed; row++)
+  for (int row = row_begin; row < kInRowsUsed; row++)
     for (int clip = 0; clip < NC; clip++) {
       const uint32_t a = raw_offset(clip, row, 0);
       uint32_t w[4];
@@ -154,3 +155,121 @@ extern "C" int emu_k2_run(const char *blob_path, const int8_t *net_in, long long
 
 extern "C" unsigned emu_k2_image_bytes(void) { return IMAGE_BYTES; }
 extern "C" unsigned emu_k2_smem_bytes(void) { return SMEM_BYTES; }
+
+// ---- incremental mode (k2_umma_plan.h kSchedI; nnom_q7_umma_incr_kernel) --------------------------------------------------------------
+// One CTA, consecutive batches, one hop.  The row cache [nb][CACHE_BATCH_BYTES] persists across calls (hops).  Order of execution:
+//   lazy : every unit's MMAs right before its epilogue;
+//   eager: before each epilogue, the issuing thread runs as far ahead as the kernel lets it -- a unit's MMAs may run once the previous
+//          user of its TMEM slot (slot_i) has been drained and, for the units that read cached rows, once the copy started by an earlier
+//          epilogue has been made -- the other extreme, so that a missing dependency shows as a mismatch in one of the two orders.
+namespace {
+
+struct IncrRun {
+  Emu &E;
+  const int8_t *net_in;
+  long long n, nb;
+  uint8_t *cache;
+  int set, older, newer, write;
+  int8_t *softmax;
+  int mode;
+  long long n_units;
+  std::vector<char> mma_done, drained, c2_copied, c3_copied;   // per unit number / per batch
+
+  const Unit &unit(long long u) const { return kSchedI[u % kUnitsI]; }
+  long long batch_of(long long u) const { return u / kUnitsI - unit(u).lag; }
+  bool active(long long u) const { const long long b = batch_of(u); return b >= 0 && b < nb; }
+  // the previous unit that used the same TMEM slot
+  long long prev_same_slot(long long u) const {
+    for (long long v = u - 1; v >= 0; v--)
+      if (slot_i((int)(v % kUnitsI)) == slot_i((int)(u % kUnitsI))) return v;
+    return -1;
+  }
+  bool may_issue(long long u) const {
+    const long long p = prev_same_slot(u);
+    if (p >= 0 && !drained[p]) return false;
+    const int pos = (int)(u % kUnitsI);
+    if (active(u) && pos == kPosI_Conv4 && !c3_copied[batch_of(u)]) return false;
+    if (active(u) && pos == kPosI_Conv3 && !c2_copied[batch_of(u)]) return false;
+    return true;
+  }
+  void do_mma(long long u) {
+    if (active(u))
+      for (int m = 0; m < mma_count(unit(u)); m++) E.mma(mma_op(unit(u), m), slot_i((int)(u % kUnitsI)));
+    mma_done[u] = 1;
+  }
+  void copy_rows(uint32_t dst, const uint8_t *src, uint32_t bytes) { memcpy(&E.smem[dst], src, bytes); }
+  void do_epilogue(long long u) {
+    const int pos = (int)(u % kUnitsI);
+    const long long it = u / kUnitsI;
+    const Unit U = unit(u);
+    if (active(u)) {
+      const long long b = batch_of(u);
+      uint8_t *cb = cache + (size_t)b * CACHE_BATCH_BYTES;
+      for (int q = 0; q < 4; q++)
+        for (int lane = 0; lane < 32; lane++) {
+          Ctx c;
+          c.e = &E; c.slot = slot_i(pos); c.lane = lane; c.q = q; c.g = 0;
+          c.clip0 = b * NC;
+          c.nclips = (int)((n - c.clip0) < NC ? (n - c.clip0) : NC);
+          c.logits = nullptr; c.softmax = softmax; c.softmax_mode = mode; c.hist = nullptr; c.counting = false;
+          c.cache_batch = cb; c.cache_w_c2 = cache_c2_off(set, write); c.cache_w_c3 = cache_c3_off(set, write);
+          if (U.kind == DN) {
+            if (q == 0) run_dense(c);
+          } else {
+            epilogue_conv(c, U);
+          }
+        }
+      // the bulk copies the kernel's teams start at this point (they have landed before the consumers are issued: c*_copied)
+      if (pos == kPosI_Conv3) {
+        for (int row = 0; row < 2; row++)
+          for (int plane = 0; plane < 4; plane++)
+            copy_rows(OFF_C3 + plane * PLANE3 + row * 5 * PX, cb + cache_c3_off(set, row ? newer : older) + plane * CACHE_C3_ROW, CACHE_C3_ROW);
+        c3_copied[b] = 1;
+      }
+      if (pos == kPosI_Conv2) {
+        for (int row = 0; row < 2; row++)
+          for (int plane = 0; plane < 2; plane++)
+            copy_rows(OFF_C2P + plane * PLANE2 + (2 + row) * 7 * PX, cb + cache_c2_off(set, row ? newer : older) + plane * CACHE_C2_ROW, CACHE_C2_ROW);
+        c2_copied[b] = 1;
+      }
+    }
+    if (pos == kPosI_Conv3 && it >= 1 && it < nb) transpose_in(E, net_in, n, it, kIncrFirstRow);
+    drained[u] = 1;
+  }
+};
+
+}  // namespace
+
+// one hop of the incremental mode over n windows [n][403] (logical row order); cache: [ceil(n / 32)][CACHE_BATCH_BYTES], kept by the caller
+// between hops; set / older / newer / write as stream.cu derives them from the hop number.  softmax [n][10].
+extern "C" int emu_k2_incr_hop(const char *blob_path, const int8_t *net_in, long long n, uint8_t *cache, int set, int older, int newer, int write,
+                               int8_t *softmax, int mode, int eager) {
+  KwsBlob blob;
+  char err[256] = "";
+  int r = read_kws_blob(blob_path, blob, err, sizeof err);
+  if (r) { fprintf(stderr, "emu_k2_incr_hop: %s\n", err); return r; }
+  const int8_t *w[5], *b[5];
+  int rs[5], ls[5];
+  for (int i = 0; i < 5; i++) { w[i] = blob.L[i].w; b[i] = blob.L[i].b; rs[i] = (int)blob.L[i].h[5]; ls[i] = (int)blob.L[i].h[6]; }
+  Emu E;
+  build_image(E.smem.data(), w, b, rs, ls);
+  const long long nb = (n + NC - 1) / NC;
+  if (nb == 0) return 0;
+  IncrRun R{E, net_in, n, nb, cache, set, older, newer, write, softmax, mode, (nb + kMaxLagI) * kUnitsI, {}, {}, {}, {}};
+  R.mma_done.assign(R.n_units, 0); R.drained.assign(R.n_units, 0);
+  R.c2_copied.assign(nb, 0); R.c3_copied.assign(nb, 0);
+  transpose_in(E, net_in, n, 0, kIncrFirstRow);
+  long long issued = 0;
+  for (long long u = 0; u < R.n_units; u++) {
+    if (eager)
+      while (issued < R.n_units && R.may_issue(issued)) R.do_mma(issued++);
+    if (!R.mma_done[u]) {
+      if (!R.may_issue(u)) { fprintf(stderr, "emu_k2_incr_hop: unit %lld can never be issued (dependency cycle)\n", u); return -2; }
+      while (issued <= u) R.do_mma(issued++);
+    }
+    R.do_epilogue(u);
+  }
+  return 0;
+}
+
+extern "C" unsigned emu_k2_cache_batch_bytes(void) { return CACHE_BATCH_BYTES; }

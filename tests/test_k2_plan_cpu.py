@@ -61,3 +61,29 @@ def test_plan_on_real_net_inputs(emu, oracle):
     want_lg, want_sm = oracle.forward(ni, 1)
     lg, sm, _ = run(emu, ni, 1, 1)
     assert np.array_equal(lg, want_lg) and np.array_equal(sm, want_sm)
+
+
+@pytest.mark.parametrize("eager", [0, 1])
+def test_incremental_schedule_matches_full_window(emu, oracle, eager):
+    """the incremental mode's own schedule (kSchedI: one pipeline stage per iteration, static slot map, row cache with four phase sets of
+    three slots) emulated hop by hop on sliding windows: from the first inferring hop on, its softmax must equal the oracle's on the whole
+    window.  Three batches on one CTA (the last one ragged), so that five batches' stages overlap; both execution orders."""
+    n, hops = 70, 46
+    rng = np.random.default_rng(31)
+    rows = rng.integers(-128, 128, (hops + 31, n, 13)).astype(np.int8)      # row t of every stream; the window at hop h is rows h .. h + 30
+    rows[:, 0, :] = 0
+    emu.emu_k2_cache_batch_bytes.restype = ctypes.c_uint
+    nb = (n + 31) // 32
+    cache = np.zeros(nb * emu.emu_k2_cache_batch_bytes(), np.uint8)
+    checked = 0
+    for h in range(1, hops + 1):
+        win = np.ascontiguousarray(rows[h:h + 31].transpose(1, 0, 2).reshape(n, 403))
+        use = (h >> 2) % 3
+        sm = np.full((n, 10), 99, np.int8)
+        assert emu.emu_k2_incr_hop(common.BLOB.encode(), common._p(win), ctypes.c_longlong(n), common._p(cache), h & 3, (use + 1) % 3, (use + 2) % 3, use,
+                                   common._p(sm), 1, eager) == 0
+        if h >= 20:      # every cached row in use was computed from real rows by now (8 hops of history; stream.cu infers from hop 32 on)
+            _, want = oracle.forward(win, 1)
+            assert np.array_equal(sm, want), "hop %d" % h
+            checked += 1
+    assert checked == hops - 19
