@@ -18,6 +18,7 @@
 namespace edison {
 
 constexpr int kWarpsPerCta = 20;
+constexpr int kWindowStride = EDISON_NET_IN;   // STRIDED instantiations: one 13-byte row into each stream's 403-byte window (stream.cu)
 constexpr int kThreads = kWarpsPerCta * 32;
 
 struct WarpSmem {
@@ -125,7 +126,7 @@ __device__ __forceinline__ void group_tail(const MfccLaunch &P, const MfccTables
             // STRIDED (the streaming path: one row of each stream's window) is a separate instantiation: with the stride as a run-time
       // value in the batch kernel, bench.py's launch went from 10.87 to 11.29 ms (register allocation of the hot loop shifts)
       if (f0 + fr < n_frames && (!SMALL || fr < gf))
-        P.net_in[(f0 + fr) * (STRIDED ? P.net_in_stride : (long long)kNCoeff) + c] = (int8_t)net_input_q7(out[32 * fr + c], T);
+        P.net_in[(f0 + fr) * (long long)(STRIDED ? kWindowStride : kNCoeff) + c] = (int8_t)net_input_q7(out[32 * fr + c], T);
     }
   }
   __syncwarp();
@@ -247,7 +248,8 @@ cudaError_t launch_mfcc_q15(const MfccLaunch &p_in, int sm_count, cudaStream_t s
   warps = warps >= kWarpsPerCta ? kWarpsPerCta : (warps + 3) / 4 * 4;
   const unsigned threads = (unsigned)warps * 32;
   const bool aligned = (reinterpret_cast<uintptr_t>(p.pcm) & 3u) == 0 && (p.clip_stride & 1) == 0;
-  const bool strided = p.net_in && p.net_in_stride != kNCoeff;
+  if (p.net_in && p.net_in_stride != kNCoeff && p.net_in_stride != kWindowStride) return cudaErrorInvalidValue;   // packed rows or window rows only
+  const bool strided = p.net_in && p.net_in_stride == kWindowStride;
   const bool small = gf != kGroup;
   if (aligned && !strided) launch_one<true, false>(p, small, (unsigned)ctas, threads, stream);
   else if (!strided) launch_one<false, false>(p, small, (unsigned)ctas, threads, stream);
