@@ -14,7 +14,9 @@
 //     tensor core's asynchronous proxy, and release the slot (mbarrier empty[slot]);
 //   * the unit order interleaves the head of batch b with the tail of batch b - 1 so that every unit's producers are
 //     at least four units older: the only waits are those of the four-slot TMEM ring (one team of four epilogue warps per slot).
-// There is no CPU path and no legacy mma.sync path behind this entry point.
+// Two kernels share this machinery: nnom_q7_umma_kernel (the whole window, 21 units per iteration) and nnom_q7_umma_incr_kernel (the streaming
+// path's incremental mode: the bottom row of every layer per hop on an eight-unit schedule, older rows from a row cache in HBM; k2_umma_plan.h).
+// There is no CPU path and no legacy mma.sync path behind these entry points.
 #include <stdio.h>
 #include <stdlib.h>
 
